@@ -1,0 +1,113 @@
+// Turning a sequence into a time.
+//
+// Reference: include/tenzing/benchmarker.hpp:14-57, src/benchmarker.cpp:21-223.
+//  * EmpiricalBenchmarker: host-wall measurement with the reference's protocol
+//    (calibrate samples/measurement to >= 10 ms, nIters measurements, max over
+//    ranks, runs-test gate with retries, percentiles).
+//  * DeviceBenchmarker: same protocol but each measurement is timed on the
+//    device with CUDA events recorded on every platform stream (first start ->
+//    last stop), max over ranks - what BASELINE.json calls "device-timed".
+//  * CsvBenchmarker: replays a results CSV (both the DFS form with an opts line
+//    and the header-less MCTS form).
+//  * ModelBenchmarker: a cost model callback - toy problems and solver tests.
+#pragma once
+
+#include <functional>
+#include <istream>
+#include <unordered_map>
+#include <string>
+#include <vector>
+
+#include "tenzing/graph.hpp"
+#include "tenzing/platform.hpp"
+#include "tenzing/schedule.hpp"
+#include "tenzing/sequence.hpp"
+
+namespace tenzing {
+
+namespace Benchmark {
+struct Result {
+  double pct01 = 0, pct10 = 0, pct50 = 0, pct90 = 0, pct99 = 0, stddev = 0;
+  static Result from_samples(std::vector<double> samples);
+};
+struct Opts {
+  size_t nIters = 1000;     // measurements per sequence
+  size_t maxRetries = 10;   // re-measure while the series fails the runs test
+  double targetSecs = 0.01; // minimum duration of one measurement
+  bool checkRandomness = true;
+};
+} // namespace Benchmark
+
+class Benchmarker {
+public:
+  virtual ~Benchmarker() = default;
+  virtual Benchmark::Result benchmark(Sequence<BoundOp> &order, Platform &plat,
+                                      const Benchmark::Opts &opts = Benchmark::Opts()) = 0;
+};
+
+// run `order` once under a fresh epoch
+void run_sequence(Sequence<BoundOp> &order, Platform &plat);
+
+class EmpiricalBenchmarker : public Benchmarker {
+public:
+  Benchmark::Result benchmark(Sequence<BoundOp> &order, Platform &plat,
+                              const Benchmark::Opts &opts = Benchmark::Opts()) override;
+  // interleaved measurement of several schedules in a fresh random order per iteration
+  std::vector<Benchmark::Result> benchmark(std::vector<Schedule> &schedules, Platform &plat,
+                                           const Benchmark::Opts &opts = Benchmark::Opts());
+
+protected:
+  struct Measurement {
+    size_t nSamples;
+    double time; // seconds per sample, max over ranks
+  };
+  // one measurement of nSamples back-to-back executions
+  virtual double timed_run(Sequence<BoundOp> &order, Platform &plat, size_t nSamples);
+  Measurement measure(Sequence<BoundOp> &order, Platform &plat, size_t nSamplesHint,
+                      double targetSecs);
+};
+
+class DeviceBenchmarker : public EmpiricalBenchmarker {
+  std::vector<cudaEvent_t> starts_, stops_;
+  cudaEvent_t fence_ = nullptr;
+
+public:
+  ~DeviceBenchmarker() override;
+
+protected:
+  double timed_run(Sequence<BoundOp> &order, Platform &plat, size_t nSamples) override;
+};
+
+class CsvBenchmarker : public Benchmarker {
+public:
+  struct DataRow {
+    Benchmark::Result res;
+    Sequence<BoundOp> seq;
+  };
+  CsvBenchmarker(const std::string &path, const Graph<OpBase> &g);
+  static CsvBenchmarker from_text(const std::string &text, const Graph<OpBase> &g);
+  Benchmark::Result benchmark(Sequence<BoundOp> &order, Platform &plat,
+                              const Benchmark::Opts &opts = Benchmark::Opts()) override;
+  const std::vector<DataRow> &rows() const { return data_; }
+
+private:
+  CsvBenchmarker() = default;
+  void load(std::istream &is, const Graph<OpBase> &g);
+  std::vector<DataRow> data_;
+  std::unordered_map<std::string, size_t> byKey_; // canonical key -> row
+};
+
+class ModelBenchmarker : public Benchmarker {
+  std::function<double(const Sequence<BoundOp> &)> model_;
+
+public:
+  explicit ModelBenchmarker(std::function<double(const Sequence<BoundOp> &)> model)
+      : model_(std::move(model)) {}
+  Benchmark::Result benchmark(Sequence<BoundOp> &order, Platform &plat,
+                              const Benchmark::Opts &opts = Benchmark::Opts()) override;
+};
+
+// one CSV row: idx|pct01|pct10|pct50|pct90|pct99|stddev|<op json>|...
+std::string csv_row(size_t idx, const Benchmark::Result &r, const Sequence<BoundOp> &seq);
+
+} // namespace tenzing

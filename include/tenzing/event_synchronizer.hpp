@@ -1,0 +1,46 @@
+// Decides which CUDA synchronisation a candidate op still needs, given the
+// graph's edges and the sequence built so far.
+//
+// Rules (reference: include/tenzing/event_synchronizer.hpp:7-330; table in
+// SURVEY §3.3) for a graph edge p -> v, with p already in the sequence:
+//   Start -> any, CPU -> CPU, CPU -> GPU        nothing
+//   GPU(s) -> GPU(s)                            nothing (stream order)
+//   GPU(s1) -> GPU(s2)   CudaEventRecord(e,s1) after p, then CudaStreamWaitEvent(s2,e)
+//   GPU(s1) -> CPU       CudaEventRecord(e,s1) after p, then CudaEventSync(e)
+// make_syncs returns, per predecessor, only the NEXT missing op of its chain
+// (first the record, on a later call the wait), so where the record and the
+// wait are placed relative to other ready ops is itself part of the search.
+#pragma once
+
+#include <vector>
+
+#include "tenzing/graph.hpp"
+#include "tenzing/sequence.hpp"
+
+namespace tenzing {
+
+struct EventSynchronizer {
+  // true iff every graph predecessor of `bo` found in `path` is synchronised with it
+  static bool is_synced(const BoundOpPtr &bo, const Graph<OpBase> &g,
+                        const Sequence<BoundOp> &path);
+  // next missing synchronisation ops (deduplicated); empty iff is_synced
+  static std::vector<BoundOpPtr> make_syncs(const BoundOpPtr &bo, const Graph<OpBase> &g,
+                                            const Sequence<BoundOp> &path, bool quiet = true);
+
+  // building blocks, exposed like the reference's
+  static bool is_synced_gpu_then_cpu(const std::shared_ptr<BoundGpuOp> &a,
+                                     const Sequence<BoundOp> &path);
+  static bool is_synced_gpu_then_gpu(const std::shared_ptr<BoundGpuOp> &a,
+                                     const std::shared_ptr<BoundGpuOp> &b,
+                                     const Sequence<BoundOp> &path);
+  static BoundOpPtr make_sync_gpu_then_cpu(const std::shared_ptr<BoundGpuOp> &a,
+                                           const std::shared_ptr<CpuOp> &b,
+                                           const Sequence<BoundOp> &path);
+  static BoundOpPtr make_sync_gpu_then_gpu(const std::shared_ptr<BoundGpuOp> &a,
+                                           const std::shared_ptr<BoundGpuOp> &b,
+                                           const Sequence<BoundOp> &path);
+};
+
+using Synchronizer = EventSynchronizer;
+
+} // namespace tenzing

@@ -1,0 +1,365 @@
+// The program as a DAG of operations, always bracketed by Start and Finish.
+//
+// Reference: include/tenzing/graph.hpp:19-580, src/graph.cpp:13-420.  Same
+// vocabulary (start_then / then / then_finish / clone_but_replace /
+// clone_but_expand / frontier / dump_graphviz ...), different representation:
+// vertices live in a dense vector, edges are integer adjacency lists and a
+// hash index maps an op's interned uid to its vertex.  Rewrites copy the
+// (small) index arrays and share the op objects, so the solvers can afford a
+// graph per decision.
+#pragma once
+
+#include <algorithm>
+#include <fstream>
+#include <memory>
+#include <sstream>
+#include <unordered_map>
+#include <vector>
+
+#include "tenzing/cuda/ops_cuda.hpp"
+#include "tenzing/operation.hpp"
+
+namespace tenzing {
+
+template <typename T> class Graph {
+public:
+  using op_t = std::shared_ptr<T>;
+  using vid_t = int;
+
+private:
+  struct Vertex {
+    op_t op;
+    std::vector<vid_t> succs, preds;
+    bool alive = true;
+  };
+  std::vector<Vertex> v_;
+  std::unordered_map<uint32_t, vid_t> index_;  // op uid -> vertex
+  std::unordered_map<uint32_t, vid_t> uindex_; // op unbound uid -> vertex
+  vid_t start_ = -1, finish_ = -1;
+
+  static void add_unique(std::vector<vid_t> &v, vid_t x) {
+    if (std::find(v.begin(), v.end(), x) == v.end()) v.push_back(x);
+  }
+  static void remove_one(std::vector<vid_t> &v, vid_t x) {
+    v.erase(std::remove(v.begin(), v.end(), x), v.end());
+  }
+  vid_t add_vertex(const op_t &op) {
+    auto it = index_.find(op->uid());
+    if (it != index_.end()) return it->second;
+    vid_t id = static_cast<vid_t>(v_.size());
+    v_.push_back(Vertex{op, {}, {}, true});
+    index_.emplace(op->uid(), id);
+    uindex_.emplace(op->unbound_uid(), id);
+    return id;
+  }
+  void add_edge(vid_t a, vid_t b) {
+    add_unique(v_[a].succs, b);
+    add_unique(v_[b].preds, a);
+  }
+  std::vector<op_t> ops_of(const std::vector<vid_t> &ids) const {
+    std::vector<op_t> r;
+    r.reserve(ids.size());
+    for (vid_t i : ids) r.push_back(v_[i].op);
+    return r;
+  }
+  vid_t must_find(const OpBase &op) const {
+    vid_t i = find_vertex(op);
+    if (i < 0) THROW_RUNTIME("op " << op.desc() << " is not in the graph");
+    return i;
+  }
+
+public:
+  Graph() {
+    start_ = add_vertex(std::make_shared<Start>());
+    finish_ = add_vertex(std::make_shared<Finish>());
+  }
+
+  // ---- construction ----
+  const op_t &start() const { return v_[start_].op; }
+  const op_t &finish() const { return v_[finish_].op; }
+
+  // Start -> op
+  const op_t &start_then(const op_t &op) {
+    vid_t b = add_vertex(op);
+    add_edge(start_, b);
+    return v_[b].op;
+  }
+  // a -> b; neither may be Start or Finish (use start_then / then_finish)
+  const op_t &then(const op_t &a, const op_t &b) {
+    if (a->uid() == v_[start_].op->uid() || a->uid() == v_[finish_].op->uid() ||
+        b->uid() == v_[start_].op->uid() || b->uid() == v_[finish_].op->uid()) {
+      THROW_RUNTIME("Graph::then does not take Start/Finish; use start_then/then_finish");
+    }
+    vid_t ia = add_vertex(a), ib = add_vertex(b);
+    add_edge(ia, ib);
+    return v_[ib].op;
+  }
+  // op -> Finish
+  void then_finish(const op_t &op) {
+    vid_t a = add_vertex(op);
+    add_edge(a, finish_);
+  }
+  // generic edge that accepts Start/Finish endpoints (used by graph builders)
+  void add_edge(const op_t &a, const op_t &b) {
+    vid_t ia = add_vertex(a), ib = add_vertex(b);
+    if (ia == finish_ || ib == start_) THROW_RUNTIME("edge out of Finish / into Start");
+    add_edge(ia, ib);
+  }
+
+  // ---- queries ----
+  size_t vertex_size() const {
+    size_t n = 0;
+    for (const auto &v : v_) n += v.alive;
+    return n;
+  }
+  size_t edge_size() const {
+    size_t n = 0;
+    for (const auto &v : v_)
+      if (v.alive) n += v.succs.size();
+    return n;
+  }
+  vid_t find_vertex(const OpBase &op) const {
+    auto it = index_.find(op.uid());
+    return it == index_.end() ? -1 : it->second;
+  }
+  // vertex whose unbound identity equals op's unbound identity
+  vid_t find_vertex_unbound(const OpBase &op) const {
+    auto it = uindex_.find(op.unbound_uid());
+    return it == uindex_.end() ? -1 : it->second;
+  }
+  bool contains(const op_t &op) const { return op && find_vertex(*op) >= 0; }
+  bool contains_unbound(const op_t &op) const { return op && find_vertex_unbound(*op) >= 0; }
+  // the graph's own pointer for an op equal to `op` (null if absent)
+  op_t find(const op_t &op) const {
+    vid_t i = find_vertex(*op);
+    return i < 0 ? nullptr : v_[i].op;
+  }
+  op_t find_unbound(const op_t &op) const {
+    vid_t i = find_vertex_unbound(*op);
+    return i < 0 ? nullptr : v_[i].op;
+  }
+  op_t find_name(const std::string &name) const {
+    for (const auto &v : v_)
+      if (v.alive && v.op->name() == name) return v.op;
+    return nullptr;
+  }
+
+  std::vector<op_t> vertices() const {
+    std::vector<op_t> r;
+    for (const auto &v : v_)
+      if (v.alive) r.push_back(v.op);
+    return r;
+  }
+  template <typename U> std::vector<std::shared_ptr<U>> nodes_cast() const {
+    std::vector<std::shared_ptr<U>> r;
+    for (const auto &v : v_)
+      if (v.alive)
+        if (auto p = std::dynamic_pointer_cast<U>(v.op)) r.push_back(p);
+    return r;
+  }
+  std::vector<op_t> start_vertices() const { return ops_of(v_[start_].succs); }
+  std::vector<op_t> finish_vertices() const { return ops_of(v_[finish_].preds); }
+
+  std::vector<op_t> succs(const op_t &op) const { return ops_of(v_[must_find(*op)].succs); }
+  std::vector<op_t> preds(const op_t &op) const { return ops_of(v_[must_find(*op)].preds); }
+  std::vector<op_t> succs_vec(const op_t &op) const { return succs(op); }
+  std::vector<op_t> preds_vec(const op_t &op) const { return preds(op); }
+  // (found, list) - `found` false when the op is not a vertex
+  std::pair<bool, std::vector<op_t>> preds_find(const op_t &op) const {
+    vid_t i = find_vertex(*op);
+    return i < 0 ? std::make_pair(false, std::vector<op_t>{})
+                 : std::make_pair(true, ops_of(v_[i].preds));
+  }
+  std::pair<bool, std::vector<op_t>> succs_find(const op_t &op) const {
+    vid_t i = find_vertex(*op);
+    return i < 0 ? std::make_pair(false, std::vector<op_t>{})
+                 : std::make_pair(true, ops_of(v_[i].succs));
+  }
+  std::pair<bool, std::vector<op_t>> preds_find_or_find_unbound(const op_t &op) const {
+    vid_t i = find_vertex_unbound(*op);
+    return i < 0 ? std::make_pair(false, std::vector<op_t>{})
+                 : std::make_pair(true, ops_of(v_[i].preds));
+  }
+  std::pair<bool, std::vector<op_t>> succs_find_or_find_unbound(const op_t &op) const {
+    vid_t i = find_vertex_unbound(*op);
+    return i < 0 ? std::make_pair(false, std::vector<op_t>{})
+                 : std::make_pair(true, ops_of(v_[i].succs));
+  }
+  std::pair<bool, std::vector<op_t>> succs_find_name(const std::string &name) const {
+    for (const auto &v : v_)
+      if (v.alive && v.op->name() == name) return {true, ops_of(v.succs)};
+    return {false, {}};
+  }
+
+  // ---- rewrites ----
+  // deep copy: every op is cloned
+  Graph clone() const {
+    Graph g(*this);
+    g.index_.clear();
+    g.uindex_.clear();
+    for (vid_t i = 0; i < static_cast<vid_t>(g.v_.size()); ++i) {
+      if (!g.v_[i].alive) continue;
+      g.v_[i].op = std::dynamic_pointer_cast<T>(v_[i].op->clone());
+      g.index_.emplace(g.v_[i].op->uid(), i);
+      g.uindex_.emplace(g.v_[i].op->unbound_uid(), i);
+    }
+    return g;
+  }
+  // in place: vertex `src` now holds `dst` (same edges)
+  void replace(const op_t &src, const op_t &dst) {
+    vid_t i = must_find(*src);
+    if (dst->uid() != src->uid() && index_.count(dst->uid()))
+      THROW_RUNTIME("replacement " << dst->desc() << " is already in the graph");
+    index_.erase(v_[i].op->uid());
+    uindex_.erase(v_[i].op->unbound_uid());
+    v_[i].op = dst;
+    index_.emplace(dst->uid(), i);
+    uindex_.emplace(dst->unbound_uid(), i);
+  }
+  // copy with `src` replaced by `dst` (ops shared, not cloned)
+  Graph clone_but_replace(const op_t &dst, const op_t &src) const {
+    Graph g(*this);
+    g.replace(src, dst);
+    return g;
+  }
+  // copy with vertex `op` replaced by the interior of `sub`:
+  //   preds(op) -> sub.start_vertices ; sub.finish_vertices -> succs(op)
+  Graph clone_but_expand(const op_t &op, const Graph &sub) const {
+    Graph g(*this);
+    const vid_t me = g.must_find(*op);
+    const std::vector<vid_t> myPreds = g.v_[me].preds, mySuccs = g.v_[me].succs;
+    g.erase_vertex(me);
+    std::vector<vid_t> map(sub.v_.size(), -1);
+    for (vid_t i = 0; i < static_cast<vid_t>(sub.v_.size()); ++i) {
+      if (!sub.v_[i].alive || i == sub.start_ || i == sub.finish_) continue;
+      if (g.index_.count(sub.v_[i].op->uid()))
+        THROW_RUNTIME("expanding " << op->name() << ": inner op " << sub.v_[i].op->name()
+                                   << " already exists in the outer graph");
+      map[i] = g.add_vertex(sub.v_[i].op);
+    }
+    for (vid_t i = 0; i < static_cast<vid_t>(sub.v_.size()); ++i) {
+      if (map[i] < 0) continue;
+      for (vid_t s : sub.v_[i].succs) {
+        if (s == sub.finish_) {
+          for (vid_t o : mySuccs) g.add_edge(map[i], o);
+        } else {
+          g.add_edge(map[i], map[s]);
+        }
+      }
+      for (vid_t p : sub.v_[i].preds) {
+        if (p == sub.start_)
+          for (vid_t o : myPreds) g.add_edge(o, map[i]);
+      }
+    }
+    // an empty compound (Start -> Finish) collapses to direct edges
+    for (vid_t s : sub.v_[sub.start_].succs)
+      if (s == sub.finish_)
+        for (vid_t p : myPreds)
+          for (vid_t q : mySuccs) g.add_edge(p, q);
+    return g;
+  }
+  // remove a vertex and its edges
+  void erase(const op_t &op) { erase_vertex(must_find(*op)); }
+  void erase_edge_only(const op_t &a, const op_t &b) {
+    vid_t ia = must_find(*a), ib = must_find(*b);
+    remove_one(v_[ia].succs, ib);
+    remove_one(v_[ib].preds, ia);
+  }
+
+  // ops whose predecessors are all in `done` and that are not in `done`
+  // themselves; comparison ignores stream bindings
+  template <typename U> std::vector<op_t> frontier(const std::vector<std::shared_ptr<U>> &done) const {
+    std::vector<char> isDone(v_.size(), 0);
+    for (const auto &d : done) {
+      vid_t i = find_vertex_unbound(*d);
+      if (i >= 0) isDone[i] = 1;
+    }
+    std::vector<op_t> r;
+    for (vid_t i = 0; i < static_cast<vid_t>(v_.size()); ++i) {
+      if (!v_[i].alive || isDone[i]) continue;
+      bool ready = true;
+      for (vid_t p : v_[i].preds) {
+        if (!isDone[p]) {
+          ready = false;
+          break;
+        }
+      }
+      if (ready) r.push_back(v_[i].op);
+    }
+    return r;
+  }
+
+  // ---- output ----
+  std::string str() const {
+    std::ostringstream ss;
+    for (const auto &v : v_) {
+      if (!v.alive) continue;
+      ss << v.op->desc() << " ->";
+      for (vid_t s : v.succs) ss << " " << v_[s].op->desc();
+      ss << "\n";
+    }
+    return ss.str();
+  }
+  void dump() const { std::cerr << str(); }
+  std::string graphviz() const {
+    std::ostringstream ss;
+    ss << "digraph D {\n";
+    for (vid_t i = 0; i < static_cast<vid_t>(v_.size()); ++i) {
+      if (!v_[i].alive) continue;
+      ss << "  op_" << i << " [label=\"" << v_[i].op->name();
+      if (auto hs = std::dynamic_pointer_cast<HasStream>(v_[i].op)) {
+        ss << "\\nstream";
+        for (const Stream &s : hs->get_streams()) ss << " " << s.str();
+      }
+      if (auto he = std::dynamic_pointer_cast<HasEvent>(v_[i].op)) {
+        ss << "\\nevent";
+        for (const Event &e : he->get_events()) ss << " " << e.str();
+      }
+      ss << "\"];\n";
+    }
+    for (vid_t i = 0; i < static_cast<vid_t>(v_.size()); ++i) {
+      if (!v_[i].alive) continue;
+      for (vid_t s : v_[i].succs) ss << "  op_" << i << " -> op_" << s << ";\n";
+    }
+    ss << "}\n";
+    return ss.str();
+  }
+  void dump_graphviz(const std::string &path) const {
+    std::ofstream os(path);
+    if (!os) THROW_RUNTIME("cannot open " << path);
+    os << graphviz();
+  }
+
+private:
+  void erase_vertex(vid_t i) {
+    if (i == start_ || i == finish_) THROW_RUNTIME("cannot erase Start/Finish");
+    for (vid_t p : v_[i].preds) remove_one(v_[p].succs, i);
+    for (vid_t s : v_[i].succs) remove_one(v_[s].preds, i);
+    v_[i].preds.clear();
+    v_[i].succs.clear();
+    v_[i].alive = false;
+    index_.erase(v_[i].op->uid());
+    uindex_.erase(v_[i].op->unbound_uid());
+  }
+};
+
+// ---- stream-assignment enumerators and equivalence (src/core/graph.cpp) ----
+// reference: src/graph.cpp:42-90,94-121,155-234,236-346,348-420
+
+// every assignment of the graph's GpuOps to `streams` (S^k graphs)
+std::vector<Graph<OpBase>> use_streams(const Graph<OpBase> &g, const std::vector<Stream> &streams);
+// canonical assignments only: the i-th GpuOp (in vertex order) may use streams
+// 0..min(i, S-1) and may open at most one new stream, which removes
+// assignments that differ only by renaming streams
+std::vector<Graph<OpBase>> use_streams2(const Graph<OpBase> &g, const std::vector<Stream> &streams);
+// bind GpuOps by name -> stream
+Graph<OpBase> apply_assignment(const Graph<OpBase> &g,
+                               const std::vector<std::pair<std::string, Stream>> &assignment);
+bool is_equivalent_stream_mapping(const Graph<OpBase> &a, const Graph<OpBase> &b);
+// same vertices (by name), same edges, streams/events consistent under one bijection
+Equivalence get_equivalence(const Graph<OpBase> &a, const Graph<OpBase> &b);
+// make every cross-stream / gpu->cpu edge explicit by inserting CER/CSWE/CES
+// vertices (the reference declares this and never defines it)
+Graph<OpBase> insert_synchronization(const Graph<OpBase> &g);
+
+} // namespace tenzing

@@ -1,0 +1,186 @@
+// Operation hierarchy of the sequential-decision-process model.
+//
+// Reference: include/tenzing/operation.hpp:35-173, operation_compound.hpp:8-12.
+// Same public surface (OpBase{name,desc,json,clone,eq,lt,tag}, BoundOp::run,
+// CpuOp, ChoiceOp::choices, CompoundOp::graph, Start, Finish, NoOp), different
+// mechanics:
+//  * identity is by value through one string `key()` ("<kind>:<name>", plus
+//    stream/event fields where they matter).  Keys are interned to a 32-bit
+//    `uid()` so graphs and states index ops with integers instead of walking
+//    std::map<shared_ptr, ...> with dynamic_casts on every comparison;
+//  * ops are treated as immutable once they are in a graph, so graph rewrites
+//    share them instead of deep-cloning (the reference clones every op - and
+//    a cuSPARSE handle per SpMV op - on every decision);
+//  * `kind()` is a stable string (also written to JSON for sync ops), `tag()`
+//    is its hash.
+// As in the reference, two ops with the same key ARE the same op: give every
+// op of a program a unique name.
+#pragma once
+
+#include <cstdint>
+#include <functional>
+#include <memory>
+#include <set>
+#include <string>
+#include <vector>
+
+#include "tenzing/json.hpp"
+#include "tenzing/macro_at.hpp"
+#include "tenzing/platform.hpp"
+
+namespace tenzing {
+
+class OpBase;
+using OpPtr = std::shared_ptr<OpBase>;
+
+// process-wide key interning
+uint32_t intern_key(const std::string &key);
+const std::string &interned_key(uint32_t uid);
+
+#define CLONE_DEF(TYPE)                                                                            \
+  std::shared_ptr<::tenzing::OpBase> clone() const override {                                      \
+    return std::make_shared<TYPE>(*this);                                                          \
+  }
+// Kept for source compatibility with ops written against the reference: eq/lt
+// are derived from key() here, so these expand to nothing.
+#define EQ_DEF(TYPE)
+#define LT_DEF(TYPE)
+
+class OpBase {
+  mutable uint32_t uid_ = 0; // 0 = not interned yet
+  mutable uint32_t unboundUid_ = 0;
+
+public:
+  OpBase() = default;
+  // copies must re-intern (a derived copy-constructor may change key fields)
+  OpBase(const OpBase &) : uid_(0), unboundUid_(0) {}
+  OpBase &operator=(const OpBase &) {
+    uid_ = unboundUid_ = 0;
+    return *this;
+  }
+  virtual ~OpBase() = default;
+
+  virtual std::string name() const = 0;
+  virtual std::string desc() const { return name(); }
+  virtual std::string kind() const { return "Op"; }
+  virtual Json json() const; // {"name": name()}
+  virtual std::shared_ptr<OpBase> clone() const = 0;
+
+  // value identity
+  virtual std::string key() const { return kind() + ":" + name(); }
+  // identity with any stream binding removed (BoundGpuOp -> the GpuOp's key)
+  virtual std::string unbound_key() const { return key(); }
+
+  uint32_t uid() const {
+    if (!uid_) uid_ = intern_key(key());
+    return uid_;
+  }
+  uint32_t unbound_uid() const {
+    if (!unboundUid_) unboundUid_ = intern_key(unbound_key());
+    return unboundUid_;
+  }
+  bool eq(const OpBase &rhs) const { return uid() == rhs.uid(); }
+  bool eq(const std::shared_ptr<const OpBase> &rhs) const { return rhs && uid() == rhs->uid(); }
+  bool lt(const OpBase &rhs) const { return key() < rhs.key(); }
+  bool lt(const std::shared_ptr<const OpBase> &rhs) const { return key() < rhs->key(); }
+  int tag() const { return static_cast<int>(std::hash<std::string>{}(kind())); }
+
+  struct compare_lt {
+    bool operator()(const std::shared_ptr<const OpBase> &a,
+                    const std::shared_ptr<const OpBase> &b) const {
+      return a->lt(*b);
+    }
+  };
+
+protected:
+  // call after changing a field that key() depends on
+  void invalidate_identity() { uid_ = unboundUid_ = 0; }
+};
+
+// not executable: several implementation alternatives for one logical operation
+class ChoiceOp : public OpBase {
+public:
+  std::string kind() const override { return "ChoiceOp"; }
+  virtual std::vector<OpPtr> choices() const = 0;
+};
+
+// executable on the platform as is
+class BoundOp : public OpBase {
+public:
+  virtual void run(Platform &plat) = 0;
+};
+using BoundOpPtr = std::shared_ptr<BoundOp>;
+
+// executes on the host thread
+class CpuOp : public BoundOp {
+public:
+  std::string kind() const override { return "CpuOp"; }
+};
+
+class Start final : public CpuOp {
+public:
+  std::string name() const override { return "Start"; }
+  std::string kind() const override { return "Start"; }
+  std::string key() const override { return "Start"; }
+  CLONE_DEF(Start)
+  void run(Platform &) override {}
+};
+
+class Finish final : public CpuOp {
+public:
+  std::string name() const override { return "Finish"; }
+  std::string kind() const override { return "Finish"; }
+  std::string key() const override { return "Finish"; }
+  CLONE_DEF(Finish)
+  void run(Platform &) override {}
+};
+
+// does nothing; identity is its name
+class NoOp : public CpuOp {
+  std::string name_;
+
+public:
+  explicit NoOp(const std::string &name) : name_(name) {}
+  std::string name() const override { return name_; }
+  std::string kind() const override { return "NoOp"; }
+  Json json() const override;
+  CLONE_DEF(NoOp)
+  void run(Platform &) override {}
+};
+
+// host op from a callable - handy for tests, toy cost models and Python ops
+class LambdaCpuOp : public CpuOp {
+  std::string name_;
+  std::function<void(Platform &)> fn_;
+
+public:
+  LambdaCpuOp(const std::string &name, std::function<void(Platform &)> fn)
+      : name_(name), fn_(std::move(fn)) {}
+  std::string name() const override { return name_; }
+  CLONE_DEF(LambdaCpuOp)
+  void run(Platform &plat) override {
+    if (fn_) fn_(plat);
+  }
+};
+
+template <typename T> class Graph;
+
+// an op that stands for a sub-graph the solver may expand in place
+class CompoundOp : public OpBase {
+public:
+  std::string kind() const override { return "CompoundOp"; }
+  virtual Graph<OpBase> graph() const = 0;
+};
+
+// ---- helpers (reference: src/operation.cpp:25-84) ----
+
+// drop later duplicates (by eq)
+void keep_uniques(std::vector<BoundOpPtr> &v);
+// the ways `op` can be placed on the platform: a GpuOp becomes one BoundGpuOp
+// per stream, a BoundOp is returned as is
+std::vector<BoundOpPtr> make_platform_variations(const Platform &plat, const OpPtr &op);
+// true iff the unbound version of e equals the unbound version of some element of v
+bool unbound_contains(const std::vector<BoundOpPtr> &v, const OpPtr &e);
+bool contains(const std::vector<OpPtr> &v, const OpPtr &e);
+
+} // namespace tenzing

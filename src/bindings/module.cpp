@@ -1,0 +1,671 @@
+// pybind11 front end: tenzing_b200._C
+//
+// The reference has no Python bindings (README roadmap, README.md:56-58); this
+// module exposes the C++ framework 1:1 - ops, graph, sequence, state, decisions,
+// synchronizer, benchmarkers, both solvers - and lets Python supply ops
+// (callables), a communicator (torch.distributed) and a benchmarker.
+#include <pybind11/functional.h>
+#include <pybind11/pybind11.h>
+#include <pybind11/stl.h>
+
+#include "tenzing/tenzing.hpp"
+
+namespace py = pybind11;
+using namespace tenzing;
+
+void bind_workloads(py::module_ &m); // bindings_workloads.cpp
+
+namespace {
+
+// ---- Python-implemented pieces ----
+class PyCpuOp : public CpuOp {
+  std::string name_;
+  py::object fn_;
+
+public:
+  PyCpuOp(const std::string &name, py::object fn) : name_(name), fn_(std::move(fn)) {}
+  ~PyCpuOp() override {
+    py::gil_scoped_acquire gil;
+    fn_ = py::object();
+  }
+  std::string name() const override { return name_; }
+  CLONE_DEF(PyCpuOp)
+  void run(Platform &) override {
+    py::gil_scoped_acquire gil;
+    if (!fn_.is_none()) fn_();
+  }
+};
+
+class PyGpuOp : public GpuOp {
+  std::string name_;
+  py::object fn_;
+
+public:
+  PyGpuOp(const std::string &name, py::object fn) : name_(name), fn_(std::move(fn)) {}
+  ~PyGpuOp() override {
+    py::gil_scoped_acquire gil;
+    fn_ = py::object();
+  }
+  std::string name() const override { return name_; }
+  CLONE_DEF(PyGpuOp)
+  void run(cudaStream_t stream) override {
+    py::gil_scoped_acquire gil;
+    if (!fn_.is_none()) fn_(reinterpret_cast<uintptr_t>(stream));
+  }
+};
+
+// forwards the control plane to a Python object (torch.distributed wrapper)
+class PyComm : public Communicator {
+  py::object obj_;
+
+public:
+  explicit PyComm(py::object obj) : obj_(std::move(obj)) {}
+  ~PyComm() override {
+    py::gil_scoped_acquire gil;
+    obj_ = py::object();
+  }
+  int rank() const override {
+    py::gil_scoped_acquire gil;
+    return obj_.attr("rank")().cast<int>();
+  }
+  int size() const override {
+    py::gil_scoped_acquire gil;
+    return obj_.attr("size")().cast<int>();
+  }
+  void barrier() override {
+    py::gil_scoped_acquire gil;
+    obj_.attr("barrier")();
+  }
+  void bcast(void *buf, size_t bytes, int root) override {
+    py::gil_scoped_acquire gil;
+    py::bytes in(static_cast<const char *>(buf), bytes);
+    std::string out = obj_.attr("bcast_bytes")(in, root).cast<std::string>();
+    if (out.size() != bytes) THROW_RUNTIME("PyComm.bcast_bytes returned the wrong length");
+    std::memcpy(buf, out.data(), bytes);
+  }
+  void allreduce_max(double *vals, size_t n) override {
+    py::gil_scoped_acquire gil;
+    std::vector<double> v(vals, vals + n);
+    std::vector<double> out = obj_.attr("allreduce_max")(v).cast<std::vector<double>>();
+    if (out.size() != n) THROW_RUNTIME("PyComm.allreduce_max returned the wrong length");
+    std::copy(out.begin(), out.end(), vals);
+  }
+  void allgather(const void *in, void *out, size_t bytesPerRank) override {
+    py::gil_scoped_acquire gil;
+    py::bytes b(static_cast<const char *>(in), bytesPerRank);
+    std::vector<std::string> parts = obj_.attr("allgather_bytes")(b).cast<std::vector<std::string>>();
+    for (size_t r = 0; r < parts.size(); ++r) {
+      if (parts[r].size() != bytesPerRank) THROW_RUNTIME("PyComm.allgather_bytes: bad part size");
+      std::memcpy(static_cast<char *>(out) + r * bytesPerRank, parts[r].data(), bytesPerRank);
+    }
+  }
+  std::string kind() const override { return "python"; }
+};
+
+class PyBenchmarker : public Benchmarker {
+  py::object fn_;
+
+public:
+  explicit PyBenchmarker(py::object fn) : fn_(std::move(fn)) {}
+  ~PyBenchmarker() override {
+    py::gil_scoped_acquire gil;
+    fn_ = py::object();
+  }
+  Benchmark::Result benchmark(Sequence<BoundOp> &order, Platform &, const Benchmark::Opts &) override {
+    py::gil_scoped_acquire gil;
+    py::object r = fn_(order);
+    if (py::isinstance<Benchmark::Result>(r)) return r.cast<Benchmark::Result>();
+    const double t = r.cast<double>();
+    Benchmark::Result res;
+    res.pct01 = res.pct10 = res.pct50 = res.pct90 = res.pct99 = t;
+    return res;
+  }
+};
+
+std::vector<int> op_streams(const OpBase &op) {
+  std::vector<int> r;
+  if (const auto *hs = dynamic_cast<const HasStream *>(&op))
+    for (const Stream &s : hs->get_streams()) r.push_back(s.id());
+  return r;
+}
+std::vector<int> op_events(const OpBase &op) {
+  std::vector<int> r;
+  if (const auto *he = dynamic_cast<const HasEvent *>(&op))
+    for (const Event &e : he->get_events()) r.push_back(e.id());
+  return r;
+}
+
+using G = Graph<OpBase>;
+using Seq = Sequence<BoundOp>;
+
+} // namespace
+
+PYBIND11_MODULE(_C, m) {
+  m.doc() = "tenzing-b200 native core";
+  m.attr("__version__") = reproduce::version_string();
+
+  // ---- L0 ----
+  m.def("init", [] { tenzing::init(); });
+  m.def("version_string", &reproduce::version_string);
+  m.def("reproduce_header", &reproduce::header_json);
+  m.def("set_verbosity", &log::set_verbosity);
+  m.def("set_log_rank", &log::set_rank);
+  m.def("avg", [](const std::vector<double> &v) { return avg(v); });
+  m.def("med", [](const std::vector<double> &v) { return med(v); });
+  m.def("var", [](const std::vector<double> &v) { return var(v); });
+  m.def("stddev", [](const std::vector<double> &v) { return stddev(v); });
+  m.def("corr", [](const std::vector<double> &a, const std::vector<double> &b) { return corr(a, b); });
+  m.def("prime_factors", [](long n) { return prime_factors<long>(n); });
+  m.def("round_up", [](long x, long s) { return round_up<long>(x, s); });
+  m.def("runs_test", &randomness::runs_test);
+  m.def("runs_test_z", &randomness::runs_test_z);
+  m.def("compound_test", &randomness::compound_test);
+  m.def("bind_to_local_memory", &numa::bind_to_local_memory);
+  m.def("numa_node_of_pci_device", &numa::node_of_pci_device);
+  m.def("numa_cpus_of_node", &numa::cpus_of_node);
+  m.def("counters", [] {
+    py::dict d;
+    const auto &mc = counters::mcts();
+    d["mcts.SELECT_TIME"] = double(mc.SELECT_TIME);
+    d["mcts.EXPAND_TIME"] = double(mc.EXPAND_TIME);
+    d["mcts.ROLLOUT_TIME"] = double(mc.ROLLOUT_TIME);
+    d["mcts.REDUNDANT_SYNC_TIME"] = double(mc.REDUNDANT_SYNC_TIME);
+    d["mcts.RMAP_TIME"] = double(mc.RMAP_TIME);
+    d["mcts.BENCHMARK_TIME"] = double(mc.BENCHMARK_TIME);
+    d["mcts.BACKPROP_TIME"] = double(mc.BACKPROP_TIME);
+    d["mcts.ITERS"] = uint64_t(mc.ITERS);
+    const auto &dc = counters::dfs();
+    d["dfs.ENUMERATE_TIME"] = double(dc.ENUMERATE_TIME);
+    d["dfs.BENCHMARK_TIME"] = double(dc.BENCHMARK_TIME);
+    d["dfs.STATES_VISITED"] = uint64_t(dc.STATES_VISITED);
+    d["dfs.STATES_PRUNED"] = uint64_t(dc.STATES_PRUNED);
+    return d;
+  });
+  m.def("reset_counters", &counters::reset);
+
+  py::class_<Equivalence>(m, "Equivalence")
+      .def("__bool__", [](const Equivalence &e) { return bool(e); })
+      .def("__str__", &Equivalence::str)
+      .def("stream_map",
+           [](const Equivalence &e) {
+             std::map<int, int> r;
+             for (const auto &kv : e.streams().forward()) r[kv.first.id()] = kv.second.id();
+             return r;
+           })
+      .def("event_map", [](const Equivalence &e) {
+        std::map<int, int> r;
+        for (const auto &kv : e.events().forward()) r[kv.first.id()] = kv.second.id();
+        return r;
+      });
+
+  // ---- communicators ----
+  py::class_<Communicator, std::shared_ptr<Communicator>>(m, "Communicator")
+      .def("rank", &Communicator::rank)
+      .def("size", &Communicator::size)
+      .def("kind", &Communicator::kind)
+      .def("barrier", &Communicator::barrier, py::call_guard<py::gil_scoped_release>())
+      .def("bcast_string", &Communicator::bcast_string, py::call_guard<py::gil_scoped_release>())
+      .def("bcast_bytes",
+           [](Communicator &c, py::bytes b, int root) {
+             std::string s = b;
+             {
+               py::gil_scoped_release rel;
+               s = c.bcast_string(s, root);
+             }
+             return py::bytes(s);
+           })
+      .def("max_over_ranks", &Communicator::max_over_ranks, py::call_guard<py::gil_scoped_release>())
+      .def("allgather_bytes", [](Communicator &c, py::bytes b) {
+        std::string s = b;
+        std::vector<std::string> parts;
+        {
+          py::gil_scoped_release rel;
+          parts = c.allgather_string(s);
+        }
+        std::vector<py::bytes> out;
+        for (auto &p : parts) out.emplace_back(p);
+        return out;
+      });
+  py::class_<SelfComm, Communicator, std::shared_ptr<SelfComm>>(m, "SelfComm").def(py::init<>());
+  py::class_<SocketComm, Communicator, std::shared_ptr<SocketComm>>(m, "SocketComm")
+      .def(py::init<int, int, const std::string &, int, double>(), py::arg("rank"), py::arg("size"),
+           py::arg("addr") = "127.0.0.1", py::arg("port") = 29517, py::arg("timeout") = 120.0,
+           py::call_guard<py::gil_scoped_release>())
+      .def_static("from_env", &SocketComm::from_env, py::arg("port_offset") = 17);
+  py::class_<PyComm, Communicator, std::shared_ptr<PyComm>>(m, "PyComm").def(py::init<py::object>());
+  // run fn(rank, comm) on `size` threads sharing a LoopbackWorld
+  m.def("loopback_run", [](int size, py::function fn) {
+    py::gil_scoped_release rel;
+    LoopbackWorld::run(size, [&](int rank, std::shared_ptr<Communicator> comm) {
+      py::gil_scoped_acquire gil;
+      fn(rank, comm);
+    });
+  });
+
+  // ---- platform ----
+  py::class_<Platform>(m, "Platform")
+      .def_static(
+          "make_n_streams",
+          [](int n, std::shared_ptr<Communicator> comm, bool null) {
+            return new Platform(Platform::make_n_streams(
+                n, std::move(comm), null ? Platform::Device::Null : Platform::Device::Cuda));
+          },
+          py::arg("n"), py::arg("comm") = nullptr, py::arg("null") = false,
+          py::return_value_policy::take_ownership)
+      .def_static(
+          "make_null",
+          [](int n, std::shared_ptr<Communicator> comm) {
+            return new Platform(Platform::make_null(n, std::move(comm)));
+          },
+          py::arg("n"), py::arg("comm") = nullptr, py::return_value_policy::take_ownership)
+      .def("is_null", &Platform::is_null)
+      .def("num_streams", &Platform::num_streams)
+      .def("new_stream", [](Platform &p) { return p.new_stream().id(); })
+      .def("adopt_stream",
+           [](Platform &p, uintptr_t s) { return p.adopt_stream(reinterpret_cast<cudaStream_t>(s)).id(); })
+      .def("ensure_streams", &Platform::ensure_streams)
+      .def("cuda_stream",
+           [](const Platform &p, int s) { return reinterpret_cast<uintptr_t>(p.cuda_stream(Stream(s))); })
+      .def("streams",
+           [](const Platform &p) {
+             std::vector<int> r;
+             for (const Stream &s : p.streams_) r.push_back(s.id());
+             return r;
+           })
+      .def("provision_events", &Platform::provision_events)
+      .def("comm", &Platform::comm_ptr)
+      .def("epoch", &Platform::epoch)
+      .def("next_epoch", &Platform::next_epoch)
+      .def("synchronize", &Platform::synchronize, py::call_guard<py::gil_scoped_release>());
+
+  // ---- ops ----
+  py::class_<OpBase, std::shared_ptr<OpBase>>(m, "OpBase")
+      .def("name", &OpBase::name)
+      .def("desc", &OpBase::desc)
+      .def("kind", &OpBase::kind)
+      .def("key", &OpBase::key)
+      .def("unbound_key", &OpBase::unbound_key)
+      .def("uid", &OpBase::uid)
+      .def("json", [](const OpBase &o) { return o.json().dump(); })
+      .def("clone", &OpBase::clone)
+      .def("eq", [](const OpBase &a, const OpBase &b) { return a.eq(b); })
+      .def("lt", [](const OpBase &a, const OpBase &b) { return a.lt(b); })
+      .def("tag", &OpBase::tag)
+      .def("streams", &op_streams)
+      .def("events", &op_events)
+      .def("__eq__", [](const OpBase &a, const OpBase &b) { return a.eq(b); })
+      .def("__hash__", [](const OpBase &a) { return a.uid(); })
+      .def("__repr__", [](const OpBase &a) { return "<" + a.kind() + " " + a.desc() + ">"; });
+  py::class_<BoundOp, OpBase, std::shared_ptr<BoundOp>>(m, "BoundOp")
+      .def("run", &BoundOp::run, py::call_guard<py::gil_scoped_release>());
+  py::class_<CpuOp, BoundOp, std::shared_ptr<CpuOp>>(m, "CpuOp");
+  py::class_<Start, CpuOp, std::shared_ptr<Start>>(m, "Start").def(py::init<>());
+  py::class_<Finish, CpuOp, std::shared_ptr<Finish>>(m, "Finish").def(py::init<>());
+  py::class_<NoOp, CpuOp, std::shared_ptr<NoOp>>(m, "NoOp").def(py::init<const std::string &>());
+  py::class_<PyCpuOp, CpuOp, std::shared_ptr<PyCpuOp>>(m, "PyCpuOp")
+      .def(py::init<const std::string &, py::object>(), py::arg("name"), py::arg("fn") = py::none());
+  py::class_<GpuOp, OpBase, std::shared_ptr<GpuOp>>(m, "GpuOp");
+  py::class_<PyGpuOp, GpuOp, std::shared_ptr<PyGpuOp>>(m, "PyGpuOp")
+      .def(py::init<const std::string &, py::object>(), py::arg("name"), py::arg("fn") = py::none());
+  py::class_<LambdaGpuOp, GpuOp, std::shared_ptr<LambdaGpuOp>>(m, "EmptyGpuOp")
+      .def(py::init([](const std::string &n) { return std::make_shared<LambdaGpuOp>(n); }));
+  py::class_<BoundGpuOp, BoundOp, std::shared_ptr<BoundGpuOp>>(m, "BoundGpuOp")
+      .def(py::init([](const GpuOpPtr &op, int s) { return std::make_shared<BoundGpuOp>(op, Stream(s)); }))
+      .def("stream", [](const BoundGpuOp &b) { return b.stream().id(); })
+      .def("unbound", &BoundGpuOp::unbound);
+  py::class_<ChoiceOp, OpBase, std::shared_ptr<ChoiceOp>>(m, "ChoiceOpBase")
+      .def("choices", &ChoiceOp::choices);
+  py::class_<ListChoiceOp, ChoiceOp, std::shared_ptr<ListChoiceOp>>(m, "ChoiceOp")
+      .def(py::init<const std::string &, const std::vector<OpPtr> &>());
+  py::class_<CompoundOp, OpBase, std::shared_ptr<CompoundOp>>(m, "CompoundOpBase")
+      .def("graph", &CompoundOp::graph);
+  py::class_<GraphCompoundOp, CompoundOp, std::shared_ptr<GraphCompoundOp>>(m, "CompoundOp")
+      .def(py::init<const std::string &, const G &>());
+
+  py::class_<CudaEventRecord, BoundOp, std::shared_ptr<CudaEventRecord>>(m, "CudaEventRecord")
+      .def(py::init([](int e, int s, const std::string &n) {
+             return std::make_shared<CudaEventRecord>(Event(e), Stream(s), n);
+           }),
+           py::arg("event"), py::arg("stream"), py::arg("name") = "CER-anon")
+      .def("event", [](const CudaEventRecord &o) { return o.event().id(); })
+      .def("stream", [](const CudaEventRecord &o) { return o.stream().id(); });
+  py::class_<CudaStreamWaitEvent, BoundOp, std::shared_ptr<CudaStreamWaitEvent>>(m, "CudaStreamWaitEvent")
+      .def(py::init([](int s, int e, const std::string &n) {
+             return std::make_shared<CudaStreamWaitEvent>(Stream(s), Event(e), n);
+           }),
+           py::arg("stream"), py::arg("event"), py::arg("name") = "CSWE-anon")
+      .def("event", [](const CudaStreamWaitEvent &o) { return o.event().id(); })
+      .def("stream", [](const CudaStreamWaitEvent &o) { return o.stream().id(); });
+  py::class_<CudaEventSync, BoundOp, std::shared_ptr<CudaEventSync>>(m, "CudaEventSync")
+      .def(py::init([](int e, const std::string &n) {
+             return std::make_shared<CudaEventSync>(Event(e), n);
+           }),
+           py::arg("event"), py::arg("name") = "CES-anon")
+      .def("event", [](const CudaEventSync &o) { return o.event().id(); });
+  py::class_<StreamWait, BoundOp, std::shared_ptr<StreamWait>>(m, "StreamWait")
+      .def(py::init([](int waitee, int waiter, int e) {
+        return std::make_shared<StreamWait>(Stream(waitee), Stream(waiter), Event(e));
+      }));
+  py::class_<StreamSync, BoundOp, std::shared_ptr<StreamSync>>(m, "StreamSync")
+      .def(py::init([](int s) { return std::make_shared<StreamSync>(Stream(s)); }))
+      .def("stream", [](const StreamSync &o) { return o.stream().id(); });
+
+  m.def("keep_uniques", [](std::vector<BoundOpPtr> v) {
+    keep_uniques(v);
+    return v;
+  });
+  m.def("make_platform_variations", &make_platform_variations);
+  m.def("unbound_contains", &unbound_contains);
+  m.def("contains", &contains);
+
+  // ---- graph ----
+  py::class_<G>(m, "Graph")
+      .def(py::init<>())
+      .def(py::init<const G &>())
+      .def("start", &G::start)
+      .def("finish", &G::finish)
+      .def("start_then", [](G &g, const OpPtr &op) { return g.start_then(op); })
+      .def("then", [](G &g, const OpPtr &a, const OpPtr &b) { return g.then(a, b); })
+      .def("then_finish", &G::then_finish)
+      .def("add_edge", [](G &g, const OpPtr &a, const OpPtr &b) { g.add_edge(a, b); })
+      .def("vertex_size", &G::vertex_size)
+      .def("edge_size", &G::edge_size)
+      .def("contains", &G::contains)
+      .def("contains_unbound", &G::contains_unbound)
+      .def("find", &G::find)
+      .def("find_unbound", &G::find_unbound)
+      .def("find_name", &G::find_name)
+      .def("vertices", &G::vertices)
+      .def("start_vertices", &G::start_vertices)
+      .def("finish_vertices", &G::finish_vertices)
+      .def("succs", &G::succs)
+      .def("preds", &G::preds)
+      .def("clone", &G::clone)
+      .def("replace", &G::replace)
+      .def("clone_but_replace", &G::clone_but_replace, py::arg("dst"), py::arg("src"))
+      .def("clone_but_expand", &G::clone_but_expand)
+      .def("erase", &G::erase)
+      .def("erase_edge_only", &G::erase_edge_only)
+      .def("frontier", [](const G &g, const std::vector<OpPtr> &done) { return g.frontier(done); })
+      .def("frontier", [](const G &g, const Seq &done) { return g.frontier(done.vector()); })
+      .def("graphviz", &G::graphviz)
+      .def("dump_graphviz", &G::dump_graphviz)
+      .def("__str__", &G::str);
+  m.def("use_streams", [](const G &g, const std::vector<int> &s) {
+    std::vector<Stream> v;
+    for (int i : s) v.emplace_back(i);
+    return use_streams(g, v);
+  });
+  m.def("use_streams2", [](const G &g, const std::vector<int> &s) {
+    std::vector<Stream> v;
+    for (int i : s) v.emplace_back(i);
+    return use_streams2(g, v);
+  });
+  m.def("apply_assignment", [](const G &g, const std::vector<std::pair<std::string, int>> &a) {
+    std::vector<std::pair<std::string, Stream>> v;
+    for (const auto &kv : a) v.emplace_back(kv.first, Stream(kv.second));
+    return apply_assignment(g, v);
+  });
+  m.def("is_equivalent_stream_mapping", &is_equivalent_stream_mapping);
+  m.def("insert_synchronization", &insert_synchronization);
+  m.def("graph_equivalence", [](const G &a, const G &b) { return get_equivalence(a, b); });
+
+  // ---- sequence ----
+  py::class_<Seq>(m, "Sequence")
+      .def(py::init<>())
+      .def(py::init([](const std::vector<BoundOpPtr> &v) { return Seq(v); }))
+      .def("__len__", &Seq::size)
+      .def("__getitem__",
+           [](const Seq &s, long i) {
+             if (i < 0) i += long(s.size());
+             if (i < 0 || size_t(i) >= s.size()) throw py::index_error();
+             return s[size_t(i)];
+           })
+      .def("__iter__", [](const Seq &s) { return py::make_iterator(s.begin(), s.end()); },
+           py::keep_alive<0, 1>())
+      .def("push_back", [](Seq &s, const BoundOpPtr &op) { s.push_back(op); })
+      .def("ops", [](const Seq &s) { return s.vector(); })
+      .def("names",
+           [](const Seq &s) {
+             std::vector<std::string> r;
+             for (const auto &o : s) r.push_back(o->name());
+             return r;
+           })
+      .def("contains", [](const Seq &s, const OpBase &o) { return s.contains(o); })
+      .def("contains_unbound", [](const Seq &s, const OpBase &o) { return s.contains_unbound(o); })
+      .def("new_unique_event", [](const Seq &s) { return s.new_unique_event().id(); })
+      .def("desc", &Seq::desc, py::arg("delim") = ", ")
+      .def("canonical_key", [](const Seq &s) { return canonical_key(s); })
+      .def("to_json", [](const Seq &s, const G &g) { return to_json(s, g).dump(); })
+      .def("run", [](Seq &s, Platform &p) { run_sequence(s, p); },
+           py::call_guard<py::gil_scoped_release>())
+      .def("__repr__", [](const Seq &s) { return "<Sequence " + s.desc() + ">"; });
+  m.def("sequence_from_json", [](const std::string &text, const G &g) {
+    Seq s;
+    from_json(Json::parse(text), g, s);
+    return s;
+  });
+  m.def("op_from_json", [](const std::string &text, const G &g) {
+    BoundOpPtr op;
+    from_json(Json::parse(text), g, op);
+    return op;
+  });
+  m.def("sequence_equivalence", [](const Seq &a, const Seq &b) { return get_equivalence(a, b); });
+  m.def("bcast_sequence",
+        [](const Seq &s, const G &g, Communicator &c, int root) { return bcast(s, g, c, root); },
+        py::arg("seq"), py::arg("graph"), py::arg("comm"), py::arg("root") = 0,
+        py::call_guard<py::gil_scoped_release>());
+  m.def("csv_row", &csv_row);
+
+  // ---- decisions / state / synchronizer ----
+  py::class_<Decision, DecisionPtr>(m, "Decision")
+      .def("desc", &Decision::desc)
+      .def("kind",
+           [](const Decision &d) {
+             switch (d.kind()) {
+             case Decision::Kind::ExecuteOp: return "ExecuteOp";
+             case Decision::Kind::ExpandOp: return "ExpandOp";
+             case Decision::Kind::ChooseOp: return "ChooseOp";
+             case Decision::Kind::AssignOpStream: return "AssignOpStream";
+             }
+             return "?";
+           })
+      .def("__repr__", [](const Decision &d) { return "<Decision " + d.desc() + ">"; });
+  py::class_<ExecuteOp, Decision, std::shared_ptr<ExecuteOp>>(m, "ExecuteOp")
+      .def(py::init<const BoundOpPtr &>())
+      .def_readonly("op", &ExecuteOp::op);
+  py::class_<ExpandOp, Decision, std::shared_ptr<ExpandOp>>(m, "ExpandOp")
+      .def(py::init<const std::shared_ptr<CompoundOp> &>())
+      .def_readonly("op", &ExpandOp::op);
+  py::class_<ChooseOp, Decision, std::shared_ptr<ChooseOp>>(m, "ChooseOp")
+      .def(py::init<const std::shared_ptr<ChoiceOp> &, const OpPtr &>())
+      .def_readonly("orig", &ChooseOp::orig)
+      .def_readonly("replacement", &ChooseOp::replacement);
+  py::class_<AssignOpStream, Decision, std::shared_ptr<AssignOpStream>>(m, "AssignOpStream")
+      .def(py::init([](const GpuOpPtr &op, int s) { return std::make_shared<AssignOpStream>(op, Stream(s)); }))
+      .def_readonly("op", &AssignOpStream::op)
+      .def_property_readonly("stream", [](const AssignOpStream &a) { return a.stream.id(); });
+
+  py::class_<SDP::State>(m, "State")
+      .def(py::init<const G &>())
+      .def(py::init<const G &, const Seq &>())
+      .def("graph", &SDP::State::graph, py::return_value_policy::copy)
+      .def("sequence", &SDP::State::sequence, py::return_value_policy::copy)
+      .def("get_syncs_before_op", &SDP::State::get_syncs_before_op)
+      .def("get_decisions", &SDP::State::get_decisions, py::arg("plat"), py::arg("quiet") = true)
+      .def("apply", &SDP::State::apply)
+      .def("frontier", &SDP::State::frontier, py::arg("plat"), py::arg("quiet") = true)
+      .def("is_terminal", &SDP::State::is_terminal)
+      .def("canonical_key", &SDP::State::canonical_key);
+  m.def("state_equivalence",
+        [](const SDP::State &a, const SDP::State &b) { return SDP::get_equivalence(a, b); });
+
+  py::class_<EventSynchronizer>(m, "EventSynchronizer")
+      .def_static("is_synced", &EventSynchronizer::is_synced)
+      .def_static("make_syncs", &EventSynchronizer::make_syncs, py::arg("op"), py::arg("graph"),
+                  py::arg("path"), py::arg("quiet") = true);
+
+  // ---- schedule ----
+  m.def("remove_redundant_syncs", [](Seq &s) { return Schedule::remove_redundant_syncs(s); });
+  m.def("make_schedules",
+        [](const G &g, size_t maxCount) {
+          std::vector<Seq> r;
+          for (auto &s : make_schedules(g, maxCount)) r.push_back(std::move(s.order));
+          return r;
+        },
+        py::arg("graph"), py::arg("max_count") = 0);
+  m.def("make_schedules_random",
+        [](const G &g, size_t n, uint64_t seed) {
+          std::vector<Seq> r;
+          for (auto &s : make_schedules_random(g, n, seed)) r.push_back(std::move(s.order));
+          return r;
+        },
+        py::arg("graph"), py::arg("n"), py::arg("seed") = 0);
+  m.def("count_schedules", &count_schedules);
+
+  // ---- benchmarkers ----
+  py::class_<Benchmark::Result>(m, "BenchResult")
+      .def(py::init<>())
+      .def_readwrite("pct01", &Benchmark::Result::pct01)
+      .def_readwrite("pct10", &Benchmark::Result::pct10)
+      .def_readwrite("pct50", &Benchmark::Result::pct50)
+      .def_readwrite("pct90", &Benchmark::Result::pct90)
+      .def_readwrite("pct99", &Benchmark::Result::pct99)
+      .def_readwrite("stddev", &Benchmark::Result::stddev)
+      .def_static("from_samples", &Benchmark::Result::from_samples)
+      .def("__repr__", [](const Benchmark::Result &r) {
+        std::ostringstream ss;
+        ss << "<BenchResult pct10=" << r.pct10 << " pct50=" << r.pct50 << " stddev=" << r.stddev << ">";
+        return ss.str();
+      });
+  py::class_<Benchmark::Opts>(m, "BenchOpts")
+      .def(py::init<>())
+      .def(py::init([](size_t nIters, size_t maxRetries, double targetSecs, bool check) {
+             Benchmark::Opts o;
+             o.nIters = nIters;
+             o.maxRetries = maxRetries;
+             o.targetSecs = targetSecs;
+             o.checkRandomness = check;
+             return o;
+           }),
+           py::arg("n_iters") = 1000, py::arg("max_retries") = 10, py::arg("target_secs") = 0.01,
+           py::arg("check_randomness") = true)
+      .def_readwrite("n_iters", &Benchmark::Opts::nIters)
+      .def_readwrite("max_retries", &Benchmark::Opts::maxRetries)
+      .def_readwrite("target_secs", &Benchmark::Opts::targetSecs)
+      .def_readwrite("check_randomness", &Benchmark::Opts::checkRandomness);
+  py::class_<Benchmarker>(m, "Benchmarker")
+      .def("benchmark",
+           [](Benchmarker &b, Seq &s, Platform &p, const Benchmark::Opts &o) {
+             return b.benchmark(s, p, o);
+           },
+           py::arg("seq"), py::arg("plat"), py::arg("opts") = Benchmark::Opts(),
+           py::call_guard<py::gil_scoped_release>());
+  py::class_<EmpiricalBenchmarker, Benchmarker>(m, "EmpiricalBenchmarker").def(py::init<>());
+  py::class_<DeviceBenchmarker, EmpiricalBenchmarker>(m, "DeviceBenchmarker").def(py::init<>());
+  py::class_<CsvBenchmarker, Benchmarker>(m, "CsvBenchmarker")
+      .def(py::init<const std::string &, const G &>())
+      .def_static("from_text", [](const std::string &t, const G &g) {
+        return new CsvBenchmarker(CsvBenchmarker::from_text(t, g));
+      }, py::return_value_policy::take_ownership)
+      .def("num_rows", [](const CsvBenchmarker &b) { return b.rows().size(); });
+  py::class_<PyBenchmarker, Benchmarker>(m, "PyBenchmarker").def(py::init<py::object>());
+
+  // ---- DFS ----
+  py::module_ d = m.def_submodule("dfs");
+  py::class_<dfs::Opts>(d, "Opts")
+      .def(py::init<>())
+      .def_readwrite("max_seqs", &dfs::Opts::maxSeqs)
+      .def_readwrite("remove_redundant_syncs", &dfs::Opts::removeRedundantSyncs)
+      .def_readwrite("bench_opts", &dfs::Opts::benchOpts);
+  py::class_<dfs::SimResult>(d, "SimResult")
+      .def_readonly("seq", &dfs::SimResult::seq)
+      .def_readonly("bench_result", &dfs::SimResult::benchResult);
+  py::class_<dfs::Result>(d, "Result")
+      .def_readonly("sim_results", &dfs::Result::simResults)
+      .def("csv", &dfs::Result::csv)
+      .def("best", &dfs::Result::best);
+  d.def("get_all_sequences", &dfs::get_all_sequences, py::arg("graph"), py::arg("plat"),
+        py::arg("max_seqs") = -1, py::arg("remove_redundant_syncs") = false,
+        py::call_guard<py::gil_scoped_release>());
+  d.def("explore", &dfs::explore, py::arg("graph"), py::arg("plat"), py::arg("benchmarker"),
+        py::arg("opts") = dfs::Opts(), py::call_guard<py::gil_scoped_release>());
+
+  // ---- MCTS ----
+  py::module_ mc = m.def_submodule("mcts");
+  py::class_<mcts::Opts>(mc, "Opts")
+      .def(py::init<>())
+      .def_readwrite("n_iters", &mcts::Opts::nIters)
+      .def_readwrite("dump_tree", &mcts::Opts::dumpTree)
+      .def_readwrite("dump_tree_prefix", &mcts::Opts::dumpTreePrefix)
+      .def_readwrite("expand_rollout", &mcts::Opts::expandRollout)
+      .def_readwrite("seed", &mcts::Opts::seed)
+      .def_readwrite("remove_redundant_syncs", &mcts::Opts::removeRedundantSyncs)
+      .def_readwrite("bench_opts", &mcts::Opts::benchOpts);
+  py::class_<mcts::SimResult>(mc, "SimResult")
+      .def_readonly("path", &mcts::SimResult::path)
+      .def_readonly("bench_result", &mcts::SimResult::benchResult);
+  py::class_<mcts::Result>(mc, "Result")
+      .def_readonly("sim_results", &mcts::Result::simResults)
+      .def("csv", &mcts::Result::csv)
+      .def("best", &mcts::Result::best);
+  py::class_<mcts::Strategy>(mc, "Strategy").def("name", &mcts::Strategy::name);
+  mc.def("make_strategy", [](const std::string &n) { return mcts::make_strategy(n); });
+  mc.def("strategy_names", &mcts::strategy_names);
+  mc.def("histogram", &mcts::histogram, py::arg("v"), py::arg("t_min"), py::arg("t_max"),
+         py::arg("n_bins") = 10);
+  mc.def("explore",
+         [](const G &g, Platform &plat, Benchmarker &b, const std::string &strategy,
+            const mcts::Opts &opts) {
+           auto s = mcts::make_strategy(strategy);
+           return mcts::explore(g, plat, b, *s, opts);
+         },
+         py::arg("graph"), py::arg("plat"), py::arg("benchmarker"), py::arg("strategy") = "FastMin",
+         py::arg("opts") = mcts::Opts(), py::call_guard<py::gil_scoped_release>());
+  mc.def("get_frontier", &mcts::get_frontier);
+
+  // tree-level access for tests / notebooks
+  py::class_<mcts::Node>(mc, "Node")
+      .def(py::init<const G &>())
+      .def_readonly("n", &mcts::Node::n_)
+      .def_readonly("fully_visited", &mcts::Node::fullyVisited_)
+      .def_readonly("expanded", &mcts::Node::expanded_)
+      .def("op", [](const mcts::Node &n) { return n.op_; })
+      .def("parent", [](mcts::Node &n) { return n.parent_; }, py::return_value_policy::reference)
+      .def("children",
+           [](mcts::Node &n) {
+             py::list l;
+             for (auto &c : n.children_) l.append(py::cast(c.get(), py::return_value_policy::reference));
+             return l;
+           },
+           py::keep_alive<0, 1>())
+      .def("times", [](const mcts::Node &n) { return n.state_.times; })
+      .def("size", &mcts::Node::size)
+      .def("unvisited_size", &mcts::Node::unvisited_size)
+      .def("fully_visited_size", &mcts::Node::fully_visited_size)
+      .def("is_leaf", &mcts::Node::is_leaf)
+      .def("is_terminal", &mcts::Node::is_terminal)
+      .def("get_sequence", &mcts::Node::get_sequence)
+      .def("ensure_children", &mcts::Node::ensure_children)
+      .def("expand", &mcts::Node::expand, py::return_value_policy::reference)
+      .def("root", [](mcts::Node &n) -> mcts::Node & { return n.root(); },
+           py::return_value_policy::reference)
+      .def("graphviz", [](const mcts::Node &n) { return mcts::graphviz(n); })
+      .def("desc", &mcts::Node::desc);
+  // one full MCTS iteration on an explicit tree with a Python cost function
+  mc.def("iterate", [](mcts::Node &root, const Platform &plat, mcts::Strategy &strategy,
+                       py::function cost, uint64_t seed, bool expandRollout) {
+    std::mt19937_64 rng(seed);
+    mcts::Node &sel = root.select(strategy, rng);
+    mcts::Node &child = sel.expand(plat);
+    auto rr = child.get_rollout(plat, rng, expandRollout);
+    Schedule::remove_redundant_syncs(rr.sequence);
+    const double t = cost(rr.sequence).cast<double>();
+    Benchmark::Result br;
+    br.pct01 = br.pct10 = br.pct50 = br.pct90 = br.pct99 = t;
+    rr.backpropStart->backprop(strategy, br);
+    return rr.sequence;
+  });
+
+  bind_workloads(m);
+}

@@ -1,0 +1,223 @@
+#include "tenzing/benchmarker.hpp"
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <fstream>
+#include <numeric>
+#include <random>
+#include <sstream>
+
+#include "tenzing/communicator.hpp"
+#include "tenzing/cuda/cuda_runtime.hpp"
+#include "tenzing/numeric.hpp"
+#include "tenzing/operation_serdes.hpp"
+#include "tenzing/randomness.hpp"
+
+namespace tenzing {
+
+using Benchmark::Opts;
+using Benchmark::Result;
+
+namespace {
+double wall() {
+  using clk = std::chrono::steady_clock;
+  return std::chrono::duration<double>(clk::now().time_since_epoch()).count();
+}
+} // namespace
+
+Result Result::from_samples(std::vector<double> s) {
+  Result r;
+  if (s.empty()) return r;
+  std::sort(s.begin(), s.end());
+  r.pct01 = percentile_sorted(s, 1);
+  r.pct10 = percentile_sorted(s, 10);
+  r.pct50 = percentile_sorted(s, 50);
+  r.pct90 = percentile_sorted(s, 90);
+  r.pct99 = percentile_sorted(s, 99);
+  r.stddev = ::tenzing::stddev(s);
+  return r;
+}
+
+void run_sequence(Sequence<BoundOp> &order, Platform &plat) {
+  plat.next_epoch();
+  for (auto &op : order) op->run(plat);
+}
+
+// ---- host-wall benchmarker ----
+double EmpiricalBenchmarker::timed_run(Sequence<BoundOp> &order, Platform &plat, size_t nSamples) {
+  plat.comm().barrier();
+  const double t0 = wall();
+  for (size_t i = 0; i < nSamples; ++i) run_sequence(order, plat);
+  return wall() - t0;
+}
+
+EmpiricalBenchmarker::Measurement EmpiricalBenchmarker::measure(Sequence<BoundOp> &order,
+                                                                Platform &plat, size_t hint,
+                                                                double targetSecs) {
+  Measurement m{std::max<size_t>(hint, 1), 0};
+  while (true) {
+    double elapsed = plat.comm().max_over_ranks(timed_run(order, plat, m.nSamples));
+    if (elapsed >= targetSecs || m.nSamples >= (size_t(1) << 24)) {
+      m.time = elapsed / double(m.nSamples);
+      return m;
+    }
+    // step half-way towards 1.1x the estimated sample count (same rule on every rank,
+    // elapsed is already the max over ranks)
+    const double perSample = std::max(elapsed / double(m.nSamples), 1e-9);
+    const double est = 1.1 * targetSecs / perSample;
+    const double step = std::ceil((est - double(m.nSamples)) * 0.5);
+    m.nSamples += size_t(std::max(1.0, step));
+  }
+}
+
+Result EmpiricalBenchmarker::benchmark(Sequence<BoundOp> &order, Platform &plat, const Opts &opts) {
+  std::vector<double> times;
+  for (size_t attempt = 0; attempt <= opts.maxRetries; ++attempt) {
+    times.clear();
+    Measurement m = measure(order, plat, 1, opts.targetSecs); // calibrate
+    for (size_t i = 0; i < opts.nIters; ++i) {
+      m = measure(order, plat, m.nSamples, opts.targetSecs);
+      times.push_back(m.time);
+    }
+    // every rank holds the same max-reduced series, so the verdict agrees everywhere
+    if (!opts.checkRandomness || !randomness::compound_test(times)) break;
+    if (attempt < opts.maxRetries) TENZING_INFO("measurement series failed the runs test, retrying");
+  }
+  return Result::from_samples(times);
+}
+
+std::vector<Result> EmpiricalBenchmarker::benchmark(std::vector<Schedule> &schedules,
+                                                    Platform &plat, const Opts &opts) {
+  Communicator &comm = plat.comm();
+  std::vector<int> perm(schedules.size());
+  std::iota(perm.begin(), perm.end(), 0);
+  std::vector<std::vector<double>> times(schedules.size());
+  std::mt19937 rng(12345);
+  for (size_t i = 0; i < opts.nIters; ++i) {
+    if (comm.rank() == 0) std::shuffle(perm.begin(), perm.end(), rng);
+    comm.bcast(perm.data(), perm.size() * sizeof(int), 0);
+    for (int si : perm) times[si].push_back(timed_run(schedules[si].order, plat, 1));
+  }
+  std::vector<Result> out;
+  for (auto &t : times) {
+    comm.allreduce_max(t.data(), t.size());
+    out.push_back(Result::from_samples(t));
+  }
+  return out;
+}
+
+// ---- device-timed benchmarker ----
+DeviceBenchmarker::~DeviceBenchmarker() {
+  for (auto e : starts_) cudaEventDestroy(e);
+  for (auto e : stops_) cudaEventDestroy(e);
+  if (fence_) cudaEventDestroy(fence_);
+}
+
+double DeviceBenchmarker::timed_run(Sequence<BoundOp> &order, Platform &plat, size_t nSamples) {
+  if (plat.is_null()) return EmpiricalBenchmarker::timed_run(order, plat, nSamples);
+  const int ns = plat.num_streams();
+  while (int(starts_.size()) < 1) {
+    cudaEvent_t e;
+    CUDA_RUNTIME(cudaEventCreate(&e));
+    starts_.push_back(e);
+  }
+  while (int(stops_.size()) < ns + 1) {
+    cudaEvent_t e;
+    CUDA_RUNTIME(cudaEventCreate(&e));
+    stops_.push_back(e);
+  }
+  plat.synchronize();
+  plat.comm().barrier();
+  // start: recorded on stream 0, every other stream starts behind it
+  cudaStream_t s0 = plat.cuda_stream(plat.streams_[0]);
+  CUDA_RUNTIME(cudaEventRecord(starts_[0], s0));
+  for (int i = 1; i < ns; ++i)
+    CUDA_RUNTIME(cudaStreamWaitEvent(plat.cuda_stream(plat.streams_[i]), starts_[0], 0));
+  for (size_t i = 0; i < nSamples; ++i) run_sequence(order, plat);
+  // stop: stream 0 joins every stream, then records
+  for (int i = 1; i < ns; ++i) {
+    CUDA_RUNTIME(cudaEventRecord(stops_[i], plat.cuda_stream(plat.streams_[i])));
+    CUDA_RUNTIME(cudaStreamWaitEvent(s0, stops_[i], 0));
+  }
+  CUDA_RUNTIME(cudaEventRecord(stops_[ns], s0));
+  CUDA_RUNTIME(cudaEventSynchronize(stops_[ns]));
+  float ms = 0;
+  CUDA_RUNTIME(cudaEventElapsedTime(&ms, starts_[0], stops_[ns]));
+  return double(ms) * 1e-3;
+}
+
+// ---- CSV replay ----
+std::string csv_row(size_t idx, const Result &r, const Sequence<BoundOp> &seq) {
+  std::ostringstream ss;
+  ss << idx << "|" << r.pct01 << "|" << r.pct10 << "|" << r.pct50 << "|" << r.pct90 << "|"
+     << r.pct99 << "|" << r.stddev;
+  for (const auto &op : seq) ss << "|" << op->json().dump();
+  return ss.str();
+}
+
+void CsvBenchmarker::load(std::istream &is, const Graph<OpBase> &g) {
+  std::string line;
+  size_t lineNo = 0;
+  while (std::getline(is, line)) {
+    ++lineNo;
+    if (line.empty() || line[0] == '{' || line[0] == '#') continue; // reproduce / opts headers
+    std::vector<std::string> cols;
+    {
+      std::stringstream ss(line);
+      std::string c;
+      while (std::getline(ss, c, '|')) cols.push_back(c);
+    }
+    if (cols.size() < 8) continue;
+    DataRow row;
+    try {
+      row.res.pct01 = std::stod(cols[1]);
+      row.res.pct10 = std::stod(cols[2]);
+      row.res.pct50 = std::stod(cols[3]);
+      row.res.pct90 = std::stod(cols[4]);
+      row.res.pct99 = std::stod(cols[5]);
+      row.res.stddev = std::stod(cols[6]);
+    } catch (const std::exception &) {
+      if (data_.empty()) continue; // a textual column header
+      THROW_RUNTIME("csv line " << lineNo << ": bad statistics columns");
+    }
+    for (size_t c = 7; c < cols.size(); ++c) {
+      if (cols[c].empty()) continue; // padded rows
+      BoundOpPtr op;
+      from_json(Json::parse(cols[c]), g, op);
+      row.seq.push_back(op);
+    }
+    byKey_.emplace(canonical_key(row.seq), data_.size());
+    data_.push_back(std::move(row));
+  }
+}
+
+CsvBenchmarker::CsvBenchmarker(const std::string &path, const Graph<OpBase> &g) {
+  std::ifstream is(path);
+  if (!is) THROW_RUNTIME("cannot open " << path);
+  load(is, g);
+}
+
+CsvBenchmarker CsvBenchmarker::from_text(const std::string &text, const Graph<OpBase> &g) {
+  CsvBenchmarker b;
+  std::istringstream is(text);
+  b.load(is, g);
+  return b;
+}
+
+Result CsvBenchmarker::benchmark(Sequence<BoundOp> &order, Platform &, const Opts &) {
+  auto it = byKey_.find(canonical_key(order));
+  if (it == byKey_.end()) THROW_RUNTIME("no CSV row matches sequence: " << order.desc());
+  return data_[it->second].res;
+}
+
+// ---- cost model ----
+Result ModelBenchmarker::benchmark(Sequence<BoundOp> &order, Platform &, const Opts &) {
+  const double t = model_(order);
+  Result r;
+  r.pct01 = r.pct10 = r.pct50 = r.pct90 = r.pct99 = t;
+  r.stddev = 0;
+  return r;
+}
+
+} // namespace tenzing

@@ -1,0 +1,116 @@
+#include "tenzing/cuda/ops_cuda.hpp"
+
+namespace tenzing {
+
+Json BoundGpuOp::json() const {
+  Json j = op_->json();
+  j["stream"] = stream_.id();
+  return j;
+}
+
+void SyncOpBase::make_name(const char *prefix, const OpSet &preds, const OpSet &succs) {
+  std::string n(prefix);
+  if (!preds.empty()) {
+    n += "-after";
+    for (const auto &p : preds) n += "-" + p->name();
+  }
+  if (!succs.empty()) {
+    n += "-b4";
+    for (const auto &s : succs) n += "-" + s->name();
+  }
+  name_ = n;
+}
+
+Json CudaEventRecord::json() const {
+  Json j = Json::object();
+  j["name"] = name();
+  j["kind"] = kind();
+  j["event"] = event_.id();
+  j["stream"] = stream_.id();
+  return j;
+}
+void CudaEventRecord::run(Platform &plat) {
+  if (plat.is_null()) return;
+  CUDA_RUNTIME(cudaEventRecord(plat.cuda_event(event_), plat.cuda_stream(stream_)));
+}
+
+Json CudaStreamWaitEvent::json() const {
+  Json j = Json::object();
+  j["name"] = name();
+  j["kind"] = kind();
+  j["event"] = event_.id();
+  j["stream"] = stream_.id();
+  return j;
+}
+void CudaStreamWaitEvent::run(Platform &plat) {
+  if (plat.is_null()) return;
+  CUDA_RUNTIME(cudaStreamWaitEvent(plat.cuda_stream(stream_), plat.cuda_event(event_), 0));
+}
+
+Json CudaEventSync::json() const {
+  Json j = Json::object();
+  j["name"] = name();
+  j["kind"] = kind();
+  j["event"] = event_.id();
+  return j;
+}
+void CudaEventSync::run(Platform &plat) {
+  if (plat.is_null()) return;
+  CUDA_RUNTIME(cudaEventSynchronize(plat.cuda_event(event_)));
+}
+
+Json StreamWait::json() const {
+  Json j = Json::object();
+  j["name"] = name();
+  j["kind"] = kind();
+  j["waitee"] = waitee_.id();
+  j["waiter"] = waiter_.id();
+  j["event"] = event_.id();
+  return j;
+}
+void StreamWait::run(Platform &plat) {
+  if (plat.is_null()) return;
+  cudaEvent_t e = plat.cuda_event(event_);
+  CUDA_RUNTIME(cudaEventRecord(e, plat.cuda_stream(waitee_)));
+  CUDA_RUNTIME(cudaStreamWaitEvent(plat.cuda_stream(waiter_), e, 0));
+}
+
+Json StreamSync::json() const {
+  Json j = Json::object();
+  j["name"] = name();
+  j["kind"] = kind();
+  j["stream"] = stream_.id();
+  return j;
+}
+void StreamSync::run(Platform &plat) {
+  if (plat.is_null()) return;
+  CUDA_RUNTIME(cudaStreamSynchronize(plat.cuda_stream(stream_)));
+}
+
+BoundOpPtr sync_op_from_json(const Json &j) {
+  if (!j.contains("kind") || !j.at("kind").is_string()) return nullptr;
+  const std::string &kind = j.at("kind").as_string();
+  const std::string name = j.contains("name") ? j.at("name").as_string() : std::string();
+  auto geti = [&](const char *k) { return static_cast<int>(j.at(k).as_int()); };
+  if (kind == "CudaEventRecord") {
+    return std::make_shared<CudaEventRecord>(Event(geti("event")), Stream(geti("stream")),
+                                             name.empty() ? "CER-anon" : name);
+  } else if (kind == "CudaStreamWaitEvent") {
+    return std::make_shared<CudaStreamWaitEvent>(Stream(geti("stream")), Event(geti("event")),
+                                                 name.empty() ? "CSWE-anon" : name);
+  } else if (kind == "CudaEventSync") {
+    return std::make_shared<CudaEventSync>(Event(geti("event")), name.empty() ? "CES-anon" : name);
+  } else if (kind == "StreamWait") {
+    auto p = std::make_shared<StreamWait>(Stream(geti("waitee")), Stream(geti("waiter")),
+                                          Event(j.contains("event") ? geti("event") : 0));
+    if (!name.empty()) p->set_name(name);
+    return p;
+  } else if (kind == "StreamSync") {
+    auto p = std::make_shared<StreamSync>(Stream(geti("stream")));
+    if (!name.empty()) p->set_name(name);
+    return p;
+  }
+  return nullptr;
+}
+
+} // namespace tenzing

@@ -1,0 +1,147 @@
+// L0 odds and ends: logging state, runs test, counters, signal trap,
+// reproducibility header, init notice.
+#include <csignal>
+#include <cstdlib>
+#include <limits>
+
+#include "tenzing/counters.hpp"
+#include "tenzing/init.hpp"
+#include "tenzing/json.hpp"
+#include "tenzing/macro_at.hpp"
+#include "tenzing/numeric.hpp"
+#include "tenzing/randomness.hpp"
+#include "tenzing/reproduce.hpp"
+#include "tenzing/trap.hpp"
+#include "tenzing/version.hpp"
+
+namespace tenzing {
+
+namespace log {
+int &rank_ref() {
+  static int r = 0;
+  return r;
+}
+int &verbosity_ref() {
+  static int v = [] {
+    const char *e = std::getenv("TENZING_VERBOSE");
+    return e ? std::atoi(e) : 0;
+  }();
+  return v;
+}
+} // namespace log
+
+// ---- randomness ----
+namespace randomness {
+
+double runs_test_z(const std::vector<double> &v) {
+  const double nan = std::numeric_limits<double>::quiet_NaN();
+  if (v.size() < 2) return nan;
+  const double median = med(v);
+  size_t nHi = 0, nLo = 0, runs = 1;
+  bool prev = false;
+  for (size_t i = 0; i < v.size(); ++i) {
+    const bool hi = v[i] >= median;
+    (hi ? nHi : nLo)++;
+    if (i && hi != prev) ++runs;
+    prev = hi;
+  }
+  if (nHi < 10 || nLo < 10) return nan;
+  const double a = double(nHi), b = double(nLo);
+  const double expected = 2 * a * b / (a + b) + 1;
+  const double sd = std::sqrt(2 * a * b * (2 * a * b - a - b) / ((a + b) * (a + b) * (a + b - 1)));
+  return std::abs((double(runs) - expected) / sd);
+}
+
+bool runs_test(const std::vector<double> &v) {
+  const double z = runs_test_z(v);
+  if (std::isnan(z)) return true; // test does not apply -> reject, as the reference does
+  return z > 1.96;                // alpha = 0.05
+}
+
+bool compound_test(const std::vector<double> &v) { return runs_test(v); }
+
+} // namespace randomness
+
+// ---- counters ----
+namespace counters {
+Mcts &mcts() {
+  static Mcts m;
+  return m;
+}
+Dfs &dfs() {
+  static Dfs d;
+  return d;
+}
+void reset() {
+  mcts() = Mcts();
+  dfs() = Dfs();
+}
+} // namespace counters
+
+// ---- trap ----
+namespace {
+TrapHandler &trap_fn() {
+  static TrapHandler fn;
+  return fn;
+}
+void on_signal(int sig) {
+  TrapHandler fn = trap_fn();
+  if (fn) fn(sig);
+  std::_Exit(1);
+}
+} // namespace
+
+void register_handler(TrapHandler fn) {
+  trap_fn() = std::move(fn);
+  std::signal(SIGINT, on_signal);
+  std::signal(SIGABRT, on_signal);
+  std::signal(SIGTERM, on_signal);
+}
+void unregister_handler() {
+  trap_fn() = nullptr;
+  std::signal(SIGINT, SIG_DFL);
+  std::signal(SIGABRT, SIG_DFL);
+  std::signal(SIGTERM, SIG_DFL);
+}
+
+// ---- reproduce ----
+namespace reproduce {
+std::string version_string() {
+  return std::to_string(TENZING_VERSION_MAJOR) + "." + std::to_string(TENZING_VERSION_MINOR) +
+         "." + std::to_string(TENZING_VERSION_PATCH) + "-" + TENZING_VERSION_HASH;
+}
+std::string header_json(const std::vector<std::string> &args) {
+  Json j = Json::object();
+  Json a = Json::array();
+  for (const auto &s : args) a.push_back(s);
+  j["args"] = a;
+  j["hash"] = TENZING_VERSION_HASH;
+  j["major"] = TENZING_VERSION_MAJOR;
+  j["minor"] = TENZING_VERSION_MINOR;
+  j["patch"] = TENZING_VERSION_PATCH;
+  return j.dump();
+}
+void dump_with_cli(int argc, char **argv) {
+  std::vector<std::string> args;
+  for (int i = 0; i < argc; ++i) args.emplace_back(argv[i]);
+  std::cout << header_json(args) << std::endl;
+}
+} // namespace reproduce
+
+// ---- init ----
+bool notice_acknowledged() { return std::getenv("TENZING_ACK_NOTICE") != nullptr; }
+
+void init() {
+  static bool done = false;
+  if (done) return;
+  done = true;
+  if (!notice_acknowledged()) {
+    std::cerr << "tenzing-b200 " << reproduce::version_string()
+              << ": research software, provided as is; schedules are benchmarked on YOUR "
+                 "hardware and results depend on it. Set TENZING_ACK_NOTICE=1 to silence "
+                 "this notice.\n";
+  }
+}
+void init(int &, char **&) { init(); }
+
+} // namespace tenzing
