@@ -1,0 +1,127 @@
+/* C ABI of the tenzing-b200 kernel library (libtenzing_b200_kernels.so).
+ *
+ * Every hot op the schedule search can place is one of these sm_100a kernels.
+ * All functions return a cudaError_t value as int (0 = success), launch on the
+ * given stream and do not synchronise.  Pointers are device pointers unless
+ * stated otherwise; "peer" pointers are device pointers into another GPU's
+ * memory (CUDA IPC / peer access over NVLink) and may be used wherever a
+ * destination or flag is expected.
+ *
+ * Cross-GPU protocol: a producer kernel writes its payload, then publishes a
+ * 64-bit epoch to a flag word with release semantics at system scope; a
+ * consumer kernel spins on its own flag word with acquire semantics until the
+ * value is >= the epoch it was launched with.  Epochs only grow.
+ */
+#ifndef TENZING_B200_H
+#define TENZING_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---------------------------------------------------------------- SpMV ---- */
+/* Replaces the reference's cuSPARSE call (include/tenzing/spmv/ops_spmv.cuh:91-126)
+ * and its unused scalar kernel (ops_spmv.cuh:25-39).
+ * y = A x (accumulate == 0) or y += A x (accumulate != 0); CSR, 32-bit indices. */
+int tzb_spmv_csr_f64(int rows, const int *rowPtr, const int *colInd, const double *val,
+                     const double *x, double *y, int accumulate, void *stream);
+int tzb_spmv_csr_f32(int rows, const int *rowPtr, const int *colInd, const float *val,
+                     const float *x, float *y, int accumulate, void *stream);
+
+/* dst[i] = src[idx[i]] - the reference's `scatter` kernel, really a gather
+ * (ops_spmv.cuh:41-59). */
+int tzb_gather_f64(int n, const int *idx, const double *src, double *dst, void *stream);
+int tzb_gather_f32(int n, const int *idx, const float *src, float *dst, void *stream);
+
+/* y[i] += a[i] - the reference's VectorAdd is an empty function
+ * (src/spmv/ops_spmv.cu:45-47). */
+int tzb_vector_add_f64(int n, const double *a, double *y, void *stream);
+int tzb_vector_add_f32(int n, const float *a, float *y, void *stream);
+
+/* Gather fused with the send (replaces Scatter + PostSend,
+ * ops_spmv.cuh:167-215,217-240): entry i of the send list goes to
+ * peerDst[p][i - displ[p]] where p is the peer whose [displ[p], displ[p+1])
+ * range contains i (ranges may be empty).  After the last block finishes,
+ * flag[p] <- epoch is published (release, system scope) for every peer whose
+ * flag pointer is not NULL.
+ * `counter` is one zeroed uint32 of scratch in device memory (left zero). */
+typedef struct {
+  int nPeers;
+  int displ[17];        /* nPeers + 1 entries, displ[0] = 0 */
+  void *peerDst[16];    /* base of this rank's slot in each peer's rx buffer */
+  uint64_t *peerFlag[16];
+} TzbGatherPutArgs;
+int tzb_gather_put_f64(const TzbGatherPutArgs *args, const int *idx, const double *src,
+                       uint64_t epoch, uint32_t *counter, void *stream);
+int tzb_gather_put_f32(const TzbGatherPutArgs *args, const int *idx, const float *src,
+                       uint64_t epoch, uint32_t *counter, void *stream);
+
+/* Receive fused with the off-diagonal product (replaces WaitRecv + the remote
+ * cuSPARSE call + VectorAdd, ops_spmv.cuh:276-304): every block first waits
+ * until all nFlags local flag words are >= epoch, then y (+)= A_remote rx. */
+int tzb_spmv_csr_wait_f64(int rows, const int *rowPtr, const int *colInd, const double *val,
+                          const double *x, double *y, int accumulate, const uint64_t *flags,
+                          int nFlags, uint64_t epoch, void *stream);
+int tzb_spmv_csr_wait_f32(int rows, const int *rowPtr, const int *colInd, const float *val,
+                          const float *x, float *y, int accumulate, const uint64_t *flags,
+                          int nFlags, uint64_t epoch, void *stream);
+
+/* ----------------------------------------------------------- box copies ---- */
+/* One description serves pack, unpack, pack+put and direct put of a halo
+ * region in either storage order (replaces pack/unpack kernels
+ * src/halo_exchange/ops_halo_exchange.cu:519-664 and the Isend/Irecv/Wait
+ * around them).  A box is a 4-level loop nest; the innermost `run` elements
+ * are contiguous in both source and destination. Strides are in elements. */
+typedef struct {
+  const void *src;
+  void *dst;                 /* may be a peer pointer */
+  int64_t s1, s2, s3;        /* source strides of loop levels 1 (fastest) .. 3 */
+  int64_t d1, d2, d3;        /* destination strides */
+  int32_t n1, n2, n3, run;   /* extents */
+  uint64_t *signal;          /* flag to publish after the box is complete (may be peer), or NULL */
+  const uint64_t *wait;      /* local flag to wait on before touching the box, or NULL */
+} TzbBox;
+
+/* A plan is the device image of the boxes plus a table that cuts them into
+ * block-sized work items.  Build it on the host, copy `planBytes` to the
+ * device once, launch many times. */
+typedef struct {
+  int32_t nBoxes;
+  int32_t nItems;
+  int32_t elemSize;          /* 4 or 8 */
+  int32_t reserved;
+  size_t planBytes;          /* size of the host/device image */
+  size_t scratchBytes;       /* zeroed device scratch needed at launch (per-box counters) */
+  size_t payloadBytes;       /* bytes moved per launch */
+} TzbBoxPlanInfo;
+
+/* Pass hostImage == NULL to query sizes only. */
+int tzb_boxcopy_plan(const TzbBox *boxes, int nBoxes, int elemSize, TzbBoxPlanInfo *info,
+                     void *hostImage);
+/* devPlan: device copy of the image. scratch: info.scratchBytes of zeroed device
+ * memory (the kernel leaves it zeroed again). */
+int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t epoch,
+                       void *scratch, void *stream);
+
+/* ----------------------------------------------------------------- flags ---- */
+/* publish epoch to up to 32 (possibly peer) flags; wait for n contiguous local flags. */
+typedef struct {
+  int n;
+  uint64_t *flag[32];
+} TzbFlagList;
+int tzb_flags_signal(const TzbFlagList *list, uint64_t epoch, void *stream);
+int tzb_flags_wait(const uint64_t *flags, int n, uint64_t epoch, void *stream);
+
+/* ------------------------------------------------------------ diagnostics -- */
+/* plain device copy used as the local bandwidth yardstick in the benchmarks */
+int tzb_copy_bytes(void *dst, const void *src, size_t bytes, void *stream);
+/* number of kernels launched through this library since load (for bench.py's launch count) */
+uint64_t tzb_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TENZING_B200_H */

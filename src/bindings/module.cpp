@@ -571,6 +571,45 @@ PYBIND11_MODULE(_C, m) {
       .def("num_rows", [](const CsvBenchmarker &b) { return b.rows().size(); });
   py::class_<PyBenchmarker, Benchmarker>(m, "PyBenchmarker").def(py::init<py::object>());
 
+  // device-timed steps with an L2 flush between them (bench.py): returns seconds per step
+  m.def(
+      "device_time_steps",
+      [](Seq &seq, Platform &plat, int steps, uintptr_t flushPtr, size_t flushBytes) {
+        std::vector<double> out;
+        if (plat.is_null()) return out;
+        cudaEvent_t start, stop;
+        std::vector<cudaEvent_t> joins(size_t(plat.num_streams()));
+        CUDA_RUNTIME(cudaEventCreate(&start));
+        CUDA_RUNTIME(cudaEventCreate(&stop));
+        for (auto &e : joins) CUDA_RUNTIME(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        cudaStream_t s0 = plat.cuda_stream(plat.streams_[0]);
+        for (int i = 0; i < steps; ++i) {
+          if (flushPtr && flushBytes)
+            CUDA_RUNTIME(cudaMemsetAsync(reinterpret_cast<void *>(flushPtr), i & 0xff, flushBytes, s0));
+          plat.synchronize();
+          plat.comm().barrier();
+          CUDA_RUNTIME(cudaEventRecord(start, s0));
+          for (int k = 1; k < plat.num_streams(); ++k)
+            CUDA_RUNTIME(cudaStreamWaitEvent(plat.cuda_stream(plat.streams_[size_t(k)]), start, 0));
+          run_sequence(seq, plat);
+          for (int k = 1; k < plat.num_streams(); ++k) {
+            CUDA_RUNTIME(cudaEventRecord(joins[size_t(k)], plat.cuda_stream(plat.streams_[size_t(k)])));
+            CUDA_RUNTIME(cudaStreamWaitEvent(s0, joins[size_t(k)], 0));
+          }
+          CUDA_RUNTIME(cudaEventRecord(stop, s0));
+          CUDA_RUNTIME(cudaEventSynchronize(stop));
+          float ms = 0;
+          CUDA_RUNTIME(cudaEventElapsedTime(&ms, start, stop));
+          out.push_back(double(ms) * 1e-3);
+        }
+        cudaEventDestroy(start);
+        cudaEventDestroy(stop);
+        for (auto &e : joins) cudaEventDestroy(e);
+        return out;
+      },
+      py::arg("seq"), py::arg("plat"), py::arg("steps"), py::arg("flush_ptr") = 0,
+      py::arg("flush_bytes") = 0, py::call_guard<py::gil_scoped_release>());
+
   // ---- DFS ----
   py::module_ d = m.def_submodule("dfs");
   py::class_<dfs::Opts>(d, "Opts")

@@ -1,0 +1,267 @@
+// Batched strided box copies for sm_100a: one kernel moves any set of halo
+// regions (pack, unpack, pack fused with the put into a peer GPU, direct put
+// into the peer's ghost cells), waits on / publishes the cross-GPU flags of
+// each region, and is cut into equal work items so all 148 SMs stay busy
+// whatever the mix of thick faces, thin faces, edges and corners.
+//
+// Reference counterparts: pack/unpack kernels
+// src/halo_exchange/ops_halo_exchange.cu:519-664 (which ignore their thread
+// indices) and the MPI_Isend/Irecv/Wait ops around them.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <atomic>
+#include <cstdint>
+#include <cstring>
+#include <vector>
+
+#include "device_sync.cuh"
+#include "tenzing_b200.h"
+
+namespace tzb {
+
+extern std::atomic<uint64_t> g_launches;
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kWarps = kThreads / 32;
+constexpr int kSMs = 148;
+constexpr int kBlocksPerSM = 8;
+// a work item moves about this many bytes: small enough that the largest
+// workload yields several items per resident block, large enough to amortise
+// the per-item bookkeeping
+constexpr int64_t kItemBytes = 32 * 1024;
+
+struct alignas(16) BoxDesc {
+  const char *src;
+  char *dst;
+  int64_t s1, s2, s3, d1, d2, d3; // element strides
+  int32_t n1, n2, n3, run;
+  uint64_t *signal;
+  const uint64_t *wait;
+  int32_t nItems; // work items this box was cut into
+  int32_t pad;
+};
+
+// rows [i1, i1+c1) x [i2, i2+c2) of plane i3 of box `box`
+struct alignas(8) WorkItem {
+  int32_t box, i3, i2, c2, i1, c1;
+};
+
+struct PlanHeader {
+  int32_t nBoxes, nItems, elemSize, pad;
+  // followed by BoxDesc[nBoxes], WorkItem[nItems]
+};
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads, kBlocksPerSM)
+box_copy_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restrict__ items, int nItems,
+                uint64_t epoch, unsigned *counters) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int it = blockIdx.x; it < nItems; it += gridDim.x) {
+    const WorkItem w = items[it];
+    const BoxDesc &b = boxes[w.box];
+    if (b.wait) {
+      // the data of this box is only there once the producer published this epoch
+      if (threadIdx.x == 0) wait_flag_geq(b.wait, epoch);
+      __syncthreads();
+    }
+    const T *src = reinterpret_cast<const T *>(b.src) + int64_t(w.i3) * b.s3;
+    T *dst = reinterpret_cast<T *>(b.dst) + int64_t(w.i3) * b.d3;
+    const int run = b.run;
+    const int rows = w.c1 * w.c2;
+    if (run >= 64) {
+      // thick rows: one warp per row, lanes stride through the contiguous run,
+      // four independent 8 B accesses in flight per lane
+      for (int r = warp; r < rows; r += kWarps) {
+        const int j2 = r / w.c1, j1 = r - j2 * w.c1;
+        const T *s = src + int64_t(w.i2 + j2) * b.s2 + int64_t(w.i1 + j1) * b.s1;
+        T *d = dst + int64_t(w.i2 + j2) * b.d2 + int64_t(w.i1 + j1) * b.d1;
+        int e = lane;
+        for (; e + 96 < run; e += 128) {
+          const T v0 = s[e], v1 = s[e + 32], v2 = s[e + 64], v3 = s[e + 96];
+          d[e] = v0;
+          d[e + 32] = v1;
+          d[e + 64] = v2;
+          d[e + 96] = v3;
+        }
+        for (; e < run; e += 32) d[e] = s[e];
+      }
+    } else {
+      // thin rows (x-faces, edges, corners): threads run over (row, element)
+      // pairs so that whichever side is dense is accessed fully coalesced
+      const int total = rows * run;
+      for (int f = threadIdx.x; f < total; f += kThreads) {
+        const int r = f / run, e = f - r * run;
+        const int j2 = r / w.c1, j1 = r - j2 * w.c1;
+        dst[int64_t(w.i2 + j2) * b.d2 + int64_t(w.i1 + j1) * b.d1 + e] =
+            src[int64_t(w.i2 + j2) * b.s2 + int64_t(w.i1 + j1) * b.s1 + e];
+      }
+    }
+    if (b.signal) {
+      // last item of the box publishes the epoch to the (peer) flag
+      if (block_arrive_last(counters + w.box, unsigned(b.nItems))) {
+        if (threadIdx.x == 0) st_release_sys(b.signal, epoch);
+      }
+    }
+  }
+}
+
+__global__ void flags_signal_kernel(TzbFlagList l, uint64_t epoch) {
+  if (int(threadIdx.x) < l.n) {
+    __threadfence_system();
+    st_release_sys(l.flag[threadIdx.x], epoch);
+  }
+}
+
+__global__ void flags_wait_kernel(const uint64_t *flags, int n, uint64_t epoch) {
+  for (int i = threadIdx.x; i < n; i += blockDim.x) wait_flag_geq(flags + i, epoch);
+}
+
+__global__ void __launch_bounds__(kThreads)
+copy_bytes_kernel(uint4 *__restrict__ dst, const uint4 *__restrict__ src, size_t n16) {
+  size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  const size_t stride = size_t(gridDim.x) * blockDim.x;
+  for (; i + 3 * stride < n16; i += 4 * stride) {
+    const uint4 a = src[i], b = src[i + stride], c = src[i + 2 * stride], d = src[i + 3 * stride];
+    dst[i] = a;
+    dst[i + stride] = b;
+    dst[i + 2 * stride] = c;
+    dst[i + 3 * stride] = d;
+  }
+  for (; i < n16; i += stride) dst[i] = src[i];
+}
+
+} // namespace
+} // namespace tzb
+
+using namespace tzb;
+
+extern "C" {
+
+int tzb_boxcopy_plan(const TzbBox *boxes, int nBoxes, int elemSize, TzbBoxPlanInfo *info,
+                     void *hostImage) {
+  if (!info || nBoxes < 0 || (elemSize != 4 && elemSize != 8)) return cudaErrorInvalidValue;
+  std::vector<BoxDesc> descs(nBoxes);
+  std::vector<WorkItem> items;
+  size_t payload = 0;
+  for (int b = 0; b < nBoxes; ++b) {
+    const TzbBox &in = boxes[b];
+    if (in.n1 < 0 || in.n2 < 0 || in.n3 < 0 || in.run < 0) return cudaErrorInvalidValue;
+    BoxDesc &d = descs[b];
+    d.src = static_cast<const char *>(in.src);
+    d.dst = static_cast<char *>(in.dst);
+    d.s1 = in.s1, d.s2 = in.s2, d.s3 = in.s3;
+    d.d1 = in.d1, d.d2 = in.d2, d.d3 = in.d3;
+    d.n1 = in.n1, d.n2 = in.n2, d.n3 = in.n3, d.run = in.run;
+    d.signal = in.signal;
+    d.wait = in.wait;
+    d.pad = 0;
+    const int64_t rowBytes = int64_t(in.run) * elemSize;
+    const int64_t volume = rowBytes * in.n1 * in.n2 * in.n3;
+    payload += size_t(volume);
+    int count = 0;
+    if (volume == 0) {
+      // an empty box still has to wait/publish its flags
+      if (in.signal || in.wait) {
+        items.push_back(WorkItem{b, 0, 0, 0, 0, 0});
+        count = 1;
+      }
+    } else {
+      // rows per item, then cut (i2, i1) into c2 x c1 tiles of about that many rows
+      const int64_t rowsPerItem = std::max<int64_t>(1, kItemBytes / std::max<int64_t>(rowBytes, 1));
+      int c1 = int(std::min<int64_t>(in.n1, rowsPerItem));
+      int c2 = int(std::min<int64_t>(in.n2, std::max<int64_t>(1, rowsPerItem / c1)));
+      for (int i3 = 0; i3 < in.n3; ++i3)
+        for (int i2 = 0; i2 < in.n2; i2 += c2)
+          for (int i1 = 0; i1 < in.n1; i1 += c1) {
+            items.push_back(WorkItem{b, i3, i2, std::min(c2, in.n2 - i2), i1, std::min(c1, in.n1 - i1)});
+            ++count;
+          }
+    }
+    d.nItems = count;
+  }
+  // interleave the boxes' items so that concurrently running blocks touch
+  // different regions (and different peers) instead of draining one box at a time
+  if (nBoxes > 1) {
+    std::vector<std::vector<WorkItem>> perBox(nBoxes);
+    for (const WorkItem &w : items) perBox[w.box].push_back(w);
+    std::vector<WorkItem> mixed;
+    mixed.reserve(items.size());
+    std::vector<size_t> pos(nBoxes, 0);
+    // proportional round-robin: each sweep takes from box b a share matching its size
+    size_t maxItems = 1;
+    for (auto &v : perBox) maxItems = std::max(maxItems, v.size());
+    for (size_t step = 1; step <= maxItems; ++step) {
+      for (int b = 0; b < nBoxes; ++b) {
+        const size_t want = perBox[b].size() * step / maxItems;
+        while (pos[b] < want) mixed.push_back(perBox[b][pos[b]++]);
+      }
+    }
+    items.swap(mixed);
+  }
+  info->nBoxes = nBoxes;
+  info->nItems = int(items.size());
+  info->elemSize = elemSize;
+  info->reserved = 0;
+  info->planBytes = sizeof(PlanHeader) + sizeof(BoxDesc) * size_t(nBoxes) + sizeof(WorkItem) * items.size();
+  info->scratchBytes = sizeof(unsigned) * size_t(std::max(nBoxes, 1));
+  info->payloadBytes = payload;
+  if (hostImage) {
+    char *p = static_cast<char *>(hostImage);
+    PlanHeader h{nBoxes, int(items.size()), elemSize, 0};
+    std::memcpy(p, &h, sizeof(h));
+    p += sizeof(h);
+    if (nBoxes) std::memcpy(p, descs.data(), sizeof(BoxDesc) * size_t(nBoxes));
+    p += sizeof(BoxDesc) * size_t(nBoxes);
+    if (!items.empty()) std::memcpy(p, items.data(), sizeof(WorkItem) * items.size());
+  }
+  return cudaSuccess;
+}
+
+int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t epoch,
+                       void *scratch, void *stream) {
+  if (!devPlan || !info) return cudaErrorInvalidValue;
+  if (info->nItems == 0) return cudaSuccess;
+  const char *p = static_cast<const char *>(devPlan) + sizeof(PlanHeader);
+  const BoxDesc *boxes = reinterpret_cast<const BoxDesc *>(p);
+  const WorkItem *items =
+      reinterpret_cast<const WorkItem *>(p + sizeof(BoxDesc) * size_t(info->nBoxes));
+  const int blocks = std::min(info->nItems, kSMs * kBlocksPerSM);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  ++g_launches;
+  if (info->elemSize == 8)
+    box_copy_kernel<double><<<blocks, kThreads, 0, s>>>(boxes, items, info->nItems, epoch,
+                                                        static_cast<unsigned *>(scratch));
+  else
+    box_copy_kernel<float><<<blocks, kThreads, 0, s>>>(boxes, items, info->nItems, epoch,
+                                                       static_cast<unsigned *>(scratch));
+  return cudaGetLastError();
+}
+
+int tzb_flags_signal(const TzbFlagList *list, uint64_t epoch, void *stream) {
+  if (!list || list->n < 0 || list->n > 32) return cudaErrorInvalidValue;
+  if (list->n == 0) return cudaSuccess;
+  ++g_launches;
+  flags_signal_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(*list, epoch);
+  return cudaGetLastError();
+}
+
+int tzb_flags_wait(const uint64_t *flags, int n, uint64_t epoch, void *stream) {
+  if (n <= 0) return cudaSuccess;
+  ++g_launches;
+  flags_wait_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(flags, n, epoch);
+  return cudaGetLastError();
+}
+
+int tzb_copy_bytes(void *dst, const void *src, size_t bytes, void *stream) {
+  if (bytes % 16) return cudaErrorInvalidValue;
+  if (!bytes) return cudaSuccess;
+  ++g_launches;
+  copy_bytes_kernel<<<kSMs * kBlocksPerSM, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<uint4 *>(dst), static_cast<const uint4 *>(src), bytes / 16);
+  return cudaGetLastError();
+}
+
+} // extern "C"

@@ -494,11 +494,14 @@ Result explore(const Graph<OpBase> &g, Platform &plat, Benchmarker &benchmarker,
     TENZING_COUNTER_OP(mcts, BENCHMARK_TIME, += counters::now() - t);
     comm.barrier();
 
-    if (rank == 0) {
+    {
+      // every rank keeps the (identical, max-reduced) results; only rank 0 owns the tree
       SimResult sr;
       sr.path = order;
       sr.benchResult = br;
       result.simResults.push_back(std::move(sr));
+    }
+    if (rank == 0) {
       t = counters::now();
       endpoint->backprop(strategy, br);
       TENZING_COUNTER_OP(mcts, BACKPROP_TIME, += counters::now() - t);

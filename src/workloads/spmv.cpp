@@ -1,0 +1,423 @@
+#include "tenzing/spmv/row_part_spmv.hpp"
+
+#include <cstring>
+#include <set>
+
+#include "tenzing/cuda/cuda_runtime.hpp"
+#include "tenzing/halo/halo_exchange.hpp" // CudaFreeDeleter
+#include "tenzing_b200.h"
+
+namespace tzb {
+// C++ kernel entries with an explicit lanes-per-row hint (src/cuda/spmv_kernels.cu)
+cudaError_t spmv_csr(int, const int *, const int *, const double *, const double *, double *, bool,
+                     int, cudaStream_t);
+cudaError_t spmv_csr(int, const int *, const int *, const float *, const float *, float *, bool,
+                     int, cudaStream_t);
+cudaError_t spmv_csr_wait(int, const int *, const int *, const double *, const double *, double *,
+                          bool, int, const uint64_t *, int, uint64_t, cudaStream_t);
+cudaError_t spmv_csr_wait(int, const int *, const int *, const float *, const float *, float *,
+                          bool, int, const uint64_t *, int, uint64_t, cudaStream_t);
+} // namespace tzb
+
+namespace tenzing {
+
+namespace {
+
+std::shared_ptr<void> to_device(const void *host, size_t bytes, bool null) {
+  if (null) {
+    void *p = std::malloc(bytes ? bytes : 1);
+    if (bytes) std::memcpy(p, host, bytes);
+    return std::shared_ptr<void>(p, [](void *q) { std::free(q); });
+  }
+  void *p = nullptr;
+  CUDA_RUNTIME(cudaMalloc(&p, bytes ? bytes : 16));
+  if (bytes) CUDA_RUNTIME(cudaMemcpy(p, host, bytes, cudaMemcpyHostToDevice));
+  return std::shared_ptr<void>(p, CudaFreeDeleter());
+}
+
+template <typename Scalar>
+DeviceCsr<Scalar> upload(const CsrMat<int, Scalar> &m, bool null) {
+  DeviceCsr<Scalar> d;
+  d.rows = int(m.num_rows());
+  d.cols = int(m.num_cols());
+  d.nnz = m.nnz();
+  d.rowPtr = to_device(m.rowPtr_.data(), m.rowPtr_.size() * sizeof(int), null);
+  d.colInd = to_device(m.colInd_.data(), m.colInd_.size() * sizeof(int), null);
+  d.val = to_device(m.val_.data(), m.val_.size() * sizeof(Scalar), null);
+  return d;
+}
+
+size_t up256(size_t v) { return (v + 255) / 256 * 256; }
+
+} // namespace
+
+template <typename Scalar>
+RowPartSpmv<Scalar>::RowPartSpmv(std::shared_ptr<Communicator> comm,
+                                 const CsrMat<int, Scalar> &myRows, int64_t n,
+                                 SymmetricHeap::Memory memory)
+    : n_(n) {
+  if (!comm) comm = std::make_shared<SelfComm>();
+  const int me = comm->rank(), np = comm->size();
+  const bool null = memory == SymmetricHeap::Memory::Host;
+  range_ = get_partition(n, me, np);
+  if (myRows.num_rows() != range_.extent())
+    THROW_RUNTIME("rank " << me << " holds " << myRows.num_rows() << " rows, expected "
+                          << range_.extent());
+  split_ = split_local_remote(myRows, range_.lb, range_.ub);
+  lA_ = upload(split_.local, null);
+  rA_ = upload(split_.remote, null);
+
+  // what I need, grouped by owner (globals are ascending, so groups are contiguous)
+  const std::vector<int> &need = split_.globals;
+  {
+    size_t i = 0;
+    while (i < need.size()) {
+      const int owner = get_owner(n, need[i], np);
+      const Range orange = get_partition(n, owner, np);
+      size_t j = i;
+      while (j < need.size() && need[j] < orange.ub) ++j;
+      Param p;
+      p.peer = owner, p.displ = int(i), p.count = int(j - i);
+      recvParams_.push_back(p);
+      i = j;
+    }
+  }
+
+  // everybody learns everybody's need list (set-up only; the reference does an
+  // all-pairs Isend/Probe/Recv here, row_part_spmv.cuh:321-403)
+  std::string mine(reinterpret_cast<const char *>(need.data()), need.size() * sizeof(int));
+  const std::vector<std::string> all = comm->allgather_string(mine);
+  std::vector<int> sendIdx;
+  for (int r = 0; r < np; ++r) {
+    if (r == me) continue;
+    const int *theirs = reinterpret_cast<const int *>(all[size_t(r)].data());
+    const size_t cnt = all[size_t(r)].size() / sizeof(int);
+    const int *lo = std::lower_bound(theirs, theirs + cnt, int(range_.lb));
+    const int *hi = std::lower_bound(theirs, theirs + cnt, int(range_.ub));
+    if (lo == hi) continue;
+    Param p;
+    p.peer = r, p.displ = int(sendIdx.size()), p.count = int(hi - lo), p.dstDispl = int(lo - theirs);
+    for (const int *q = lo; q != hi; ++q) sendIdx.push_back(*q - int(range_.lb));
+    sendParams_.push_back(p);
+  }
+  numSend_ = int(sendIdx.size());
+  xSendIdx_ = to_device(sendIdx.data(), sendIdx.size() * sizeof(int), null);
+  const uint32_t zero = 0;
+  counter_ = to_device(&zero, sizeof(zero), null);
+
+  std::set<int> ps;
+  for (const auto &p : sendParams_) ps.insert(p.peer);
+  for (const auto &p : recvParams_) ps.insert(p.peer);
+  peers_.assign(ps.begin(), ps.end());
+  if (peers_.size() > 16) THROW_RUNTIME("more than 16 SpMV peers are not supported");
+
+  // symmetric allocation sized by the largest rank
+  double sizes[3] = {double(range_.extent()), double(need.size()), double(numSend_)};
+  comm->allreduce_max(sizes, 3);
+  const size_t maxRows = size_t(sizes[0]), maxRemote = size_t(sizes[1]), maxSend = size_t(sizes[2]);
+  const size_t es = sizeof(Scalar);
+  const size_t flagBytes = sizeof(uint64_t) * 3 * size_t(np);
+  const size_t total = 3 * up256(maxRows * es) + 2 * up256(maxRemote * es) + up256(maxSend * es) +
+                       up256(flagBytes) + 4096;
+  heap_.reset(new SymmetricHeap(comm, total, memory));
+  lxOff_ = heap_->alloc(maxRows * es);
+  lyOff_ = heap_->alloc(maxRows * es);
+  ryOff_ = heap_->alloc(maxRows * es);
+  rxOff_[0] = heap_->alloc(maxRemote * es);
+  rxOff_[1] = heap_->alloc(maxRemote * es);
+  sendOff_ = heap_->alloc(maxSend * es);
+  flagOff_ = heap_->alloc(flagBytes);
+}
+
+template <typename Scalar> size_t RowPartSpmv<Scalar>::hbm_bytes() const {
+  const size_t es = sizeof(Scalar);
+  const size_t nnz = size_t(lA_.nnz + rA_.nnz), rows = size_t(lA_.rows);
+  // val + colInd per nnz, two rowPtr streams, x read once (local + remote), y written/updated
+  return nnz * (es + 4) + 2 * (rows + 1) * 4 + (rows + size_t(num_remote_cols())) * es + 2 * rows * es;
+}
+
+template <typename Scalar>
+std::shared_ptr<RowPartSpmv<Scalar>> make_band_spmv(std::shared_ptr<Communicator> comm, int64_t n,
+                                                    int64_t bw, int nnzPerRow, uint64_t seed,
+                                                    SymmetricHeap::Memory memory) {
+  if (!comm) comm = std::make_shared<SelfComm>();
+  const Range r = get_partition(n, comm->rank(), comm->size());
+  auto rows = random_band_rows<int, Scalar>(n, bw, nnzPerRow, r.lb, r.ub, seed);
+  return std::make_shared<RowPartSpmv<Scalar>>(comm, rows, n, memory);
+}
+template std::shared_ptr<RowPartSpmv<double>> make_band_spmv<double>(std::shared_ptr<Communicator>,
+                                                                     int64_t, int64_t, int, uint64_t,
+                                                                     SymmetricHeap::Memory);
+template std::shared_ptr<RowPartSpmv<float>> make_band_spmv<float>(std::shared_ptr<Communicator>,
+                                                                   int64_t, int64_t, int, uint64_t,
+                                                                   SymmetricHeap::Memory);
+
+// ---------------------------------------------------------------- ops
+namespace {
+
+template <typename Scalar> using SpmvPtr = std::shared_ptr<RowPartSpmv<Scalar>>;
+template <typename Scalar> using St = typename RowPartSpmv<Scalar>::Style;
+
+cudaError_t k_gather(int n, const int *idx, const double *s, double *d, cudaStream_t st) {
+  return cudaError_t(tzb_gather_f64(n, idx, s, d, st));
+}
+cudaError_t k_gather(int n, const int *idx, const float *s, float *d, cudaStream_t st) {
+  return cudaError_t(tzb_gather_f32(n, idx, s, d, st));
+}
+cudaError_t k_add(int n, const double *a, double *y, cudaStream_t st) {
+  return cudaError_t(tzb_vector_add_f64(n, a, y, st));
+}
+cudaError_t k_add(int n, const float *a, float *y, cudaStream_t st) {
+  return cudaError_t(tzb_vector_add_f32(n, a, y, st));
+}
+cudaError_t k_gather_put(const TzbGatherPutArgs *a, const int *idx, const double *s, uint64_t e,
+                         uint32_t *c, cudaStream_t st) {
+  return cudaError_t(tzb_gather_put_f64(a, idx, s, e, c, st));
+}
+cudaError_t k_gather_put(const TzbGatherPutArgs *a, const int *idx, const float *s, uint64_t e,
+                         uint32_t *c, cudaStream_t st) {
+  return cudaError_t(tzb_gather_put_f32(a, idx, s, e, c, st));
+}
+
+// ly = A_local * lx
+template <typename Scalar> class LocalSpMV : public GpuOp {
+  SpmvPtr<Scalar> s_;
+
+public:
+  explicit LocalSpMV(SpmvPtr<Scalar> s) : s_(std::move(s)) {}
+  std::string name() const override { return "yl"; }
+  CLONE_DEF(LocalSpMV)
+  void run(cudaStream_t st) override {
+    if (s_->null_device()) return;
+    const auto &A = s_->lA();
+    CUDA_RUNTIME(tzb::spmv_csr(A.rows, A.row_ptr(), A.col_ind(), A.values(), s_->lx(), s_->ly(),
+                               false, A.nnz_per_row(), st));
+  }
+};
+
+// remote product A_remote * rx.  intoLy: accumulate into ly (yl must precede),
+// else write ry.  wait: fuse the wait for every rank's flag of this epoch.
+template <typename Scalar> class RemoteSpMV : public GpuOp {
+  SpmvPtr<Scalar> s_;
+  bool intoLy_, wait_;
+  St<Scalar> style_;
+
+public:
+  RemoteSpMV(SpmvPtr<Scalar> s, bool intoLy, bool wait, St<Scalar> style)
+      : s_(std::move(s)), intoLy_(intoLy), wait_(wait), style_(style) {}
+  std::string name() const override { return "yr"; }
+  CLONE_DEF(RemoteSpMV)
+  void run(cudaStream_t) override { THROW_RUNTIME("yr needs the platform epoch"); }
+  void run(Platform &plat, cudaStream_t st) override {
+    if (s_->null_device() || plat.is_null()) return;
+    const auto &A = s_->rA();
+    const Scalar *x = s_->rx(s_->rank(), int(plat.epoch() & 1));
+    Scalar *y = intoLy_ ? s_->ly() : s_->ry();
+    if (wait_) {
+      CUDA_RUNTIME(tzb::spmv_csr_wait(A.rows, A.row_ptr(), A.col_ind(), A.values(), x, y, intoLy_,
+                                      A.nnz_per_row(), s_->flag(s_->rank(), style_, 0), s_->size(),
+                                      plat.epoch(), st));
+    } else {
+      CUDA_RUNTIME(tzb::spmv_csr(A.rows, A.row_ptr(), A.col_ind(), A.values(), x, y, intoLy_,
+                                 A.nnz_per_row(), st));
+    }
+  }
+};
+
+// the reference's Scatter, named "Pack": xSendBuf[i] = lx[xSendIdx[i]]
+template <typename Scalar> class Scatter : public GpuOp {
+  SpmvPtr<Scalar> s_;
+
+public:
+  explicit Scatter(SpmvPtr<Scalar> s) : s_(std::move(s)) {}
+  std::string name() const override { return "Pack"; }
+  CLONE_DEF(Scatter)
+  void run(cudaStream_t st) override {
+    if (s_->null_device()) return;
+    CUDA_RUNTIME(k_gather(s_->num_send(), s_->x_send_idx(), s_->lx(), s_->x_send_buf(), st));
+  }
+};
+
+// ly += ry
+template <typename Scalar> class VectorAdd : public GpuOp {
+  SpmvPtr<Scalar> s_;
+
+public:
+  explicit VectorAdd(SpmvPtr<Scalar> s) : s_(std::move(s)) {}
+  std::string name() const override { return "y"; }
+  CLONE_DEF(VectorAdd)
+  void run(cudaStream_t st) override {
+    if (s_->null_device()) return;
+    CUDA_RUNTIME(k_add(int(s_->row_range().extent()), s_->ry(), s_->ly(), st));
+  }
+};
+
+// gather fused with the put into every peer's rx, then one flag per rank
+template <typename Scalar> class PackPut : public GpuOp {
+  SpmvPtr<Scalar> s_;
+  St<Scalar> style_;
+
+public:
+  PackPut(SpmvPtr<Scalar> s, St<Scalar> style) : s_(std::move(s)), style_(style) {}
+  std::string name() const override { return "PackPut"; }
+  CLONE_DEF(PackPut)
+  void run(cudaStream_t) override { THROW_RUNTIME("PackPut needs the platform epoch"); }
+  void run(Platform &plat, cudaStream_t st) override {
+    if (s_->null_device() || plat.is_null()) return;
+    const int np = s_->size(), me = s_->rank(), parity = int(plat.epoch() & 1);
+    TzbGatherPutArgs a;
+    std::memset(&a, 0, sizeof(a));
+    a.nPeers = np;
+    // one slot per rank, in rank order; ranks that get no data still get the flag so the
+    // handshake is all-to-all and nobody can run more than one epoch ahead of anybody
+    size_t k = 0;
+    const auto &sp = s_->send_params();
+    int displ = 0;
+    for (int r = 0; r < np; ++r) {
+      a.displ[r] = displ;
+      a.peerFlag[r] = s_->flag(r, style_, me);
+      if (k < sp.size() && sp[k].peer == r) {
+        a.peerDst[r] = s_->rx(r, parity) + sp[k].dstDispl;
+        displ += sp[k].count;
+        ++k;
+      }
+    }
+    a.displ[np] = displ;
+    CUDA_RUNTIME(k_gather_put(&a, s_->x_send_idx(), s_->lx(), plat.epoch(), s_->counter(), st));
+  }
+};
+
+// host-driven transport of the reference structure (copy engine + flags)
+struct SpmvTransport {
+  cudaStream_t send = nullptr, recv = nullptr;
+  bool null;
+  explicit SpmvTransport(bool n) : null(n) {
+    if (null) return;
+    CUDA_RUNTIME(cudaStreamCreateWithFlags(&send, cudaStreamNonBlocking));
+    CUDA_RUNTIME(cudaStreamCreateWithFlags(&recv, cudaStreamNonBlocking));
+  }
+  ~SpmvTransport() {
+    if (send) cudaStreamDestroy(send);
+    if (recv) cudaStreamDestroy(recv);
+  }
+};
+
+template <typename Scalar> class PostSend : public CpuOp {
+  SpmvPtr<Scalar> s_;
+  std::shared_ptr<SpmvTransport> tr_;
+
+public:
+  PostSend(SpmvPtr<Scalar> s, std::shared_ptr<SpmvTransport> tr) : s_(std::move(s)), tr_(std::move(tr)) {}
+  std::string name() const override { return "PostSend"; }
+  CLONE_DEF(PostSend)
+  void run(Platform &plat) override {
+    if (tr_->null || plat.is_null()) return;
+    const int parity = int(plat.epoch() & 1), me = s_->rank();
+    for (const auto &p : s_->send_params())
+      CUDA_RUNTIME(cudaMemcpyAsync(s_->rx(p.peer, parity) + p.dstDispl, s_->x_send_buf() + p.displ,
+                                   size_t(p.count) * sizeof(Scalar), cudaMemcpyDeviceToDevice,
+                                   tr_->send));
+    TzbFlagList l;
+    l.n = 0;
+    for (int r = 0; r < s_->size(); ++r) l.flag[l.n++] = s_->flag(r, St<Scalar>::Reference, me);
+    CUDA_RUNTIME(cudaError_t(tzb_flags_signal(&l, plat.epoch(), tr_->send)));
+  }
+};
+
+template <typename Scalar> class WaitSend : public CpuOp {
+  std::shared_ptr<SpmvTransport> tr_;
+
+public:
+  explicit WaitSend(std::shared_ptr<SpmvTransport> tr) : tr_(std::move(tr)) {}
+  std::string name() const override { return "WaitSend"; }
+  CLONE_DEF(WaitSend)
+  void run(Platform &plat) override {
+    if (tr_->null || plat.is_null()) return;
+    CUDA_RUNTIME(cudaStreamSynchronize(tr_->send));
+  }
+};
+
+template <typename Scalar> class WaitRecv : public CpuOp {
+  SpmvPtr<Scalar> s_;
+  std::shared_ptr<SpmvTransport> tr_;
+
+public:
+  WaitRecv(SpmvPtr<Scalar> s, std::shared_ptr<SpmvTransport> tr) : s_(std::move(s)), tr_(std::move(tr)) {}
+  std::string name() const override { return "WaitRecv"; }
+  CLONE_DEF(WaitRecv)
+  void run(Platform &plat) override {
+    if (tr_->null || plat.is_null()) return;
+    CUDA_RUNTIME(cudaError_t(tzb_flags_wait(s_->flag(s_->rank(), St<Scalar>::Reference, 0), s_->size(),
+                                            plat.epoch(), tr_->recv)));
+    CUDA_RUNTIME(cudaStreamSynchronize(tr_->recv));
+  }
+};
+
+} // namespace
+
+template <typename Scalar>
+SpMV<Scalar>::SpMV(const std::string &name, const std::shared_ptr<RowPartSpmv<Scalar>> &s, Style style)
+    : name_(name) {
+  Graph<OpBase> &g = graph_;
+  OpPtr yl = std::make_shared<LocalSpMV<Scalar>>(s);
+  if (style == Style::Reference) {
+    auto tr = std::make_shared<SpmvTransport>(s->null_device());
+    OpPtr pack = std::make_shared<Scatter<Scalar>>(s);
+    OpPtr postSend = std::make_shared<PostSend<Scalar>>(s, tr);
+    OpPtr postRecv = std::make_shared<NoOp>("PostRecv");
+    OpPtr waitSend = std::make_shared<WaitSend<Scalar>>(tr);
+    OpPtr waitRecv = std::make_shared<WaitRecv<Scalar>>(s, tr);
+    OpPtr yr = std::make_shared<RemoteSpMV<Scalar>>(s, false, false, style);
+    OpPtr y = std::make_shared<VectorAdd<Scalar>>(s);
+    g.start_then(yl);
+    g.start_then(postRecv);
+    g.start_then(pack);
+    g.then(pack, postSend);
+    g.then(postSend, waitSend);
+    g.then(postSend, waitRecv);
+    g.then(postRecv, waitSend);
+    g.then(postRecv, waitRecv);
+    g.then(waitRecv, yr);
+    g.then(yl, y);
+    g.then(yr, y);
+    g.then_finish(y);
+    g.then_finish(waitSend);
+  } else if (style == Style::Fused) {
+    OpPtr put = std::make_shared<PackPut<Scalar>>(s, style);
+    OpPtr yr = std::make_shared<RemoteSpMV<Scalar>>(s, true, true, style);
+    g.start_then(yl);
+    g.start_then(put);
+    g.then(put, yr);
+    g.then(yl, yr);
+    g.then_finish(yr);
+  } else {
+    OpPtr put = std::make_shared<PackPut<Scalar>>(s, style);
+    OpPtr yr = std::make_shared<RemoteSpMV<Scalar>>(s, false, true, style);
+    OpPtr y = std::make_shared<VectorAdd<Scalar>>(s);
+    g.start_then(yl);
+    g.start_then(put);
+    g.then(put, yr);
+    g.then(yl, y);
+    g.then(yr, y);
+    g.then_finish(y);
+  }
+}
+
+template <typename Scalar>
+std::shared_ptr<ChoiceOp> make_spmv_choice(const std::shared_ptr<RowPartSpmv<Scalar>> &s) {
+  using Style = typename RowPartSpmv<Scalar>::Style;
+  std::vector<OpPtr> alts;
+  alts.push_back(std::make_shared<SpMV<Scalar>>("spmv_reference", s, Style::Reference));
+  alts.push_back(std::make_shared<SpMV<Scalar>>("spmv_fused", s, Style::Fused));
+  alts.push_back(std::make_shared<SpMV<Scalar>>("spmv_fused_separate", s, Style::FusedSeparate));
+  return std::make_shared<ListChoiceOp>("spmv", alts);
+}
+template std::shared_ptr<ChoiceOp> make_spmv_choice<double>(const std::shared_ptr<RowPartSpmv<double>> &);
+template std::shared_ptr<ChoiceOp> make_spmv_choice<float>(const std::shared_ptr<RowPartSpmv<float>> &);
+
+template class RowPartSpmv<double>;
+template class RowPartSpmv<float>;
+template class SpMV<double>;
+template class SpMV<float>;
+
+} // namespace tenzing

@@ -1,0 +1,100 @@
+"""Single-GPU end-to-end checks of both workloads: every implementation style must
+produce exactly the oracle result, for both epoch parities (double buffers)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("order", ["XYZQ", "QXYZ"])
+@pytest.mark.parametrize("style", ["reference", "staged", "direct", "fused_all", "fused_staged"])
+def test_halo_styles_single_rank_periodic(style, order):
+    from tenzing_b200.models import HaloExchange, common
+    h = HaloExchange(nX=20, nY=12, nZ=9, nQ=3, nGhost=3, storage_order=order)
+    seq = common.fixed_schedule(h.graph(style), h.platform)
+    for _ in range(3):  # odd and even epochs
+        h.fill()
+        assert not h.check()
+        h.run(seq)
+        assert h.check(), f"{style}/{order} wrong after exchange"
+
+
+@pytest.mark.parametrize("neighbors", [6, 18])
+def test_halo_fewer_neighbors(neighbors):
+    from tenzing_b200.models import HaloExchange, common
+    h = HaloExchange(nX=16, nQ=2, nGhost=2, neighbors=neighbors)
+    seq = common.fixed_schedule(h.graph("staged"), h.platform)
+    h.fill()
+    h.run(seq)
+    assert h.check()
+
+
+def test_halo_fp32_and_thick_rows():
+    from tenzing_b200.models import HaloExchange, common
+    h = HaloExchange(nX=200, nY=10, nZ=10, nQ=1, nGhost=3, dtype=torch.float32)
+    seq = common.fixed_schedule(h.graph("fused_staged"), h.platform)
+    h.fill()
+    h.run(seq)
+    assert h.check()
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("style", ["reference", "fused", "fused_separate"])
+def test_spmv_styles_single_rank(style, dtype):
+    from tenzing_b200.models import DistributedSpMV, common
+    s = DistributedSpMV(n=20011, nnz_per_row=10, dtype=dtype)
+    seq = common.fixed_schedule(s.graph(style), s.platform)
+    for _ in range(2):
+        s.fill()
+        s.run(seq)
+        assert s.check(), f"{style} wrong"
+
+
+def test_gpu_graph_stream_assignment_equivalence():
+    """reference test/test_gpu_graph.cu:41-118"""
+    import tenzing_b200 as tz
+    from tenzing_b200 import _C
+    k1, k2, k3 = (tz.EmptyGpuOp(n) for n in ("k1", "k2", "k3"))
+    g = tz.Graph()
+    g.start_then(k1)
+    g.then(k1, k2)
+    g.then(k1, k3)
+    g.then_finish(k2)
+    g.then_finish(k3)
+    plat = tz.Platform.make_n_streams(2)
+    st = tz.State(g)
+    ds = st.get_decisions(plat)
+    assigns = [d for d in ds if d.kind() == "AssignOpStream"]
+    assert sorted(d.stream for d in assigns) == [0, 1] and len(ds) == 2
+    s0, s1 = (st.apply(d) for d in assigns)
+    assert bool(_C.state_equivalence(s0, s1))
+    assert bool(_C.graph_equivalence(s0.graph(), s1.graph()))
+    assert s0.graph().contains(tz.BoundGpuOp(k1, assigns[0].stream))
+    execs = [d for d in s0.get_decisions(plat) if d.kind() == "ExecuteOp"]
+    assert len(execs) == 1 and execs[0].op.name() == "k1"
+
+
+def test_dfs_search_on_device_finds_valid_best():
+    from tenzing_b200.models import DistributedSpMV, common
+    s = DistributedSpMV(n=50000, nnz_per_row=10)
+    res = s.search("dfs", style="fused", bench=common.bench_opts(n_iters=3, target_secs=0.001,
+                                                                 check_randomness=False))
+    assert len(res.sim_results) == 8
+    seq, br = common.best_of(res)
+    assert br.pct10 > 0
+    s.fill()
+    s.run(seq)
+    assert s.check()
+    assert res.csv().splitlines()[0].startswith('{"dfs__Opts"')
+
+
+def test_mcts_search_on_device_halo():
+    from tenzing_b200.models import HaloExchange, common
+    h = HaloExchange(nX=32, nQ=1, nGhost=2, neighbors=6)
+    res = h.search("mcts", style="choice", iters=12,
+                   bench=common.bench_opts(n_iters=3, target_secs=0.001, check_randomness=False))
+    assert len(res.sim_results) == 12
+    seq, br = common.best_of(res)
+    h.fill()
+    h.run(seq)
+    assert h.check()
