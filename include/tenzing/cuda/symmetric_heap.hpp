@@ -25,14 +25,14 @@ public:
   SymmetricHeap(const SymmetricHeap &) = delete;
   SymmetricHeap &operator=(const SymmetricHeap &) = delete;
 
-  int rank() const { return comm_->rank(); }
-  int size() const { return comm_->size(); }
+  int rank() const { return rank_; }
+  int size() const { return size_; }
   size_t bytes() const { return bytes_; }
   Memory memory() const { return memory_; }
   Communicator &comm() const { return *comm_; }
   std::shared_ptr<Communicator> comm_ptr() const { return comm_; }
 
-  void *local() const { return bases_[size_t(comm_->rank())]; }
+  void *local() const { return bases_[size_t(rank_)]; }
   void *peer(int rank) const { return bases_.at(size_t(rank)); }
   template <typename T> T *at(int rank, size_t offsetBytes) const {
     return reinterpret_cast<T *>(static_cast<char *>(peer(rank)) + offsetBytes);
@@ -48,6 +48,7 @@ public:
 
 private:
   std::shared_ptr<Communicator> comm_;
+  int rank_ = 0, size_ = 1; // cached: the destructor must not call into the communicator
   size_t bytes_;
   Memory memory_;
   size_t used_ = 0;

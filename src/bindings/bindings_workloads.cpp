@@ -90,6 +90,14 @@ void bind_workloads(py::module_ &m) {
     check(tzb_flags_signal(&l, epoch, ptr<void>(s)), "flags_signal");
   });
   k.def("launch_count", [] { return tzb_launch_count(); });
+  // cudaLimitMaxL2FetchGranularity hint: returns the value the device reports afterwards
+  k.def("set_l2_fetch_granularity", [](size_t bytes) {
+    cudaError_t e = cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, bytes);
+    if (e != cudaSuccess) (void)cudaGetLastError();
+    size_t v = 0;
+    cudaDeviceGetLimit(&v, cudaLimitMaxL2FetchGranularity);
+    return std::make_pair(int(e), v);
+  });
 
   // ---- symmetric heap ----
   py::class_<SymmetricHeap, std::shared_ptr<SymmetricHeap>>(m, "SymmetricHeap")

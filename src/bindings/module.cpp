@@ -57,21 +57,19 @@ public:
 // forwards the control plane to a Python object (torch.distributed wrapper)
 class PyComm : public Communicator {
   py::object obj_;
+  int rank_, size_; // fixed for the life of the group; cached so late callers need no Python
 
 public:
-  explicit PyComm(py::object obj) : obj_(std::move(obj)) {}
+  explicit PyComm(py::object obj) : obj_(std::move(obj)) {
+    rank_ = obj_.attr("rank")().cast<int>();
+    size_ = obj_.attr("size")().cast<int>();
+  }
   ~PyComm() override {
     py::gil_scoped_acquire gil;
     obj_ = py::object();
   }
-  int rank() const override {
-    py::gil_scoped_acquire gil;
-    return obj_.attr("rank")().cast<int>();
-  }
-  int size() const override {
-    py::gil_scoped_acquire gil;
-    return obj_.attr("size")().cast<int>();
-  }
+  int rank() const override { return rank_; }
+  int size() const override { return size_; }
   void barrier() override {
     py::gil_scoped_acquire gil;
     obj_.attr("barrier")();
@@ -310,7 +308,12 @@ PYBIND11_MODULE(_C, m) {
   py::class_<LambdaGpuOp, GpuOp, std::shared_ptr<LambdaGpuOp>>(m, "EmptyGpuOp")
       .def(py::init([](const std::string &n) { return std::make_shared<LambdaGpuOp>(n); }));
   py::class_<BoundGpuOp, BoundOp, std::shared_ptr<BoundGpuOp>>(m, "BoundGpuOp")
-      .def(py::init([](const GpuOpPtr &op, int s) { return std::make_shared<BoundGpuOp>(op, Stream(s)); }))
+      .def(py::init([](const OpPtr &op, int s) {
+        // ops defined in C++ workload libraries arrive typed as OpBase
+        auto g = std::dynamic_pointer_cast<GpuOp>(op);
+        if (!g) throw std::runtime_error("BoundGpuOp: " + op->desc() + " is not a GpuOp");
+        return std::make_shared<BoundGpuOp>(g, Stream(s));
+      }))
       .def("stream", [](const BoundGpuOp &b) { return b.stream().id(); })
       .def("unbound", &BoundGpuOp::unbound);
   py::class_<ChoiceOp, OpBase, std::shared_ptr<ChoiceOp>>(m, "ChoiceOpBase")

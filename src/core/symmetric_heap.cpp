@@ -25,6 +25,8 @@ SymmetricHeap::SymmetricHeap(std::shared_ptr<Communicator> comm, size_t bytes, M
     : comm_(std::move(comm)), bytes_(bytes), memory_(memory) {
   if (!comm_) comm_ = std::make_shared<SelfComm>();
   const int n = comm_->size(), me = comm_->rank();
+  rank_ = me;
+  size_ = n;
   bases_.assign(size_t(n), nullptr);
   ipcOpened_.assign(size_t(n), false);
 
@@ -83,7 +85,7 @@ SymmetricHeap::SymmetricHeap(std::shared_ptr<Communicator> comm, size_t bytes, M
 }
 
 SymmetricHeap::~SymmetricHeap() {
-  const int me = comm_->rank();
+  const int me = rank_;
   for (size_t r = 0; r < bases_.size(); ++r)
     if (ipcOpened_[r] && bases_[r]) cudaIpcCloseMemHandle(bases_[r]);
   if (memory_ == Memory::Host) {

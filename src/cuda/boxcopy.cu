@@ -27,11 +27,13 @@ namespace {
 constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;
 constexpr int kSMs = 148;
-constexpr int kBlocksPerSM = 8;
+constexpr int kBlocksPerSM = 4;
 // a work item moves about this many bytes: small enough that the largest
 // workload yields several items per resident block, large enough to amortise
 // the per-item bookkeeping
 constexpr int64_t kItemBytes = 32 * 1024;
+constexpr int kThick = 8; // 8-byte loads in flight per lane, thick rows
+constexpr int kThin = 8;  // and for thin rows
 
 struct alignas(16) BoxDesc {
   const char *src;
@@ -54,17 +56,29 @@ struct PlanHeader {
   // followed by BoxDesc[nBoxes], WorkItem[nItems]
 };
 
+// Memory-level parallelism is what this kernel lives on: the regions are far
+// larger than L2 reuse could help and every byte is touched once, so each lane
+// keeps kThick/kThin independent 8-byte loads in flight before the first store
+// (thick rows: one warp per row; thin rows: lanes run over (row, element)
+// pairs so the dense side of a pack/unpack stays fully coalesced).
+
 template <typename T>
 __global__ void __launch_bounds__(kThreads, kBlocksPerSM)
 box_copy_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restrict__ items, int nItems,
-                uint64_t epoch, unsigned *counters) {
+                int nBoxes, int anySignal, uint64_t epoch, unsigned *counter) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __shared__ unsigned readyMask; // boxes whose wait flag this block has already seen
+  if (threadIdx.x == 0) readyMask = 0;
+  __syncthreads();
   for (int it = blockIdx.x; it < nItems; it += gridDim.x) {
     const WorkItem w = items[it];
     const BoxDesc &b = boxes[w.box];
     if (b.wait) {
       // the data of this box is only there once the producer published this epoch
-      if (threadIdx.x == 0) wait_flag_geq(b.wait, epoch);
+      if (threadIdx.x == 0 && !((readyMask >> (w.box & 31)) & 1u)) {
+        wait_flag_geq(b.wait, epoch);
+        if (w.box < 32) readyMask |= 1u << w.box;
+      }
       __syncthreads();
     }
     const T *src = reinterpret_cast<const T *>(b.src) + int64_t(w.i3) * b.s3;
@@ -72,38 +86,56 @@ box_copy_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restrict__ 
     const int run = b.run;
     const int rows = w.c1 * w.c2;
     if (run >= 64) {
-      // thick rows: one warp per row, lanes stride through the contiguous run,
-      // four independent 8 B accesses in flight per lane
       for (int r = warp; r < rows; r += kWarps) {
         const int j2 = r / w.c1, j1 = r - j2 * w.c1;
         const T *s = src + int64_t(w.i2 + j2) * b.s2 + int64_t(w.i1 + j1) * b.s1;
         T *d = dst + int64_t(w.i2 + j2) * b.d2 + int64_t(w.i1 + j1) * b.d1;
         int e = lane;
-        for (; e + 96 < run; e += 128) {
-          const T v0 = s[e], v1 = s[e + 32], v2 = s[e + 64], v3 = s[e + 96];
-          d[e] = v0;
-          d[e + 32] = v1;
-          d[e + 64] = v2;
-          d[e + 96] = v3;
+        for (; e + 32 * (kThick - 1) < run; e += 32 * kThick) {
+          T v[kThick];
+#pragma unroll
+          for (int u = 0; u < kThick; ++u) v[u] = __ldcs(s + e + 32 * u);
+#pragma unroll
+          for (int u = 0; u < kThick; ++u) d[e + 32 * u] = v[u];
         }
         for (; e < run; e += 32) d[e] = s[e];
       }
     } else {
-      // thin rows (x-faces, edges, corners): threads run over (row, element)
-      // pairs so that whichever side is dense is accessed fully coalesced
+      // the plan sizes thin items to a multiple of kThreads * kThin elements where it
+      // can, so the scalar tail below is the exception
       const int total = rows * run;
-      for (int f = threadIdx.x; f < total; f += kThreads) {
+      const int c1 = w.c1;
+      auto offsets = [&](int f, int64_t &so, int64_t &dof) {
         const int r = f / run, e = f - r * run;
-        const int j2 = r / w.c1, j1 = r - j2 * w.c1;
-        dst[int64_t(w.i2 + j2) * b.d2 + int64_t(w.i1 + j1) * b.d1 + e] =
-            src[int64_t(w.i2 + j2) * b.s2 + int64_t(w.i1 + j1) * b.s1 + e];
+        const int j2 = r / c1, j1 = r - j2 * c1;
+        so = int64_t(w.i2 + j2) * b.s2 + int64_t(w.i1 + j1) * b.s1 + e;
+        dof = int64_t(w.i2 + j2) * b.d2 + int64_t(w.i1 + j1) * b.d1 + e;
+      };
+      int f = threadIdx.x;
+      for (; f + kThreads * (kThin - 1) < total; f += kThreads * kThin) {
+        T v[kThin];
+        int64_t dof[kThin];
+#pragma unroll
+        for (int u = 0; u < kThin; ++u) {
+          int64_t so;
+          offsets(f + kThreads * u, so, dof[u]);
+          v[u] = src[so];
+        }
+#pragma unroll
+        for (int u = 0; u < kThin; ++u) dst[dof[u]] = v[u];
+      }
+      for (; f < total; f += kThreads) {
+        int64_t so, dof;
+        offsets(f, so, dof);
+        dst[dof] = src[so];
       }
     }
-    if (b.signal) {
-      // last item of the box publishes the epoch to the (peer) flag
-      if (block_arrive_last(counters + w.box, unsigned(b.nItems))) {
-        if (threadIdx.x == 0) st_release_sys(b.signal, epoch);
-      }
+  }
+  if (anySignal) {
+    // one system-scope fence per block; the last block to finish publishes every flag
+    if (block_arrive_last(counter, gridDim.x)) {
+      for (int bx = threadIdx.x; bx < nBoxes; bx += kThreads)
+        if (boxes[bx].signal) st_release_sys(boxes[bx].signal, epoch);
     }
   }
 }
@@ -146,6 +178,12 @@ int tzb_boxcopy_plan(const TzbBox *boxes, int nBoxes, int elemSize, TzbBoxPlanIn
   std::vector<BoxDesc> descs(nBoxes);
   std::vector<WorkItem> items;
   size_t payload = 0;
+  // item size: enough items to give every resident block several, within [4 KB, kItemBytes]
+  int64_t totalBytes = 0;
+  for (int b = 0; b < nBoxes; ++b)
+    totalBytes += int64_t(boxes[b].run) * elemSize * boxes[b].n1 * boxes[b].n2 * boxes[b].n3;
+  const int64_t itemBytes =
+      std::min<int64_t>(kItemBytes, std::max<int64_t>(4096, totalBytes / (kSMs * kBlocksPerSM * 4)));
   for (int b = 0; b < nBoxes; ++b) {
     const TzbBox &in = boxes[b];
     if (in.n1 < 0 || in.n2 < 0 || in.n3 < 0 || in.run < 0) return cudaErrorInvalidValue;
@@ -170,7 +208,18 @@ int tzb_boxcopy_plan(const TzbBox *boxes, int nBoxes, int elemSize, TzbBoxPlanIn
       }
     } else {
       // rows per item, then cut (i2, i1) into c2 x c1 tiles of about that many rows
-      const int64_t rowsPerItem = std::max<int64_t>(1, kItemBytes / std::max<int64_t>(rowBytes, 1));
+      // thick rows are copied one warp per row: never hand a block fewer rows than it has warps
+      const int64_t minRows = in.run >= 64 ? kWarps : 1;
+      int64_t rowsPerItem =
+          std::max<int64_t>(minRows, itemBytes / std::max<int64_t>(rowBytes, 1));
+      if (in.run < 64) {
+        // thin rows: make rows*run a multiple of the unrolled batch (kThreads * kThin elements)
+        const int64_t batch = int64_t(kThreads) * kThin;
+        int64_t g = batch, r = in.run;
+        while (r) { const int64_t t = g % r; g = r; r = t; } // gcd(batch, run)
+        const int64_t quantum = batch / g;
+        if (int64_t(in.n1) * in.n2 >= quantum) rowsPerItem = (rowsPerItem + quantum - 1) / quantum * quantum;
+      }
       int c1 = int(std::min<int64_t>(in.n1, rowsPerItem));
       int c2 = int(std::min<int64_t>(in.n2, std::max<int64_t>(1, rowsPerItem / c1)));
       for (int i3 = 0; i3 < in.n3; ++i3)
@@ -204,9 +253,11 @@ int tzb_boxcopy_plan(const TzbBox *boxes, int nBoxes, int elemSize, TzbBoxPlanIn
   info->nBoxes = nBoxes;
   info->nItems = int(items.size());
   info->elemSize = elemSize;
-  info->reserved = 0;
+  info->reserved = 0; // becomes 1 if any box publishes a flag
+  for (int b = 0; b < nBoxes; ++b)
+    if (boxes[b].signal) info->reserved = 1;
   info->planBytes = sizeof(PlanHeader) + sizeof(BoxDesc) * size_t(nBoxes) + sizeof(WorkItem) * items.size();
-  info->scratchBytes = sizeof(unsigned) * size_t(std::max(nBoxes, 1));
+  info->scratchBytes = 256; // one arrival counter (kept aligned)
   info->payloadBytes = payload;
   if (hostImage) {
     char *p = static_cast<char *>(hostImage);
@@ -231,11 +282,14 @@ int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t
   const int blocks = std::min(info->nItems, kSMs * kBlocksPerSM);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   ++g_launches;
+  const int anySignal = info->reserved;
   if (info->elemSize == 8)
-    box_copy_kernel<double><<<blocks, kThreads, 0, s>>>(boxes, items, info->nItems, epoch,
+    box_copy_kernel<double><<<blocks, kThreads, 0, s>>>(boxes, items, info->nItems, info->nBoxes,
+                                                        anySignal, epoch,
                                                         static_cast<unsigned *>(scratch));
   else
-    box_copy_kernel<float><<<blocks, kThreads, 0, s>>>(boxes, items, info->nItems, epoch,
+    box_copy_kernel<float><<<blocks, kThreads, 0, s>>>(boxes, items, info->nItems, info->nBoxes,
+                                                       anySignal, epoch,
                                                        static_cast<unsigned *>(scratch));
   return cudaGetLastError();
 }

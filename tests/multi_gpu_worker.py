@@ -1,0 +1,86 @@
+"""Worker run under torch.distributed.run by test_gpu_multi.py: one rank per GPU.
+
+Checks, on every rank, that each implementation style of both workloads produces the oracle
+result when the neighbours are OTHER GPUs (peer stores + device flags over NVLink), for several
+consecutive epochs (both staging parities), then runs a short search."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+os.environ.setdefault("TENZING_ACK_NOTICE", "1")
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+from tenzing_b200.parallel import init_process_group_from_env, make_comm  # noqa: E402
+from tenzing_b200.models import HaloExchange, DistributedSpMV, common  # noqa: E402
+
+
+def all_ok(ok):
+    t = torch.tensor([1.0 if ok else 0.0], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    return bool(t.item() > 0.5)
+
+
+def main():
+    rank, world, _ = init_process_group_from_env()
+    comm = make_comm()
+    failures = []
+    for order in ("XYZQ", "QXYZ"):
+        h = HaloExchange(comm=comm, nX=24, nY=10, nZ=12, nQ=2, nGhost=3, storage_order=order)
+        for style in ("reference", "staged", "direct", "fused_all", "fused_staged"):
+            seq = common.fixed_schedule(h.graph(style), h.platform)
+            for _ in range(3):
+                h.fill()
+                comm.barrier()
+                h.run(seq)
+                h.sync()
+                comm.barrier()
+                if not all_ok(h.check()):
+                    failures.append(f"halo {order} {style}")
+                    break
+    for dtype in (torch.float64, torch.float32):
+        for n, bw in ((40_000, None), (30_011, 30_011)):  # band (neighbour peers) and random (all peers)
+            s = DistributedSpMV(comm=comm, n=n, bw=bw, nnz_per_row=10, dtype=dtype)
+            for style in ("reference", "fused", "fused_separate"):
+                seq = common.fixed_schedule(s.graph(style), s.platform)
+                for _ in range(3):
+                    s.fill()
+                    comm.barrier()
+                    s.run(seq)
+                    s.sync()
+                    comm.barrier()
+                    if not all_ok(s.check()):
+                        failures.append(f"spmv {dtype} n={n} {style}")
+                        break
+    # a short search across ranks: rank 0 drives, all ranks execute in lock step
+    h = HaloExchange(comm=comm, nX=32, nQ=1, nGhost=2, neighbors=6)
+    res = h.search("mcts", style="choice", iters=8,
+                   bench=common.bench_opts(n_iters=2, target_secs=0.0005, check_randomness=False))
+    seq, br = common.best_of(res)
+    h.fill()
+    comm.barrier()
+    h.run(seq)
+    h.sync()
+    comm.barrier()
+    if not all_ok(h.check()):
+        failures.append("halo after mcts")
+    s = DistributedSpMV(comm=comm, n=50_000, nnz_per_row=10)
+    res = s.search("dfs", style="fused",
+                   bench=common.bench_opts(n_iters=2, target_secs=0.0005, check_randomness=False))
+    seq, br = common.best_of(res)
+    s.fill()
+    comm.barrier()
+    s.run(seq)
+    s.sync()
+    comm.barrier()
+    if not all_ok(s.check()):
+        failures.append("spmv after dfs")
+    if rank == 0:
+        print("MULTI_GPU_RESULT", "OK" if not failures else "FAIL " + "; ".join(failures), flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+    return 1 if failures else 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
