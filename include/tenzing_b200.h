@@ -106,6 +106,36 @@ int tzb_boxcopy_plan(const TzbBox *boxes, int nBoxes, int elemSize, TzbBoxPlanIn
 int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t epoch,
                        void *scratch, void *stream);
 
+/* Box copy for callers that cannot allocate device memory.  (This entry point has
+ * no counterpart in the reference.)
+ *
+ * tzb_boxcopy_launch needs a device copy of the plan and a zeroed counter, which
+ * the caller normally gets from cudaMalloc.  That is not possible everywhere:
+ * inside another framework's caching allocator a raw cudaMalloc can fragment or
+ * stall the pool, on a latency-critical path the implicit synchronisation of
+ * cudaMalloc/cudaFree is unwelcome, and a plug-in may simply be given buffers
+ * and a stream and no right to allocate.  This variant keeps the plan and the
+ * counter in an array of TZB_STATIC_SCRATCH_BYTES that is built into the
+ * library's device image (so every GPU that loads the library holds that much
+ * memory until the process exits) and calls no cudaMalloc/cudaFree or any other
+ * allocating routine.  Source and destination buffers still come from the caller.
+ *
+ *  - A copy whose plan does not fit is refused with cudaErrorInvalidValue and a
+ *    message in tzb_last_error(); the plan needs about 96 bytes per box plus 24
+ *    bytes per ~32 KB of payload, so the array covers roughly 300 MB per call.
+ *  - The first call on each device looks up the array's device address; make
+ *    that call (with that device current) before any stream capture starts.
+ *  - All calls share the one array, which keeps the previous call's contents;
+ *    the counter is cleared on the stream before each launch.  Two calls whose
+ *    kernels may overlap on the GPU (different streams, no ordering between
+ *    them) race on it: order them, or use tzb_boxcopy_launch for one of them.
+ */
+#define TZB_STATIC_SCRATCH_BYTES (256 * 1024)
+int tzb_boxcopy_static(const TzbBox *boxes, int nBoxes, int elemSize, uint64_t epoch,
+                       void *stream);
+/* message of the last failed tzb_boxcopy_static call on this thread ("" if none) */
+const char *tzb_last_error(void);
+
 /* ----------------------------------------------------------------- flags ---- */
 /* publish epoch to up to 32 (possibly peer) flags; wait for n contiguous local flags. */
 typedef struct {

@@ -12,6 +12,7 @@
 #include <algorithm>
 #include <atomic>
 #include <cstdint>
+#include <cstdio>
 #include <cstring>
 #include <vector>
 
@@ -316,6 +317,110 @@ int tzb_copy_bytes(void *dst, const void *src, size_t bytes, void *stream) {
   copy_bytes_kernel<<<kSMs * kBlocksPerSM, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<uint4 *>(dst), static_cast<const uint4 *>(src), bytes / 16);
   return cudaGetLastError();
+}
+
+} // extern "C"
+
+// ---------------------------------------------------------------------------
+// Allocation-free box copy.
+//
+// tzb_boxcopy_launch() expects the caller to have put the plan image and a
+// zeroed counter into device memory it allocated itself.  Some callers cannot
+// do that: code running inside another framework's memory pool (where a stray
+// cudaMalloc fragments or deadlocks the pool), code on a latency-critical path
+// where the implicit device synchronisation of cudaMalloc/cudaFree is not
+// acceptable, and plug-ins that are handed buffers and a stream and nothing
+// else.  For them the plan image and the counter live in one fixed-size array
+// that is part of this library's device image.  Every GPU that loads the
+// library carries these TZB_STATIC_SCRATCH_BYTES until the process exits.
+// ---------------------------------------------------------------------------
+namespace tzb {
+namespace {
+
+// layout: [0, 256) arrival counter (must be zero at kernel start), [256, ...) plan image
+static __device__ __align__(256) unsigned char g_static_scratch[TZB_STATIC_SCRATCH_BYTES];
+
+constexpr int kMaxDevices = 64;
+constexpr size_t kStaticCounterBytes = 256;
+
+struct StaticScratch {
+  std::atomic<unsigned char *> ptr[kMaxDevices];
+  StaticScratch() {
+    for (auto &p : ptr) p.store(nullptr);
+  }
+};
+StaticScratch g_static;
+
+thread_local char g_lastError[256] = "";
+
+void set_error(const char *fmt, long long a = 0, long long b = 0) {
+  std::snprintf(g_lastError, sizeof(g_lastError), fmt, a, b);
+}
+
+// Device address of the array on the CURRENT device.  In host code the name
+// g_static_scratch is only a stand-in for the symbol, not an address a kernel
+// could use, so the address is asked for once per device and remembered.
+cudaError_t static_scratch_address(unsigned char **out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= kMaxDevices) return cudaErrorInvalidDevice;
+  unsigned char *p = g_static.ptr[dev].load(std::memory_order_acquire);
+  if (!p) {
+    e = cudaGetSymbolAddress(reinterpret_cast<void **>(&p), g_static_scratch);
+    if (e != cudaSuccess) return e;
+    g_static.ptr[dev].store(p, std::memory_order_release); // same answer from every thread
+  }
+  *out = p;
+  return cudaSuccess;
+}
+
+} // namespace
+} // namespace tzb
+
+extern "C" {
+
+const char *tzb_last_error(void) { return tzb::g_lastError; }
+
+int tzb_boxcopy_static(const TzbBox *boxes, int nBoxes, int elemSize, uint64_t epoch, void *stream) {
+  using namespace tzb;
+  g_lastError[0] = 0;
+  if (!boxes || nBoxes <= 0) {
+    set_error("tzb_boxcopy_static: need at least one box");
+    return cudaErrorInvalidValue;
+  }
+  TzbBoxPlanInfo info;
+  int err = tzb_boxcopy_plan(boxes, nBoxes, elemSize, &info, nullptr);
+  if (err != cudaSuccess) {
+    set_error("tzb_boxcopy_static: invalid box description");
+    return err;
+  }
+  if (info.planBytes + kStaticCounterBytes > size_t(TZB_STATIC_SCRATCH_BYTES)) {
+    set_error("tzb_boxcopy_static: this copy needs %lld bytes of plan scratch but the built-in "
+              "array holds %lld; split the boxes over several calls or use tzb_boxcopy_launch",
+              (long long)info.planBytes, (long long)(TZB_STATIC_SCRATCH_BYTES - kStaticCounterBytes));
+    return cudaErrorInvalidValue;
+  }
+  if (info.nItems == 0) return cudaSuccess;
+  unsigned char *base = nullptr;
+  cudaError_t ce = static_scratch_address(&base);
+  if (ce != cudaSuccess) {
+    set_error("tzb_boxcopy_static: cudaGetSymbolAddress failed (%lld)", (long long)ce);
+    return ce;
+  }
+  // host image: host memory only; the device side is the built-in array
+  std::vector<char> image(info.planBytes);
+  err = tzb_boxcopy_plan(boxes, nBoxes, elemSize, &info, image.data());
+  if (err != cudaSuccess) return err;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  // the array still holds whatever the previous call left: the counter has to start at zero
+  ce = cudaMemsetAsync(base, 0, kStaticCounterBytes, s);
+  if (ce != cudaSuccess) return ce;
+  // pageable source: the runtime stages it before returning, so `image` may go out of scope
+  ce = cudaMemcpyAsync(base + kStaticCounterBytes, image.data(), info.planBytes,
+                       cudaMemcpyHostToDevice, s);
+  if (ce != cudaSuccess) return ce;
+  return tzb_boxcopy_launch(base + kStaticCounterBytes, &info, epoch, base, stream);
 }
 
 } // extern "C"
