@@ -1,5 +1,6 @@
 // Python bindings for the distributed SpMV workload.
 #include <pybind11/pybind11.h>
+#include "op_cast.hpp"
 #include <pybind11/stl.h>
 
 #include "tenzing/spmv/row_part_spmv.hpp"
@@ -75,7 +76,7 @@ template <typename Scalar> void bind_one(py::module_ &m, const char *suffix) {
                                              : SymmetricHeap::Memory::Device);
         },
         py::arg("comm"), py::arg("n"), py::arg("bw"), py::arg("nnz_per_row") = 10,
-        py::arg("seed") = 0, py::arg("host") = false);
+        py::arg("seed") = 0, py::arg("host") = false, py::call_guard<py::gil_scoped_release>());
   const std::string rows = std::string("random_band_rows") + suffix;
   m.def(rows.c_str(),
         [](int64_t n, int64_t bw, int nnzPerRow, int64_t rb, int64_t re, uint64_t seed) {

@@ -2,6 +2,7 @@
 // kernel entry points (used by the numerics tests).
 #include <pybind11/functional.h>
 #include <pybind11/pybind11.h>
+#include "op_cast.hpp"
 #include <pybind11/stl.h>
 
 #include "tenzing/halo/halo_exchange.hpp"
@@ -106,7 +107,8 @@ void bind_workloads(py::module_ &m) {
                                                     host ? SymmetricHeap::Memory::Host
                                                          : SymmetricHeap::Memory::Device);
            }),
-           py::arg("comm"), py::arg("bytes"), py::arg("host") = false)
+           py::arg("comm"), py::arg("bytes"), py::arg("host") = false,
+           py::call_guard<py::gil_scoped_release>()) // collective: other ranks may be threads
       .def("rank", &SymmetricHeap::rank)
       .def("size", &SymmetricHeap::size)
       .def("bytes", &SymmetricHeap::bytes)
@@ -145,7 +147,8 @@ void bind_workloads(py::module_ &m) {
                                              host ? SymmetricHeap::Memory::Host
                                                   : SymmetricHeap::Memory::Device);
            }),
-           py::arg("comm"), py::arg("args"), py::arg("host") = false)
+           py::arg("comm"), py::arg("args"), py::arg("host") = false,
+           py::call_guard<py::gil_scoped_release>())
       .def("rank", &Domain::rank)
       .def("size", &Domain::size)
       .def("extent", [](const Domain &d) { auto e = d.extent(); return std::vector<int>{e.x, e.y, e.z}; })

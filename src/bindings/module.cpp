@@ -6,6 +6,7 @@
 // (callables), a communicator (torch.distributed) and a benchmarker.
 #include <pybind11/functional.h>
 #include <pybind11/pybind11.h>
+#include "op_cast.hpp"
 #include <pybind11/stl.h>
 
 #include "tenzing/tenzing.hpp"
@@ -677,10 +678,10 @@ PYBIND11_MODULE(_C, m) {
       .def("children",
            [](mcts::Node &n) {
              py::list l;
+             // references into the tree: valid while the root object is alive
              for (auto &c : n.children_) l.append(py::cast(c.get(), py::return_value_policy::reference));
              return l;
-           },
-           py::keep_alive<0, 1>())
+           })
       .def("times", [](const mcts::Node &n) { return n.state_.times; })
       .def("size", &mcts::Node::size)
       .def("unvisited_size", &mcts::Node::unvisited_size)

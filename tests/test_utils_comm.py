@@ -1,0 +1,149 @@
+"""L0 utilities and control-plane communicators (no GPU)."""
+import json
+import math
+import multiprocessing as mp
+import os
+import random
+import subprocess
+import sys
+
+import pytest
+
+import tenzing_b200 as tz
+from tenzing_b200 import _C
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def test_numeric_helpers():
+    v = [3.0, 1.0, 2.0, 10.0]
+    assert _C.avg(v) == 4.0
+    assert _C.med(v) == 2.5 and _C.med([5.0, 1.0, 3.0]) == 3.0
+    assert _C.var(v) == pytest.approx(sum((x - 4.0) ** 2 for x in v) / 4)
+    assert _C.stddev(v) == pytest.approx(math.sqrt(_C.var(v)))
+    assert _C.corr([1, 2, 3, 4], [2, 4, 6, 8]) == pytest.approx(1.0)
+    assert _C.corr([1, 2, 3, 4], [8, 6, 4, 2]) == pytest.approx(-1.0)
+    assert _C.corr([1, 1, 1], [1, 2, 3]) == 0.0
+    assert _C.prime_factors(360) == [5, 3, 3, 2, 2, 2]
+    assert _C.prime_factors(8) == [2, 2, 2] and _C.prime_factors(1) == [] and _C.prime_factors(13) == [13]
+    assert _C.round_up(13, 8) == 16 and _C.round_up(16, 8) == 16
+
+
+def test_runs_test_accepts_noise_and_rejects_drift():
+    rng = random.Random(0)
+    noise = [rng.random() for _ in range(200)]
+    assert not _C.runs_test(noise)
+    drift = [i * 0.01 + rng.random() * 0.001 for i in range(200)]
+    assert _C.runs_test(drift)
+    assert _C.runs_test([1.0, 2.0, 3.0])  # too few samples: "does not apply" counts as reject
+    assert math.isnan(_C.runs_test_z([1.0, 2.0, 3.0]))
+    assert _C.runs_test_z(drift) > 1.96
+
+
+def test_reproduce_header_and_version():
+    h = json.loads(_C.reproduce_header(["prog", "-i", "3"]))
+    assert h["args"] == ["prog", "-i", "3"] and set(h) == {"args", "hash", "major", "minor", "patch"}
+    assert _C.version_string().startswith(f'{h["major"]}.{h["minor"]}.{h["patch"]}-')
+
+
+def test_bench_result_percentiles_follow_the_reference_index_rule():
+    s = [float(i) for i in range(100, 0, -1)]  # 100 samples, unsorted
+    r = tz.BenchResult.from_samples(s)
+    assert (r.pct01, r.pct10, r.pct50, r.pct90, r.pct99) == (2.0, 11.0, 51.0, 91.0, 100.0)
+    assert r.stddev == pytest.approx(_C.stddev(s))
+
+
+def test_partition_and_rank_grid_rules():
+    sp = _C.spmv
+    parts = [sp.get_partition(10, i, 4) for i in range(4)]
+    assert parts == [(0, 3), (3, 6), (6, 8), (8, 10)]  # remainder rows go to the low ranks
+    for i in range(10):
+        lo, hi = parts[sp.get_owner(10, i, 4)]
+        assert lo <= i < hi
+    assert _C.halo.rank_grid(8) == [2, 2, 2] and _C.halo.rank_grid(4) == [2, 2, 1]
+    assert _C.halo.rank_grid(6) == [3, 2, 1] and _C.halo.rank_grid(1) == [1, 1, 1]
+    assert _C.halo.dir_to_tag(-1, -1, -1) == 0 and _C.halo.dir_to_tag(1, 1, 1) == 26
+
+
+def test_empirical_benchmarker_on_null_platform_measures_host_ops():
+    import time
+    g = tz.Graph()
+    op = tz.PyCpuOp("sleepy", lambda: time.sleep(0.002))
+    g.start_then(op)
+    g.then_finish(op)
+    plat = tz.Platform.make_null(1)
+    seq = tz.dfs.get_all_sequences(g, plat)[0]
+    r = tz.EmpiricalBenchmarker().benchmark(
+        seq, plat, tz.BenchOpts(n_iters=5, max_retries=0, target_secs=0.004, check_randomness=False))
+    assert 0.0018 < r.pct50 < 0.01
+    assert plat.epoch() >= 5
+
+
+def test_loopback_world_collectives_and_lockstep_dfs():
+    """config 1 of BASELINE.json: the noop-graph DFS with a world of two (no MPI: two threads)"""
+    results = {}
+
+    def body(rank, comm):
+        assert comm.size() == 2 and comm.rank() == rank and comm.kind() == "loopback"
+        assert comm.bcast_string("hello" if rank == 0 else "", 0) == "hello"
+        assert comm.max_over_ranks(float(rank + 1)) == 2.0
+        parts = comm.allgather_bytes(bytes([rank]) * (rank + 1))
+        assert parts == [b"\x00", b"\x01\x01"]
+        g = tz.Graph()
+        op1 = tz.NoOp("op1")
+        g.start_then(op1)
+        g.then_finish(op1)
+        plat = tz.Platform.make_null(1, comm)
+        res = tz.dfs.explore(g, plat, tz.PyBenchmarker(lambda s: 1.0 + rank))
+        results[rank] = [r.seq.names() for r in res.sim_results]
+        comm.barrier()
+
+    _C.loopback_run(2, body)
+    assert results[0] == results[1] == [["Start", "op1", "Finish"]]
+
+
+def _socket_rank(rank, size, port, q):
+    os.environ["TENZING_ACK_NOTICE"] = "1"
+    import tenzing_b200 as tz2
+    from tenzing_b200 import _C as C
+    comm = C.SocketComm(rank, size, "127.0.0.1", port, 30.0)
+    out = [comm.bcast_string("x" * 1000 if rank == 1 else "", 1) == "x" * 1000,
+           comm.max_over_ranks(float(rank)) == float(size - 1),
+           comm.allgather_bytes(bytes([65 + rank])) == [bytes([65 + r]) for r in range(size)]]
+    comm.barrier()
+    # a search in lock step: rank 0 enumerates, every rank "benchmarks"
+    g = tz2.Graph()
+    a, b = tz2.NoOp("a"), tz2.NoOp("b")
+    for o in (a, b):
+        g.start_then(o)
+        g.then_finish(o)
+    plat = tz2.Platform.make_null(1, comm)
+    res = tz2.dfs.explore(g, plat, tz2.PyBenchmarker(lambda s: 1.0))
+    out.append(sorted(tuple(r.seq.names()) for r in res.sim_results) ==
+               [("Start", "a", "b", "Finish"), ("Start", "b", "a", "Finish")])
+    q.put((rank, out))
+
+
+def test_socket_comm_three_processes():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31000 + os.getpid() % 2000
+    procs = [ctx.Process(target=_socket_rank, args=(r, 3, port, q)) for r in range(3)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(all(v) for v in got.values()), got
+
+
+def test_gloo_world_of_two_runs_the_noop_dfs():
+    """same configuration through torch.distributed (gloo), launched like bench.py is"""
+    script = os.path.join(HERE, "gloo_worker.py")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+           "--master-addr", "127.0.0.1", "--master-port", str(29800 + os.getpid() % 100), script]
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="")
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env)
+    assert p.returncode == 0, (p.stdout + p.stderr)[-3000:]
+    assert "GLOO_WORKER_OK" in p.stdout, (p.stdout + p.stderr)[-3000:]
