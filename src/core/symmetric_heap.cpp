@@ -72,8 +72,11 @@ SymmetricHeap::SymmetricHeap(std::shared_ptr<Communicator> comm, size_t bytes, M
         }
       }
     } else {
-      if (memory_ == Memory::Host)
-        THROW_RUNTIME("SymmetricHeap: host memory mode needs all ranks in one process");
+      if (memory_ == Memory::Host) {
+        // dry-run across processes (no GPU): ops are no-ops in this mode and never
+        // dereference a peer pointer, so the peer base stays null
+        continue;
+      }
       if (h.hostId != mine.hostId) THROW_RUNTIME("SymmetricHeap: rank " << r << " is on another host");
       void *p = nullptr;
       CUDA_RUNTIME(cudaIpcOpenMemHandle(&p, h.handle, cudaIpcMemLazyEnablePeerAccess));
