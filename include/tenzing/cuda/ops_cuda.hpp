@@ -39,6 +39,11 @@ public:
     (void)plat;
     run(stream);
   }
+  // True for kernels whose real data dependency is a device-side flag published by ANOTHER
+  // rank (wait+unpack style ops).  Their graph predecessors on the GPU then only have to be
+  // ISSUED before them (sequence order), not completed, so the EventSynchronizer inserts no
+  // CudaEventRecord/CudaStreamWaitEvent for those edges and the kernels may overlap.
+  virtual bool issue_order_only() const { return false; }
 };
 using GpuOpPtr = std::shared_ptr<GpuOp>;
 

@@ -19,6 +19,14 @@
 //   Direct     put straight into the neighbour's ghost cells, one wait op
 //   FusedAll   one kernel for all direct puts, one wait for all of them
 //   FusedStaged one kernel packs+puts all regions, one kernel waits+unpacks all
+//   FusedGroups the same in three direction groups (x-related / y / z), so the unpack of one
+//              group can overlap the puts of the next
+//   FusedMixed regions with an x component (24-byte rows) go through staging so they cross
+//              NVLink as dense aligned bursts; all other regions (4 KB rows) are put straight
+//              into the neighbour's ghost cells and need no unpack
+//   FusedPipelined one put kernel that publishes every region's flag as soon as that region
+//              is complete and one unpack kernel that may run at the same time and follows
+//              region by region (thin regions first): transfer and unpack overlap
 #pragma once
 
 #include <array>
@@ -62,7 +70,7 @@ template <typename T> std::shared_ptr<T> cuda_make_shared(size_t n) {
 namespace HaloExchange {
 
 enum class StorageOrder { QXYZ, XYZQ };
-enum class Style { Reference, Staged, Direct, FusedAll, FusedStaged };
+enum class Style { Reference, Staged, Direct, FusedAll, FusedStaged, FusedGroups, FusedMixed, FusedPipelined };
 const char *style_name(Style s);
 
 // MPI-style message tag of a direction (reference: ops_halo_exchange.cu:16-27)
@@ -156,11 +164,16 @@ class BoxCopyOp : public GpuOp {
   std::string name_;
   std::shared_ptr<std::array<Plan, 2>> plans_; // shared between clones
   bool null_ = false;
+  bool issueOrderOnly_ = false;
 
 public:
   // boxes[parity]: the copies to perform when (epoch & 1) == parity
+  // ordered: boxes are processed in the given order and publish their flags one by one
   BoxCopyOp(const std::string &name, const std::vector<TzbBox> &even,
-            const std::vector<TzbBox> &odd, int elemSize, bool nullDevice = false);
+            const std::vector<TzbBox> &odd, int elemSize, bool nullDevice = false,
+            bool ordered = false);
+  void set_issue_order_only(bool v) { issueOrderOnly_ = v; }
+  bool issue_order_only() const override { return issueOrderOnly_; }
   std::string name() const override { return name_; }
   CLONE_DEF(BoxCopyOp)
   void run(cudaStream_t) override { THROW_RUNTIME("BoxCopyOp needs the platform epoch"); }
@@ -188,7 +201,10 @@ std::shared_ptr<ChoiceOp> make_choice(const std::shared_ptr<Domain> &dom,
                                                                           Style::Staged,
                                                                           Style::Direct,
                                                                           Style::FusedAll,
-                                                                          Style::FusedStaged});
+                                                                          Style::FusedStaged,
+                                                                          Style::FusedGroups,
+                                                                          Style::FusedMixed,
+                                                                          Style::FusedPipelined});
 
 } // namespace HaloExchange
 } // namespace tenzing

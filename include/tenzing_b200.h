@@ -92,7 +92,7 @@ typedef struct {
   int32_t nBoxes;
   int32_t nItems;
   int32_t elemSize;          /* 4 or 8 */
-  int32_t reserved;
+  int32_t reserved;          /* internal flags set by the plan functions */
   size_t planBytes;          /* size of the host/device image */
   size_t scratchBytes;       /* zeroed device scratch needed at launch (per-box counters) */
   size_t payloadBytes;       /* bytes moved per launch */
@@ -101,6 +101,11 @@ typedef struct {
 /* Pass hostImage == NULL to query sizes only. */
 int tzb_boxcopy_plan(const TzbBox *boxes, int nBoxes, int elemSize, TzbBoxPlanInfo *info,
                      void *hostImage);
+/* Same, but the boxes are worked through one after the other in the order given (instead of
+ * interleaved) and every box's flag is published as soon as that box is complete, so a consumer
+ * kernel running at the same time can start on early boxes while later ones are still in flight. */
+int tzb_boxcopy_plan_ordered(const TzbBox *boxes, int nBoxes, int elemSize, TzbBoxPlanInfo *info,
+                             void *hostImage);
 /* devPlan: device copy of the image. scratch: info.scratchBytes of zeroed device
  * memory (the kernel leaves it zeroed again). */
 int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t epoch,

@@ -70,6 +70,9 @@ PredInfo classify(const BoundOpPtr &pred, const BoundOpPtr &bo) {
     return r;
   }
   if (r.pGpu && bGpu) {
+    // a flag-driven consumer only needs its GPU predecessors issued earlier, which the
+    // sequence order already guarantees
+    if (std::static_pointer_cast<BoundGpuOp>(bo)->unbound()->issue_order_only()) return r;
     r.need = Need::GpuThenGpu;
     return r;
   }

@@ -71,9 +71,32 @@ box_copy_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restrict__ 
   __shared__ unsigned readyMask; // boxes whose wait flag this block has already seen
   if (threadIdx.x == 0) readyMask = 0;
   __syncthreads();
+  // ordered plans publish each box's flag as soon as the box is complete: a block counts the
+  // items it finished of the current box and hands the count in (one system-scope fence) when
+  // it moves on to another box
+  const bool perBox = (anySignal & 2) != 0;
+  int curBox = -1;
+  unsigned curCount = 0;
+  auto hand_in = [&](int box, unsigned n) {
+    __syncthreads(); // all threads' stores of these items are issued
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      const unsigned prev = atomicAdd(counter + 1 + box, n);
+      if (prev + n == unsigned(boxes[box].nItems)) {
+        counter[1 + box] = 0;
+        if (boxes[box].signal) st_release_sys(boxes[box].signal, epoch);
+      }
+    }
+  };
   for (int it = blockIdx.x; it < nItems; it += gridDim.x) {
     const WorkItem w = items[it];
     const BoxDesc &b = boxes[w.box];
+    if (perBox && w.box != curBox) {
+      if (curBox >= 0) hand_in(curBox, curCount);
+      curBox = w.box;
+      curCount = 0;
+    }
+    ++curCount;
     if (b.wait) {
       // the data of this box is only there once the producer published this epoch
       if (threadIdx.x == 0 && !((readyMask >> (w.box & 31)) & 1u)) {
@@ -91,6 +114,36 @@ box_copy_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restrict__ 
         const int j2 = r / w.c1, j1 = r - j2 * w.c1;
         const T *s = src + int64_t(w.i2 + j2) * b.s2 + int64_t(w.i1 + j1) * b.s1;
         T *d = dst + int64_t(w.i2 + j2) * b.d2 + int64_t(w.i1 + j1) * b.d1;
+        // 16-byte accesses on whichever side is 16-byte aligned (staging buffers always
+        // are; grid rows start at x = nGhost and usually are not): over NVLink a warp then
+        // stores 512 contiguous, aligned bytes instead of 256 that straddle sectors
+        const bool sVec = (reinterpret_cast<uintptr_t>(s) & 15) == 0;
+        const bool dVec = (reinterpret_cast<uintptr_t>(d) & 15) == 0;
+        if (sizeof(T) == 8 && (run & 1) == 0 && (sVec || dVec)) {
+          const int pairs = run >> 1;
+          constexpr int kPairs = kThick / 2;
+          int p = lane;
+          for (; p + 32 * (kPairs - 1) < pairs; p += 32 * kPairs) {
+            double2 v[kPairs];
+#pragma unroll
+            for (int u = 0; u < kPairs; ++u) {
+              const double *sp = reinterpret_cast<const double *>(s) + 2 * (p + 32 * u);
+              if (sVec) v[u] = __ldcs(reinterpret_cast<const double2 *>(sp));
+              else v[u] = make_double2(__ldcs(sp), __ldcs(sp + 1));
+            }
+#pragma unroll
+            for (int u = 0; u < kPairs; ++u) {
+              double *dp = reinterpret_cast<double *>(d) + 2 * (p + 32 * u);
+              if (dVec) *reinterpret_cast<double2 *>(dp) = v[u];
+              else dp[0] = v[u].x, dp[1] = v[u].y;
+            }
+          }
+          for (; p < pairs; p += 32) {
+            d[2 * p] = s[2 * p];
+            d[2 * p + 1] = s[2 * p + 1];
+          }
+          continue;
+        }
         int e = lane;
         for (; e + 32 * (kThick - 1) < run; e += 32 * kThick) {
           T v[kThick];
@@ -132,7 +185,9 @@ box_copy_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restrict__ 
       }
     }
   }
-  if (anySignal) {
+  if (perBox) {
+    if (curBox >= 0) hand_in(curBox, curCount);
+  } else if (anySignal) {
     // one system-scope fence per block; the last block to finish publishes every flag
     if (block_arrive_last(counter, gridDim.x)) {
       for (int bx = threadIdx.x; bx < nBoxes; bx += kThreads)
@@ -173,8 +228,8 @@ using namespace tzb;
 
 extern "C" {
 
-int tzb_boxcopy_plan(const TzbBox *boxes, int nBoxes, int elemSize, TzbBoxPlanInfo *info,
-                     void *hostImage) {
+static int boxcopy_plan_impl(const TzbBox *boxes, int nBoxes, int elemSize, TzbBoxPlanInfo *info,
+                             void *hostImage, bool ordered) {
   if (!info || nBoxes < 0 || (elemSize != 4 && elemSize != 8)) return cudaErrorInvalidValue;
   std::vector<BoxDesc> descs(nBoxes);
   std::vector<WorkItem> items;
@@ -234,7 +289,7 @@ int tzb_boxcopy_plan(const TzbBox *boxes, int nBoxes, int elemSize, TzbBoxPlanIn
   }
   // interleave the boxes' items so that concurrently running blocks touch
   // different regions (and different peers) instead of draining one box at a time
-  if (nBoxes > 1) {
+  if (nBoxes > 1 && !ordered) {
     std::vector<std::vector<WorkItem>> perBox(nBoxes);
     for (const WorkItem &w : items) perBox[w.box].push_back(w);
     std::vector<WorkItem> mixed;
@@ -254,11 +309,14 @@ int tzb_boxcopy_plan(const TzbBox *boxes, int nBoxes, int elemSize, TzbBoxPlanIn
   info->nBoxes = nBoxes;
   info->nItems = int(items.size());
   info->elemSize = elemSize;
-  info->reserved = 0; // becomes 1 if any box publishes a flag
-  for (int b = 0; b < nBoxes; ++b)
-    if (boxes[b].signal) info->reserved = 1;
+  info->reserved = 0; // bit 0: some box publishes a flag; bit 1: some box waits for one
+  for (int b = 0; b < nBoxes; ++b) {
+    if (boxes[b].signal) info->reserved |= 1;
+    if (boxes[b].wait) info->reserved |= 2;
+  }
+  if (ordered && (info->reserved & 1)) info->reserved |= 4; // publish per box
   info->planBytes = sizeof(PlanHeader) + sizeof(BoxDesc) * size_t(nBoxes) + sizeof(WorkItem) * items.size();
-  info->scratchBytes = 256; // one arrival counter (kept aligned)
+  info->scratchBytes = (sizeof(unsigned) * size_t(nBoxes + 1) + 255) / 256 * 256; // arrival counters
   info->payloadBytes = payload;
   if (hostImage) {
     char *p = static_cast<char *>(hostImage);
@@ -272,6 +330,16 @@ int tzb_boxcopy_plan(const TzbBox *boxes, int nBoxes, int elemSize, TzbBoxPlanIn
   return cudaSuccess;
 }
 
+int tzb_boxcopy_plan(const TzbBox *boxes, int nBoxes, int elemSize, TzbBoxPlanInfo *info,
+                     void *hostImage) {
+  return boxcopy_plan_impl(boxes, nBoxes, elemSize, info, hostImage, false);
+}
+
+int tzb_boxcopy_plan_ordered(const TzbBox *boxes, int nBoxes, int elemSize, TzbBoxPlanInfo *info,
+                             void *hostImage) {
+  return boxcopy_plan_impl(boxes, nBoxes, elemSize, info, hostImage, true);
+}
+
 int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t epoch,
                        void *scratch, void *stream) {
   if (!devPlan || !info) return cudaErrorInvalidValue;
@@ -280,10 +348,15 @@ int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t
   const BoxDesc *boxes = reinterpret_cast<const BoxDesc *>(p);
   const WorkItem *items =
       reinterpret_cast<const WorkItem *>(p + sizeof(BoxDesc) * size_t(info->nBoxes));
-  const int blocks = std::min(info->nItems, kSMs * kBlocksPerSM);
+  // a kernel that may spin on flags never takes more than half of an SM's block slots, so a
+  // producer kernel launched from another stream can always become resident next to it
+  // (ordered plans are meant to run beside their consumer kernel and share the SMs with it)
+  const bool waits = (info->reserved & 2) != 0, ordered = (info->reserved & 4) != 0;
+  const int blocks =
+      std::min(info->nItems, kSMs * ((waits || ordered) ? kBlocksPerSM / 2 : kBlocksPerSM));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   ++g_launches;
-  const int anySignal = info->reserved;
+  const int anySignal = (info->reserved & 1) | ((info->reserved & 4) ? 2 : 0);
   if (info->elemSize == 8)
     box_copy_kernel<double><<<blocks, kThreads, 0, s>>>(boxes, items, info->nItems, info->nBoxes,
                                                         anySignal, epoch,
@@ -337,11 +410,11 @@ int tzb_copy_bytes(void *dst, const void *src, size_t bytes, void *stream) {
 namespace tzb {
 namespace {
 
-// layout: [0, 256) arrival counter (must be zero at kernel start), [256, ...) plan image
+// layout: [0, 4096) arrival counters (must be zero at kernel start), [4096, ...) plan image
 static __device__ __align__(256) unsigned char g_static_scratch[TZB_STATIC_SCRATCH_BYTES];
 
 constexpr int kMaxDevices = 64;
-constexpr size_t kStaticCounterBytes = 256;
+constexpr size_t kStaticCounterBytes = 4096; // arrival counters: up to 1023 boxes
 
 struct StaticScratch {
   std::atomic<unsigned char *> ptr[kMaxDevices];
@@ -394,6 +467,11 @@ int tzb_boxcopy_static(const TzbBox *boxes, int nBoxes, int elemSize, uint64_t e
   if (err != cudaSuccess) {
     set_error("tzb_boxcopy_static: invalid box description");
     return err;
+  }
+  if (info.scratchBytes > kStaticCounterBytes) {
+    set_error("tzb_boxcopy_static: %lld boxes need more counters than the built-in array keeps (%lld)",
+              (long long)nBoxes, (long long)(kStaticCounterBytes / sizeof(unsigned) - 1));
+    return cudaErrorInvalidValue;
   }
   if (info.planBytes + kStaticCounterBytes > size_t(TZB_STATIC_SCRATCH_BYTES)) {
     set_error("tzb_boxcopy_static: this copy needs %lld bytes of plan scratch but the built-in "

@@ -55,9 +55,9 @@ cudaError_t launch_spmv(int rows, const int *rowPtr, const int *colInd, const T 
                         int nnzPerRowHint, cudaStream_t stream) {
   if (rows <= 0) return cudaSuccess;
   if (WAIT && nFlags > kThreads) return cudaErrorInvalidValue;
-  // lanes per row ~ nnz per row (rounded to a power of two, 2..32)
+  // lanes per row: the largest power of two not above nnz per row (2..32), so few lanes idle
   int tpr = 2;
-  while (tpr < 32 && tpr < nnzPerRowHint) tpr *= 2;
+  while (tpr < 32 && tpr * 2 <= nnzPerRowHint) tpr *= 2;
   const int groupsPerBlock = kThreads / tpr;
   int blocks = (rows + groupsPerBlock - 1) / groupsPerBlock;
   const int maxBlocks = kSMs * 8; // 8 x 256 threads = full occupancy, grid-stride beyond

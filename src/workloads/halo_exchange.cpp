@@ -19,6 +19,9 @@ const char *style_name(Style s) {
   case Style::Direct: return "direct";
   case Style::FusedAll: return "fused_all";
   case Style::FusedStaged: return "fused_staged";
+  case Style::FusedGroups: return "fused_groups";
+  case Style::FusedMixed: return "fused_mixed";
+  case Style::FusedPipelined: return "fused_pipelined";
   }
   return "?";
 }
@@ -66,7 +69,7 @@ void Args::set_default_topology(int size) {
 
 // ---------------------------------------------------------------- Domain
 namespace {
-constexpr int kNumStyles = 5;
+constexpr int kNumStyles = 8;
 size_t round_up_sz(size_t v, size_t a) { return (v + a - 1) / a * a; }
 } // namespace
 
@@ -181,8 +184,9 @@ uint64_t *Domain::flag(int rank, Style style, const Dim3<int> &side) const {
 
 // ---------------------------------------------------------------- BoxCopyOp
 BoxCopyOp::BoxCopyOp(const std::string &name, const std::vector<TzbBox> &even,
-                     const std::vector<TzbBox> &odd, int elemSize, bool nullDevice)
+                     const std::vector<TzbBox> &odd, int elemSize, bool nullDevice, bool ordered)
     : name_(name), plans_(std::make_shared<std::array<Plan, 2>>()), null_(nullDevice) {
+  auto make_plan = ordered ? tzb_boxcopy_plan_ordered : tzb_boxcopy_plan;
   const std::vector<TzbBox> *lists[2] = {&even, &odd};
   for (int p = 0; p < 2; ++p) {
     Plan &plan = (*plans_)[size_t(p)];
@@ -192,11 +196,10 @@ BoxCopyOp::BoxCopyOp(const std::string &name, const std::vector<TzbBox> &even,
       plan = (*plans_)[0]; // parity-independent op: share one plan
       continue;
     }
-    CUDA_RUNTIME(cudaError_t(
-        tzb_boxcopy_plan(boxes.data(), int(boxes.size()), elemSize, &plan.info, nullptr)));
+    CUDA_RUNTIME(cudaError_t(make_plan(boxes.data(), int(boxes.size()), elemSize, &plan.info, nullptr)));
     std::vector<char> image(plan.info.planBytes);
     CUDA_RUNTIME(cudaError_t(
-        tzb_boxcopy_plan(boxes.data(), int(boxes.size()), elemSize, &plan.info, image.data())));
+        make_plan(boxes.data(), int(boxes.size()), elemSize, &plan.info, image.data())));
     if (null_) continue;
     void *dev = nullptr, *scratch = nullptr;
     CUDA_RUNTIME(cudaMalloc(&dev, plan.info.planBytes));
@@ -507,6 +510,90 @@ void add_to_graph(Graph<OpBase> &g, const std::shared_ptr<Domain> &dom,
     connect(g, preds, putOp);
     g.add_edge(putOp, finOp);
     connect(g, finOp, succs);
+    return;
+  }
+  if (style == Style::FusedGroups) {
+    // group 0: every direction with an x component (thin rows), 1: y faces and yz edges, 2: z faces
+    auto group_of = [](const Dim3<int> &d) { return d.x != 0 ? 0 : (d.y != 0 ? 1 : 2); };
+    const char *gname[3] = {"x", "y", "z"};
+    for (int grp = 0; grp < 3; ++grp) {
+      std::vector<TzbBox> put[2], fin[2];
+      for (int p = 0; p < 2; ++p)
+        for (const auto &d : dirs) {
+          if (group_of(d) != grp) continue;
+          put[p].push_back(b.packput_box(d, p, style));
+          fin[p].push_back(b.waitunpack_box(d, p, style));
+        }
+      if (put[0].empty()) continue;
+      OpPtr putOp = b.op(std::string("he_packput_") + gname[grp], put[0], put[1]);
+      OpPtr finOp = b.op(std::string("he_waitunpack_") + gname[grp], fin[0], fin[1]);
+      connect(g, preds, putOp);
+      // only its own puts precede a group's unpack: the wait kernels leave half of every SM
+      // free (see tzb_boxcopy_launch), so a later put can always run beside a spinning unpack
+      g.add_edge(putOp, finOp);
+      connect(g, finOp, succs);
+    }
+    return;
+  }
+  if (style == Style::FusedMixed) {
+    std::vector<TzbBox> thinPut[2], thinFin[2], thick;
+    std::vector<const uint64_t *> thickFlags;
+    for (const auto &d : dirs) {
+      if (d.x != 0) {
+        for (int p = 0; p < 2; ++p) {
+          thinPut[p].push_back(b.packput_box(d, p, style));
+          thinFin[p].push_back(b.waitunpack_box(d, p, style));
+        }
+      } else {
+        TzbBox box = b.direct_box(d);
+        box.signal = dom->flag(dom->neighbor(d), style, -d);
+        thick.push_back(box);
+      }
+    }
+    // completion of the direct puts: a box-copy plan of empty boxes that only wait
+    std::vector<TzbBox> thickWait;
+    for (const auto &d : dirs) {
+      if (d.x != 0) continue;
+      TzbBox w;
+      std::memset(&w, 0, sizeof(w));
+      w.wait = dom->flag(dom->rank(), style, d);
+      thickWait.push_back(w);
+    }
+    OpPtr putThin = b.op("he_packput_thin", thinPut[0], thinPut[1]);
+    OpPtr finThin = b.op("he_waitunpack_thin", thinFin[0], thinFin[1]);
+    connect(g, preds, putThin);
+    g.add_edge(putThin, finThin);
+    connect(g, finThin, succs);
+    if (!thick.empty()) {
+      OpPtr putThick = b.op("he_put_thick", thick);
+      OpPtr finThick = b.op("he_wait_thick", thickWait);
+      connect(g, preds, putThick);
+      g.add_edge(putThick, finThick);
+      connect(g, finThick, succs);
+    }
+    return;
+  }
+  if (style == Style::FusedPipelined) {
+    // thin regions first: their unpack is the slow part, so it gets the longest overlap
+    std::vector<Dim3<int>> order;
+    for (const auto &d : dirs)
+      if (d.x != 0) order.push_back(d);
+    for (const auto &d : dirs)
+      if (d.x == 0) order.push_back(d);
+    std::vector<TzbBox> put[2], fin[2];
+    for (int p = 0; p < 2; ++p)
+      for (const auto &d : order) {
+        put[p].push_back(b.packput_box(d, p, style));
+        // the neighbour on side e sends the region it calls -e: follow the PUT order
+        fin[p].push_back(b.waitunpack_box(-d, p, style));
+      }
+    auto putOp = std::make_shared<BoxCopyOp>("he_packput_pipe", put[0], put[1], b.es, b.null, true);
+    auto finOp = std::make_shared<BoxCopyOp>("he_waitunpack_pipe", fin[0], fin[1], b.es, b.null, true);
+    finOp->set_issue_order_only(true);
+    connect(g, preds, OpPtr(putOp));
+    g.add_edge(OpPtr(putOp), OpPtr(finOp)); // issue order only: the kernels may overlap
+    connect(g, OpPtr(putOp), succs);
+    connect(g, OpPtr(finOp), succs);
     return;
   }
   THROW_RUNTIME("unknown halo style");
