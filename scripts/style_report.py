@@ -78,7 +78,7 @@ def main():
         us, ok, n = measure(halo, style)
         rows.append(dict(workload=f"halo {args.nx}^3 nQ={args.nq}", style=style, us=round(us, 2), ok=ok,
                          ops=n, n_gpus=world, bytes_out=halo.bytes_per_exchange()))
-        if args.search_iters and style in ("fused_groups", "staged", "fused_staged", "fused_mixed"):
+        if args.search_iters and style in ("fused_groups", "staged", "fused_staged", "fused_mixed", "fused_pipelined"):
             res = halo.search("mcts", style=style, iters=args.search_iters, strategy="FastMin",
                               bench=common.bench_opts(n_iters=3, target_secs=0.002, max_retries=0,
                                                       check_randomness=False))

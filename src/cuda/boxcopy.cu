@@ -33,8 +33,7 @@ constexpr int kBlocksPerSM = 4;
 // workload yields several items per resident block, large enough to amortise
 // the per-item bookkeeping
 constexpr int64_t kItemBytes = 32 * 1024;
-constexpr int kThick = 8; // 8-byte loads in flight per lane, thick rows
-constexpr int kThin = 8;  // and for thin rows
+constexpr int kThin = 8; // elements per thread in flight, thin rows (also the item quantum)
 
 struct alignas(16) BoxDesc {
   const char *src;
@@ -63,63 +62,25 @@ struct PlanHeader {
 // (thick rows: one warp per row; thin rows: lanes run over (row, element)
 // pairs so the dense side of a pack/unpack stays fully coalesced).
 
-template <typename T>
-__global__ void __launch_bounds__(kThreads, kBlocksPerSM)
-box_copy_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restrict__ items, int nItems,
-                int nBoxes, int anySignal, uint64_t epoch, unsigned *counter) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  __shared__ unsigned readyMask; // boxes whose wait flag this block has already seen
-  if (threadIdx.x == 0) readyMask = 0;
-  __syncthreads();
-  // ordered plans publish each box's flag as soon as the box is complete: a block counts the
-  // items it finished of the current box and hands the count in (one system-scope fence) when
-  // it moves on to another box
-  const bool perBox = (anySignal & 2) != 0;
-  int curBox = -1;
-  unsigned curCount = 0;
-  auto hand_in = [&](int box, unsigned n) {
-    __syncthreads(); // all threads' stores of these items are issued
-    if (threadIdx.x == 0) {
-      __threadfence_system();
-      const unsigned prev = atomicAdd(counter + 1 + box, n);
-      if (prev + n == unsigned(boxes[box].nItems)) {
-        counter[1 + box] = 0;
-        if (boxes[box].signal) st_release_sys(boxes[box].signal, epoch);
-      }
-    }
-  };
-  for (int it = blockIdx.x; it < nItems; it += gridDim.x) {
-    const WorkItem w = items[it];
-    const BoxDesc &b = boxes[w.box];
-    if (perBox && w.box != curBox) {
-      if (curBox >= 0) hand_in(curBox, curCount);
-      curBox = w.box;
-      curCount = 0;
-    }
-    ++curCount;
-    if (b.wait) {
-      // the data of this box is only there once the producer published this epoch
-      if (threadIdx.x == 0 && !((readyMask >> (w.box & 31)) & 1u)) {
-        wait_flag_geq(b.wait, epoch);
-        if (w.box < 32) readyMask |= 1u << w.box;
-      }
-      __syncthreads();
-    }
-    const T *src = reinterpret_cast<const T *>(b.src) + int64_t(w.i3) * b.s3;
-    T *dst = reinterpret_cast<T *>(b.dst) + int64_t(w.i3) * b.d3;
-    const int run = b.run;
-    const int rows = w.c1 * w.c2;
-    if (run >= 64) {
-      for (int r = warp; r < rows; r += kWarps) {
-        const int j2 = r / w.c1, j1 = r - j2 * w.c1;
-        const T *s = src + int64_t(w.i2 + j2) * b.s2 + int64_t(w.i1 + j1) * b.s1;
-        T *d = dst + int64_t(w.i2 + j2) * b.d2 + int64_t(w.i1 + j1) * b.d1;
-        // 16-byte accesses on whichever side is 16-byte aligned (staging buffers always
-        // are; grid rows start at x = nGhost and usually are not): over NVLink a warp then
-        // stores 512 contiguous, aligned bytes instead of 256 that straddle sectors
+// one work item: rows [i1, i1+c1) x [i2, i2+c2) of plane i3
+template <typename T, bool VEC, int kThick, int kThin>
+__device__ __forceinline__ void copy_item(const BoxDesc &b, const WorkItem &w, int lane, int warp) {
+  const T *src = reinterpret_cast<const T *>(b.src) + int64_t(w.i3) * b.s3;
+  T *dst = reinterpret_cast<T *>(b.dst) + int64_t(w.i3) * b.d3;
+  const int run = b.run;
+  const int rows = w.c1 * w.c2;
+  if (run >= 64) {
+    for (int r = warp; r < rows; r += kWarps) {
+      const int j2 = r / w.c1, j1 = r - j2 * w.c1;
+      const T *s = src + int64_t(w.i2 + j2) * b.s2 + int64_t(w.i1 + j1) * b.s1;
+      T *d = dst + int64_t(w.i2 + j2) * b.d2 + int64_t(w.i1 + j1) * b.d1;
+      if (VEC && sizeof(T) == 8) {
+        // 16-byte accesses on whichever side is 16-byte aligned (staging buffers always are;
+        // grid rows start at x = nGhost and usually are not): over NVLink a warp then stores
+        // 512 contiguous, aligned bytes instead of 256 that straddle sectors
         const bool sVec = (reinterpret_cast<uintptr_t>(s) & 15) == 0;
         const bool dVec = (reinterpret_cast<uintptr_t>(d) & 15) == 0;
-        if (sizeof(T) == 8 && (run & 1) == 0 && (sVec || dVec)) {
+        if ((run & 1) == 0 && (sVec || dVec)) {
           const int pairs = run >> 1;
           constexpr int kPairs = kThick / 2;
           int p = lane;
@@ -144,51 +105,125 @@ box_copy_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restrict__ 
           }
           continue;
         }
-        int e = lane;
-        for (; e + 32 * (kThick - 1) < run; e += 32 * kThick) {
-          T v[kThick];
-#pragma unroll
-          for (int u = 0; u < kThick; ++u) v[u] = __ldcs(s + e + 32 * u);
-#pragma unroll
-          for (int u = 0; u < kThick; ++u) d[e + 32 * u] = v[u];
-        }
-        for (; e < run; e += 32) d[e] = s[e];
       }
-    } else {
-      // the plan sizes thin items to a multiple of kThreads * kThin elements where it
-      // can, so the scalar tail below is the exception
-      const int total = rows * run;
-      const int c1 = w.c1;
-      auto offsets = [&](int f, int64_t &so, int64_t &dof) {
-        const int r = f / run, e = f - r * run;
-        const int j2 = r / c1, j1 = r - j2 * c1;
-        so = int64_t(w.i2 + j2) * b.s2 + int64_t(w.i1 + j1) * b.s1 + e;
-        dof = int64_t(w.i2 + j2) * b.d2 + int64_t(w.i1 + j1) * b.d1 + e;
-      };
-      int f = threadIdx.x;
-      for (; f + kThreads * (kThin - 1) < total; f += kThreads * kThin) {
-        T v[kThin];
-        int64_t dof[kThin];
+      int e = lane;
+      for (; e + 32 * (kThick - 1) < run; e += 32 * kThick) {
+        T v[kThick];
 #pragma unroll
-        for (int u = 0; u < kThin; ++u) {
-          int64_t so;
-          offsets(f + kThreads * u, so, dof[u]);
-          v[u] = src[so];
-        }
+        for (int u = 0; u < kThick; ++u) v[u] = __ldcs(s + e + 32 * u);
 #pragma unroll
-        for (int u = 0; u < kThin; ++u) dst[dof[u]] = v[u];
+        for (int u = 0; u < kThick; ++u) d[e + 32 * u] = v[u];
       }
-      for (; f < total; f += kThreads) {
-        int64_t so, dof;
-        offsets(f, so, dof);
-        dst[dof] = src[so];
+      for (; e < run; e += 32) d[e] = s[e];
+    }
+  } else {
+    // the plan sizes thin items to a multiple of kThreads * kThin elements where it can, so
+    // the scalar tail below is the exception
+    const int total = rows * run;
+    const int c1 = w.c1;
+    auto offsets = [&](int f, int64_t &so, int64_t &dof) {
+      const int r = f / run, e = f - r * run;
+      const int j2 = r / c1, j1 = r - j2 * c1;
+      so = int64_t(w.i2 + j2) * b.s2 + int64_t(w.i1 + j1) * b.s1 + e;
+      dof = int64_t(w.i2 + j2) * b.d2 + int64_t(w.i1 + j1) * b.d1 + e;
+    };
+    int f = threadIdx.x;
+    for (; f + kThreads * (kThin - 1) < total; f += kThreads * kThin) {
+      T v[kThin];
+      int64_t dof[kThin];
+#pragma unroll
+      for (int u = 0; u < kThin; ++u) {
+        int64_t so;
+        offsets(f + kThreads * u, so, dof[u]);
+        v[u] = src[so];
       }
+#pragma unroll
+      for (int u = 0; u < kThin; ++u) dst[dof[u]] = v[u];
+    }
+    for (; f < total; f += kThreads) {
+      int64_t so, dof;
+      offsets(f, so, dof);
+      dst[dof] = src[so];
     }
   }
-  if (perBox) {
+}
+
+// Memory-level parallelism is what these kernels live on: the regions are far larger than L2
+// reuse could help and every byte is touched once, so each lane keeps kThick/kThin
+// independent 8-byte loads in flight before the first store (thick rows: one warp per row;
+// thin rows: lanes run over (row, element) pairs so the dense side of a pack/unpack stays
+// fully coalesced).
+//
+// Full-occupancy variant: no flag waits, flags (if any) published once by the last block.
+template <typename T, bool VEC>
+__global__ void __launch_bounds__(kThreads, kBlocksPerSM)
+box_copy_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restrict__ items, int nItems,
+                int nBoxes, int anySignal, uint64_t epoch, unsigned *counter) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int it = blockIdx.x; it < nItems; it += gridDim.x) {
+    const WorkItem w = items[it];
+    copy_item<T, VEC, 8, kThin>(boxes[w.box], w, lane, warp);
+  }
+  if (anySignal) {
+    // one system-scope fence per block; the last block to finish publishes every flag
+    if (block_arrive_last(counter, gridDim.x)) {
+      for (int bx = threadIdx.x; bx < nBoxes; bx += kThreads)
+        if (boxes[bx].signal) st_release_sys(boxes[bx].signal, epoch);
+    }
+  }
+}
+
+// Synchronising variant: waits for region flags, and for ordered plans publishes each region's
+// flag as soon as that region is complete - a block counts the items it finished of the current
+// region and hands the count in (one system-scope fence) when it moves on to another region.
+// Ordered plans run at half occupancy (MIN_BLOCKS = 2, grid of 2 blocks per SM) so that the
+// partner kernel they are meant to overlap with always fits beside them.
+template <typename T, int MIN_BLOCKS>
+__global__ void __launch_bounds__(kThreads, MIN_BLOCKS)
+box_copy_sync_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restrict__ items,
+                     int nItems, int nBoxes, int anySignal, uint64_t epoch, unsigned *counter) {
+  constexpr bool kPerBox = MIN_BLOCKS < kBlocksPerSM; // the ordered (half-occupancy) variant
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __shared__ unsigned readyMask; // boxes whose wait flag this block has already seen
+  if (threadIdx.x == 0) readyMask = 0;
+  __syncthreads();
+  int curBox = -1;
+  unsigned curCount = 0;
+  auto hand_in = [&](int box, unsigned n) {
+    __syncthreads(); // all threads' stores of these items are issued
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      const unsigned prev = atomicAdd(counter + 1 + box, n);
+      if (prev + n == unsigned(boxes[box].nItems)) {
+        counter[1 + box] = 0;
+        if (boxes[box].signal) st_release_sys(boxes[box].signal, epoch);
+      }
+    }
+  };
+  for (int it = blockIdx.x; it < nItems; it += gridDim.x) {
+    const WorkItem w = items[it];
+    const BoxDesc &b = boxes[w.box];
+    if (kPerBox) {
+      if (w.box != curBox) {
+        if (curBox >= 0) hand_in(curBox, curCount);
+        curBox = w.box;
+        curCount = 0;
+      }
+      ++curCount;
+    }
+    if (b.wait) {
+      // the data of this box is only there once the producer published this epoch
+      if (threadIdx.x == 0 && !((readyMask >> (w.box & 31)) & 1u)) {
+        wait_flag_geq(b.wait, epoch);
+        if (w.box < 32) readyMask |= 1u << w.box;
+      }
+      __syncthreads();
+    }
+    copy_item<T, true, 8, kThin>(b, w, lane, warp);
+  }
+  if (kPerBox) {
     if (curBox >= 0) hand_in(curBox, curCount);
   } else if (anySignal) {
-    // one system-scope fence per block; the last block to finish publishes every flag
     if (block_arrive_last(counter, gridDim.x)) {
       for (int bx = threadIdx.x; bx < nBoxes; bx += kThreads)
         if (boxes[bx].signal) st_release_sys(boxes[bx].signal, epoch);
@@ -314,7 +349,15 @@ static int boxcopy_plan_impl(const TzbBox *boxes, int nBoxes, int elemSize, TzbB
     if (boxes[b].signal) info->reserved |= 1;
     if (boxes[b].wait) info->reserved |= 2;
   }
-  if (ordered && (info->reserved & 1)) info->reserved |= 4; // publish per box
+  if (ordered) info->reserved |= 4; // publish per box, share the SMs with a partner kernel
+  for (int b = 0; b < nBoxes; ++b) { // some thick box has a 16-byte aligned side: use the vector variant
+    const TzbBox &in = boxes[b];
+    if (elemSize != 8 || in.run < 64 || (in.run & 1)) continue;
+    auto aligned = [&](const void *p, int64_t s1, int64_t s2, int64_t s3) {
+      return (reinterpret_cast<uintptr_t>(p) & 15) == 0 && (s1 & 1) == 0 && (s2 & 1) == 0 && (s3 & 1) == 0;
+    };
+    if (aligned(in.src, in.s1, in.s2, in.s3) || aligned(in.dst, in.d1, in.d2, in.d3)) info->reserved |= 8;
+  }
   info->planBytes = sizeof(PlanHeader) + sizeof(BoxDesc) * size_t(nBoxes) + sizeof(WorkItem) * items.size();
   info->scratchBytes = (sizeof(unsigned) * size_t(nBoxes + 1) + 255) / 256 * 256; // arrival counters
   info->payloadBytes = payload;
@@ -348,23 +391,44 @@ int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t
   const BoxDesc *boxes = reinterpret_cast<const BoxDesc *>(p);
   const WorkItem *items =
       reinterpret_cast<const WorkItem *>(p + sizeof(BoxDesc) * size_t(info->nBoxes));
-  // a kernel that may spin on flags never takes more than half of an SM's block slots, so a
-  // producer kernel launched from another stream can always become resident next to it
-  // (ordered plans are meant to run beside their consumer kernel and share the SMs with it)
+  // ordered plans are meant to run beside a partner kernel (a put beside the unpack that follows
+  // it region by region): they never take more than half of an SM's block slots, so the partner
+  // launched from another stream can always become resident next to them
   const bool waits = (info->reserved & 2) != 0, ordered = (info->reserved & 4) != 0;
-  const int blocks =
-      std::min(info->nItems, kSMs * ((waits || ordered) ? kBlocksPerSM / 2 : kBlocksPerSM));
+  const bool vec = (info->reserved & 8) != 0;
+  const int anySignal = info->reserved & 1;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  unsigned *ctr = static_cast<unsigned *>(scratch);
   ++g_launches;
-  const int anySignal = (info->reserved & 1) | ((info->reserved & 4) ? 2 : 0);
-  if (info->elemSize == 8)
-    box_copy_kernel<double><<<blocks, kThreads, 0, s>>>(boxes, items, info->nItems, info->nBoxes,
-                                                        anySignal, epoch,
-                                                        static_cast<unsigned *>(scratch));
-  else
-    box_copy_kernel<float><<<blocks, kThreads, 0, s>>>(boxes, items, info->nItems, info->nBoxes,
-                                                       anySignal, epoch,
-                                                       static_cast<unsigned *>(scratch));
+  if (ordered) {
+    const int blocks = std::min(info->nItems, kSMs * (kBlocksPerSM / 2));
+    if (info->elemSize == 8)
+      box_copy_sync_kernel<double, kBlocksPerSM / 2><<<blocks, kThreads, 0, s>>>(
+          boxes, items, info->nItems, info->nBoxes, anySignal, epoch, ctr);
+    else
+      box_copy_sync_kernel<float, kBlocksPerSM / 2><<<blocks, kThreads, 0, s>>>(
+          boxes, items, info->nItems, info->nBoxes, anySignal, epoch, ctr);
+  } else if (waits) {
+    // strictly ordered after the local producers (graph edge): full occupancy is safe
+    const int blocks = std::min(info->nItems, kSMs * kBlocksPerSM);
+    if (info->elemSize == 8)
+      box_copy_sync_kernel<double, kBlocksPerSM><<<blocks, kThreads, 0, s>>>(
+          boxes, items, info->nItems, info->nBoxes, anySignal, epoch, ctr);
+    else
+      box_copy_sync_kernel<float, kBlocksPerSM><<<blocks, kThreads, 0, s>>>(
+          boxes, items, info->nItems, info->nBoxes, anySignal, epoch, ctr);
+  } else {
+    const int blocks = std::min(info->nItems, kSMs * kBlocksPerSM);
+    if (info->elemSize == 8 && vec)
+      box_copy_kernel<double, true><<<blocks, kThreads, 0, s>>>(boxes, items, info->nItems,
+                                                                info->nBoxes, anySignal, epoch, ctr);
+    else if (info->elemSize == 8)
+      box_copy_kernel<double, false><<<blocks, kThreads, 0, s>>>(boxes, items, info->nItems,
+                                                                 info->nBoxes, anySignal, epoch, ctr);
+    else
+      box_copy_kernel<float, false><<<blocks, kThreads, 0, s>>>(boxes, items, info->nItems,
+                                                                info->nBoxes, anySignal, epoch, ctr);
+  }
   return cudaGetLastError();
 }
 

@@ -525,11 +525,14 @@ void add_to_graph(Graph<OpBase> &g, const std::shared_ptr<Domain> &dom,
           fin[p].push_back(b.waitunpack_box(d, p, style));
         }
       if (put[0].empty()) continue;
-      OpPtr putOp = b.op(std::string("he_packput_") + gname[grp], put[0], put[1]);
-      OpPtr finOp = b.op(std::string("he_waitunpack_") + gname[grp], fin[0], fin[1]);
+      // ordered plans: these kernels run beside each other and must share the SMs
+      OpPtr putOp = std::make_shared<BoxCopyOp>(std::string("he_packput_") + gname[grp], put[0], put[1],
+                                                b.es, b.null, true);
+      OpPtr finOp = std::make_shared<BoxCopyOp>(std::string("he_waitunpack_") + gname[grp], fin[0],
+                                                fin[1], b.es, b.null, true);
       connect(g, preds, putOp);
-      // only its own puts precede a group's unpack: the wait kernels leave half of every SM
-      // free (see tzb_boxcopy_launch), so a later put can always run beside a spinning unpack
+      // only its own puts precede a group's unpack: ordered plans leave half of every SM free
+      // (see tzb_boxcopy_launch), so a later put can always run beside a spinning unpack
       g.add_edge(putOp, finOp);
       connect(g, finOp, succs);
     }

@@ -134,6 +134,18 @@ class HaloExchange:
     def bytes_per_exchange(self):
         return self.domain.bytes_per_exchange()
 
+    def remote_bytes_per_exchange(self):
+        """bytes that leave this GPU per exchange (regions whose neighbour is another rank)"""
+        a = self.args
+        g = a.nGhost
+        es = a.elemSize
+        total = 0
+        for dx, dy, dz in self.domain.dirs():
+            if self.domain.neighbor(dx, dy, dz) == self.rank:
+                continue
+            total += (g if dx else a.nX) * (g if dy else a.nY) * (g if dz else a.nZ) * a.nQ * es
+        return total
+
     # ---- running ----
     def run(self, seq, n=1):
         self.platform.provision_events(seq)

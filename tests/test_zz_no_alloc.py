@@ -119,18 +119,26 @@ def test_static_scratch_entry_matches_allocating_entry(lib, dtype):
 
 def test_static_scratch_entry_rejects_oversized_plans(lib):
     stream = torch.cuda.current_stream().cuda_stream
-    # many tiny boxes: ~96 B of plan each, so 4000 of them cannot fit into 256 KB
-    n = 4000
-    src = torch.zeros(n * 4, dtype=torch.float64, device="cuda")
-    dst = torch.zeros(n * 4, dtype=torch.float64, device="cuda")
-    arr = (TzbBox * n)()
-    for i in range(n):
-        arr[i] = TzbBox(src=src.data_ptr() + 32 * i, dst=dst.data_ptr() + 32 * i, s1=4, s2=4, s3=4,
-                        d1=4, d2=4, d3=4, n1=1, n2=1, n3=1, run=4, signal=None, wait=None)
-    rc = lib.tzb_boxcopy_static(arr, n, 8, 1, stream)
+    src = torch.zeros(16, dtype=torch.float64, device="cuda")
+    dst = torch.zeros(16, dtype=torch.float64, device="cuda")
+    # a 400 MB copy needs ~12500 work items of 24 B each: more than the 252 KB the built-in
+    # array leaves for the plan.  It is refused before anything is launched, so the (too
+    # small) buffers behind the pointers are never touched.
+    big = (TzbBox * 1)(TzbBox(src=src.data_ptr(), dst=dst.data_ptr(), s1=512, s2=0, s3=0,
+                              d1=512, d2=0, d3=0, n1=100000, n2=1, n3=1, run=512,
+                              signal=None, wait=None))
+    rc = lib.tzb_boxcopy_static(big, 1, 8, 1, stream)
     assert rc != 0
     msg = lib.tzb_last_error().decode()
     assert "built-in array" in msg and str(STATIC_BYTES - 4096) in msg
+    # too many regions for the built-in counters
+    n = 2000
+    arr = (TzbBox * n)()
+    for i in range(n):
+        arr[i] = TzbBox(src=src.data_ptr(), dst=dst.data_ptr(), s1=4, s2=4, s3=4,
+                        d1=4, d2=4, d3=4, n1=1, n2=1, n3=1, run=4, signal=None, wait=None)
+    assert lib.tzb_boxcopy_static(arr, n, 8, 1, stream) != 0
+    assert "counters" in lib.tzb_last_error().decode()
     torch.cuda.synchronize()
     # and the entry point still works afterwards
     ok = (TzbBox * 1)(arr[0])
