@@ -200,7 +200,7 @@ def main():
     # ---------------- secondary: distributed SpMV ----------------
     spmv = DistributedSpMV(comm=comm, n=args.spmv_n, nnz_per_row=10)
     spmv.fill()
-    seq_s = find_best(spmv, "dfs", ["fused", "fused_separate"], 64)
+    seq_s = find_best(spmv, "dfs", ["fused", "fused_separate", "fused_all"], 64)
     spmv.fill()
     comm.barrier()
     spmv.run(seq_s)

@@ -42,7 +42,7 @@ public:
     int count = 0;
     int dstDispl = 0; // send only: offset in the peer's rx
   };
-  enum class Style { Reference, Fused, FusedSeparate };
+  enum class Style { Reference, Fused, FusedSeparate, FusedAll };
 
   // myRows: the rows [get_partition(n, rank, size)) of the global n x n matrix, global column ids
   RowPartSpmv(std::shared_ptr<Communicator> comm, const CsrMat<int, Scalar> &myRows, int64_t n,
@@ -100,7 +100,8 @@ private:
 //   WaitRecv -> yr; {yl, yr} -> y; {y, WaitSend} -> Finish
 // with copy-engine peer copies as the transport.  Fused:
 //   Start -> {yl, PackPut}; {yl, PackPut} -> yr (waits on flags, accumulates into y) -> Finish
-// FusedSeparate keeps yl and yr independent and adds them in `y`.
+// FusedSeparate keeps yl and yr independent and adds them in `y`.  FusedAll is one op: a
+// single kernel that puts, multiplies locally, waits for the peers and accumulates the remote part.
 template <typename Scalar> class SpMV : public CompoundOp {
   std::string name_;
   Graph<OpBase> graph_;

@@ -69,6 +69,20 @@ int tzb_spmv_csr_wait_f32(int rows, const int *rowPtr, const int *colInd, const 
                           const float *x, float *y, int accumulate, const uint64_t *flags,
                           int nFlags, uint64_t epoch, void *stream);
 
+/* The whole distributed product in one launch (no counterpart in the reference, where it is
+ * seven ops): gather-put of my x entries to every peer + flag publish, y = A_local x, wait for
+ * the nFlags local flags, y += A_remote rx.  `counter`: one zeroed uint32 of scratch. */
+int tzb_spmv_fused_all_f64(const TzbGatherPutArgs *put, const int *sendIdx, int rows,
+                           const int *lRowPtr, const int *lColInd, const double *lVal,
+                           const int *rRowPtr, const int *rColInd, const double *rVal,
+                           const double *x, const double *rx, double *y, const uint64_t *flags,
+                           int nFlags, uint64_t epoch, uint32_t *counter, void *stream);
+int tzb_spmv_fused_all_f32(const TzbGatherPutArgs *put, const int *sendIdx, int rows,
+                           const int *lRowPtr, const int *lColInd, const float *lVal,
+                           const int *rRowPtr, const int *rColInd, const float *rVal,
+                           const float *x, const float *rx, float *y, const uint64_t *flags,
+                           int nFlags, uint64_t epoch, uint32_t *counter, void *stream);
+
 /* ----------------------------------------------------------- box copies ---- */
 /* One description serves pack, unpack, pack+put and direct put of a halo
  * region in either storage order (replaces pack/unpack kernels

@@ -54,6 +54,7 @@ Graph<OpBase> make_graph(const std::shared_ptr<RowPartSpmv<Scalar>> &spmv, const
   else if (style == "reference") op = std::make_shared<SpMV<Scalar>>("spmv", spmv, Style::Reference);
   else if (style == "fused") op = std::make_shared<SpMV<Scalar>>("spmv", spmv, Style::Fused);
   else if (style == "fused_separate") op = std::make_shared<SpMV<Scalar>>("spmv", spmv, Style::FusedSeparate);
+  else if (style == "fused_all") op = std::make_shared<SpMV<Scalar>>("spmv", spmv, Style::FusedAll);
   else THROW_RUNTIME("unknown style " << style);
   g.start_then(op);
   g.then_finish(op);

@@ -31,6 +31,7 @@ typename RowPartSpmv<Scalar>::Style spmv_style(const std::string &s) {
   if (s == "reference") return Style::Reference;
   if (s == "fused") return Style::Fused;
   if (s == "fused_separate") return Style::FusedSeparate;
+  if (s == "fused_all") return Style::FusedAll;
   throw std::runtime_error("unknown spmv style '" + s + "'");
 }
 
@@ -106,5 +107,5 @@ void bind_spmv(py::module_ &m) {
     return std::make_pair(r.lb, r.ub);
   });
   s.def("get_owner", &get_owner);
-  s.def("styles", [] { return std::vector<std::string>{"reference", "fused", "fused_separate"}; });
+  s.def("styles", [] { return std::vector<std::string>{"reference", "fused", "fused_separate", "fused_all"}; });
 }

@@ -8,6 +8,7 @@
 // src/spmv/ops_spmv.cu:26-47.
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <atomic>
 #include <cstdint>
 
@@ -112,6 +113,58 @@ gather_put_kernel(TzbGatherPutArgs a, const int *__restrict__ idx, const T *__re
   }
 }
 
+// The whole distributed product in ONE launch: (1) gather my x entries straight into the
+// peers' receive buffers and publish the epoch, (2) local product while those stores and the
+// peers' stores are in flight, (3) wait for every peer's flag, (4) accumulate the remote
+// product.  No block waits for another block of the same GPU; the only waiting is on flags
+// written by other GPUs, whose phase (1) does not depend on anything here.
+template <typename T, int TPR>
+__global__ void __launch_bounds__(kThreads)
+spmv_fused_all_kernel(TzbGatherPutArgs a, const int *__restrict__ sendIdx, int rows,
+                      const int *__restrict__ lRowPtr, const int *__restrict__ lColInd,
+                      const T *__restrict__ lVal, const int *__restrict__ rRowPtr,
+                      const int *__restrict__ rColInd, const T *__restrict__ rVal,
+                      const T *__restrict__ x, const T *__restrict__ rx, T *__restrict__ y,
+                      const uint64_t *flags, int nFlags, uint64_t epoch, unsigned *counter) {
+  // (1) put
+  const int nSend = a.displ[a.nPeers];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nSend; i += gridDim.x * blockDim.x) {
+    int p = 0;
+    while (i >= a.displ[p + 1]) ++p;
+    static_cast<T *>(a.peerDst[p])[i - a.displ[p]] = x[__ldg(sendIdx + i)];
+  }
+  if (block_arrive_last(counter, gridDim.x)) {
+    for (int p = threadIdx.x; p < a.nPeers; p += blockDim.x)
+      if (a.peerFlag[p]) st_release_sys(a.peerFlag[p], epoch);
+  }
+  // (2) local product
+  const int lane = threadIdx.x % TPR;
+  const int groupsPerBlock = kThreads / TPR;
+  const int row0 = blockIdx.x * groupsPerBlock + threadIdx.x / TPR;
+  const int stride = gridDim.x * groupsPerBlock;
+  for (int row = row0; row < rows; row += stride) {
+    const int begin = __ldg(lRowPtr + row), end = __ldg(lRowPtr + row + 1);
+    T acc = 0;
+    for (int j = begin + lane; j < end; j += TPR) acc += __ldg(lVal + j) * x[__ldg(lColInd + j)];
+#pragma unroll
+    for (int off = TPR / 2; off > 0; off /= 2) acc += __shfl_down_sync(0xffffffffu, acc, off, TPR);
+    if (lane == 0) y[row] = acc;
+  }
+  // (3) wait for the peers
+  if (int(threadIdx.x) < nFlags) wait_flag_geq(flags + threadIdx.x, epoch);
+  __syncthreads();
+  // (4) remote product; the same lane group wrote y[row] above, so no inter-thread hazard
+  for (int row = row0; row < rows; row += stride) {
+    const int begin = __ldg(rRowPtr + row), end = __ldg(rRowPtr + row + 1);
+    if (begin == end) continue;
+    T acc = 0;
+    for (int j = begin + lane; j < end; j += TPR) acc += __ldg(rVal + j) * rx[__ldg(rColInd + j)];
+#pragma unroll
+    for (int off = TPR / 2; off > 0; off /= 2) acc += __shfl_down_sync(0xffffffffu, acc, off, TPR);
+    if (lane == 0) y[row] += acc;
+  }
+}
+
 int grid_for(int n) {
   int blocks = (n + kThreads - 1) / kThreads;
   if (blocks > kSMs * 8) blocks = kSMs * 8;
@@ -158,6 +211,56 @@ cudaError_t spmv_csr_wait(int rows, const int *rowPtr, const int *colInd, const 
                           const uint64_t *flags, int nFlags, uint64_t epoch, cudaStream_t stream) {
   return launch_spmv<float, true>(rows, rowPtr, colInd, val, x, y, accumulate, flags, nFlags,
                                   epoch, nnzPerRow, stream);
+}
+
+template <typename T>
+cudaError_t launch_spmv_fused_all(const TzbGatherPutArgs *a, const int *sendIdx, int rows,
+                                  const int *lRowPtr, const int *lColInd, const T *lVal,
+                                  const int *rRowPtr, const int *rColInd, const T *rVal, const T *x,
+                                  const T *rx, T *y, const uint64_t *flags, int nFlags,
+                                  uint64_t epoch, uint32_t *counter, int nnzPerRow,
+                                  cudaStream_t stream) {
+  if (!a || a->nPeers < 0 || a->nPeers > 16 || nFlags > kThreads) return cudaErrorInvalidValue;
+  int tpr = 2;
+  while (tpr < 32 && tpr * 2 <= nnzPerRow) tpr *= 2;
+  const int groupsPerBlock = kThreads / tpr;
+  int blocks = (std::max(rows, 1) + groupsPerBlock - 1) / groupsPerBlock;
+  if (blocks > kSMs * 8) blocks = kSMs * 8;
+  ++g_launches;
+#define TZB_CASE(N)                                                                                \
+  case N:                                                                                          \
+    spmv_fused_all_kernel<T, N><<<blocks, kThreads, 0, stream>>>(                                  \
+        *a, sendIdx, rows, lRowPtr, lColInd, lVal, rRowPtr, rColInd, rVal, x, rx, y, flags,       \
+        nFlags, epoch, counter);                                                                   \
+    break
+  switch (tpr) {
+    TZB_CASE(2);
+    TZB_CASE(4);
+    TZB_CASE(8);
+    TZB_CASE(16);
+    TZB_CASE(32);
+  }
+#undef TZB_CASE
+  return cudaGetLastError();
+}
+
+cudaError_t spmv_fused_all(const TzbGatherPutArgs *a, const int *sendIdx, int rows,
+                           const int *lRowPtr, const int *lColInd, const double *lVal,
+                           const int *rRowPtr, const int *rColInd, const double *rVal,
+                           const double *x, const double *rx, double *y, const uint64_t *flags,
+                           int nFlags, uint64_t epoch, uint32_t *counter, int nnzPerRow,
+                           cudaStream_t stream) {
+  return launch_spmv_fused_all<double>(a, sendIdx, rows, lRowPtr, lColInd, lVal, rRowPtr, rColInd,
+                                       rVal, x, rx, y, flags, nFlags, epoch, counter, nnzPerRow, stream);
+}
+cudaError_t spmv_fused_all(const TzbGatherPutArgs *a, const int *sendIdx, int rows,
+                           const int *lRowPtr, const int *lColInd, const float *lVal,
+                           const int *rRowPtr, const int *rColInd, const float *rVal,
+                           const float *x, const float *rx, float *y, const uint64_t *flags,
+                           int nFlags, uint64_t epoch, uint32_t *counter, int nnzPerRow,
+                           cudaStream_t stream) {
+  return launch_spmv_fused_all<float>(a, sendIdx, rows, lRowPtr, lColInd, lVal, rRowPtr, rColInd,
+                                      rVal, x, rx, y, flags, nFlags, epoch, counter, nnzPerRow, stream);
 }
 
 } // namespace tzb
@@ -220,6 +323,25 @@ int tzb_gather_put_f64(const TzbGatherPutArgs *args, const int *idx, const doubl
 int tzb_gather_put_f32(const TzbGatherPutArgs *args, const int *idx, const float *src,
                        uint64_t epoch, uint32_t *counter, void *stream) {
   return launch_gather_put<float>(args, idx, src, epoch, counter, static_cast<cudaStream_t>(stream));
+}
+
+int tzb_spmv_fused_all_f64(const TzbGatherPutArgs *put, const int *sendIdx, int rows,
+                           const int *lRowPtr, const int *lColInd, const double *lVal,
+                           const int *rRowPtr, const int *rColInd, const double *rVal,
+                           const double *x, const double *rx, double *y, const uint64_t *flags,
+                           int nFlags, uint64_t epoch, uint32_t *counter, void *stream) {
+  return launch_spmv_fused_all<double>(put, sendIdx, rows, lRowPtr, lColInd, lVal, rRowPtr, rColInd,
+                                       rVal, x, rx, y, flags, nFlags, epoch, counter,
+                                       kDefaultNnzPerRow, static_cast<cudaStream_t>(stream));
+}
+int tzb_spmv_fused_all_f32(const TzbGatherPutArgs *put, const int *sendIdx, int rows,
+                           const int *lRowPtr, const int *lColInd, const float *lVal,
+                           const int *rRowPtr, const int *rColInd, const float *rVal,
+                           const float *x, const float *rx, float *y, const uint64_t *flags,
+                           int nFlags, uint64_t epoch, uint32_t *counter, void *stream) {
+  return launch_spmv_fused_all<float>(put, sendIdx, rows, lRowPtr, lColInd, lVal, rRowPtr, rColInd,
+                                      rVal, x, rx, y, flags, nFlags, epoch, counter,
+                                      kDefaultNnzPerRow, static_cast<cudaStream_t>(stream));
 }
 
 uint64_t tzb_launch_count(void) { return g_launches.load(); }

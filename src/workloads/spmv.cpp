@@ -17,6 +17,14 @@ cudaError_t spmv_csr_wait(int, const int *, const int *, const double *, const d
                           bool, int, const uint64_t *, int, uint64_t, cudaStream_t);
 cudaError_t spmv_csr_wait(int, const int *, const int *, const float *, const float *, float *,
                           bool, int, const uint64_t *, int, uint64_t, cudaStream_t);
+cudaError_t spmv_fused_all(const TzbGatherPutArgs *, const int *, int, const int *, const int *,
+                           const double *, const int *, const int *, const double *, const double *,
+                           const double *, double *, const uint64_t *, int, uint64_t, uint32_t *, int,
+                           cudaStream_t);
+cudaError_t spmv_fused_all(const TzbGatherPutArgs *, const int *, int, const int *, const int *,
+                           const float *, const int *, const int *, const float *, const float *,
+                           const float *, float *, const uint64_t *, int, uint64_t, uint32_t *, int,
+                           cudaStream_t);
 } // namespace tzb
 
 namespace tenzing {
@@ -116,7 +124,7 @@ RowPartSpmv<Scalar>::RowPartSpmv(std::shared_ptr<Communicator> comm,
   comm->allreduce_max(sizes, 3);
   const size_t maxRows = size_t(sizes[0]), maxRemote = size_t(sizes[1]), maxSend = size_t(sizes[2]);
   const size_t es = sizeof(Scalar);
-  const size_t flagBytes = sizeof(uint64_t) * 3 * size_t(np);
+  const size_t flagBytes = sizeof(uint64_t) * 4 * size_t(np); // one set per style
   const size_t total = 3 * up256(maxRows * es) + 2 * up256(maxRemote * es) + up256(maxSend * es) +
                        up256(flagBytes) + 4096;
   heap_.reset(new SymmetricHeap(comm, total, memory));
@@ -287,6 +295,54 @@ public:
   }
 };
 
+// one slot per rank, in rank order; ranks that get no data still get the flag so the handshake
+// is all-to-all and nobody can run more than one epoch ahead of anybody
+template <typename Scalar>
+TzbGatherPutArgs make_put_args(const RowPartSpmv<Scalar> &s, St<Scalar> style, int parity) {
+  const int np = s.size(), me = s.rank();
+  TzbGatherPutArgs a;
+  std::memset(&a, 0, sizeof(a));
+  a.nPeers = np;
+  size_t k = 0;
+  const auto &sp = s.send_params();
+  int displ = 0;
+  for (int r = 0; r < np; ++r) {
+    a.displ[r] = displ;
+    a.peerFlag[r] = s.flag(r, style, me);
+    if (k < sp.size() && sp[k].peer == r) {
+      a.peerDst[r] = s.rx(r, parity) + sp[k].dstDispl;
+      displ += sp[k].count;
+      ++k;
+    }
+  }
+  a.displ[np] = displ;
+  return a;
+}
+
+// the whole product as one kernel launch (put, local product, flag wait, remote product)
+template <typename Scalar> class FusedAllSpMV : public GpuOp {
+  SpmvPtr<Scalar> s_;
+
+public:
+  explicit FusedAllSpMV(SpmvPtr<Scalar> s) : s_(std::move(s)) {}
+  std::string name() const override { return "SpMVAll"; }
+  CLONE_DEF(FusedAllSpMV)
+  void run(cudaStream_t) override { THROW_RUNTIME("SpMVAll needs the platform epoch"); }
+  void run(Platform &plat, cudaStream_t st) override {
+    if (s_->null_device() || plat.is_null()) return;
+    const int parity = int(plat.epoch() & 1);
+    const auto style = St<Scalar>::FusedAll;
+    const TzbGatherPutArgs a = make_put_args(*s_, style, parity);
+    const auto &L = s_->lA();
+    const auto &R = s_->rA();
+    CUDA_RUNTIME(tzb::spmv_fused_all(&a, s_->x_send_idx(), L.rows, L.row_ptr(), L.col_ind(),
+                                     L.values(), R.row_ptr(), R.col_ind(), R.values(), s_->lx(),
+                                     s_->rx(s_->rank(), parity), s_->ly(),
+                                     s_->flag(s_->rank(), style, 0), s_->size(), plat.epoch(),
+                                     s_->counter(), std::max(L.nnz_per_row(), 2), st));
+  }
+};
+
 // host-driven transport of the reference structure (copy engine + flags)
 struct SpmvTransport {
   cudaStream_t send = nullptr, recv = nullptr;
@@ -382,6 +438,10 @@ SpMV<Scalar>::SpMV(const std::string &name, const std::shared_ptr<RowPartSpmv<Sc
     g.then(yr, y);
     g.then_finish(y);
     g.then_finish(waitSend);
+  } else if (style == Style::FusedAll) {
+    OpPtr all = std::make_shared<FusedAllSpMV<Scalar>>(s);
+    g.start_then(all);
+    g.then_finish(all);
   } else if (style == Style::Fused) {
     OpPtr put = std::make_shared<PackPut<Scalar>>(s, style);
     OpPtr yr = std::make_shared<RemoteSpMV<Scalar>>(s, true, true, style);
@@ -410,6 +470,7 @@ std::shared_ptr<ChoiceOp> make_spmv_choice(const std::shared_ptr<RowPartSpmv<Sca
   alts.push_back(std::make_shared<SpMV<Scalar>>("spmv_reference", s, Style::Reference));
   alts.push_back(std::make_shared<SpMV<Scalar>>("spmv_fused", s, Style::Fused));
   alts.push_back(std::make_shared<SpMV<Scalar>>("spmv_fused_separate", s, Style::FusedSeparate));
+  alts.push_back(std::make_shared<SpMV<Scalar>>("spmv_fused_all", s, Style::FusedAll));
   return std::make_shared<ListChoiceOp>("spmv", alts);
 }
 template std::shared_ptr<ChoiceOp> make_spmv_choice<double>(const std::shared_ptr<RowPartSpmv<double>> &);

@@ -12,7 +12,7 @@ from ..parallel import make_comm
 from ..utils.tensor import device_tensor, host_tensor
 from . import common
 
-STYLES = ("reference", "fused", "fused_separate")
+STYLES = ("reference", "fused", "fused_separate", "fused_all")
 
 
 def _csr_from_dict(d, dtype):

@@ -41,7 +41,7 @@ def main():
     for dtype in (torch.float64, torch.float32):
         for n, bw in ((40_000, None), (30_011, 30_011)):  # band (neighbour peers) and random (all peers)
             s = DistributedSpMV(comm=comm, n=n, bw=bw, nnz_per_row=10, dtype=dtype)
-            for style in ("reference", "fused", "fused_separate"):
+            for style in ("reference", "fused", "fused_separate", "fused_all"):
                 seq = common.fixed_schedule(s.graph(style), s.platform)
                 for _ in range(3):
                     s.fill()

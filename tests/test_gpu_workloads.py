@@ -39,7 +39,7 @@ def test_halo_fp32_and_thick_rows():
 
 
 @pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
-@pytest.mark.parametrize("style", ["reference", "fused", "fused_separate"])
+@pytest.mark.parametrize("style", ["reference", "fused", "fused_separate", "fused_all"])
 def test_spmv_styles_single_rank(style, dtype):
     from tenzing_b200.models import DistributedSpMV, common
     s = DistributedSpMV(n=20011, nnz_per_row=10, dtype=dtype)

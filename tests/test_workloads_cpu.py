@@ -83,7 +83,7 @@ def test_spmv_graphs_have_the_reference_shape():
     assert e.vertex_size() == inner.vertex_size()
     assert s.graph("fused").find_name("spmv").graph().vertex_size() == 5
     ch = s.graph("choice").find_name("spmv")
-    assert [c.name() for c in ch.choices()] == ["spmv_reference", "spmv_fused", "spmv_fused_separate"]
+    assert [c.name() for c in ch.choices()] == ["spmv_reference", "spmv_fused", "spmv_fused_separate", "spmv_fused_all"]
 
 
 def test_halo_geometry_and_graph_structure():
