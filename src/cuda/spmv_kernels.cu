@@ -38,6 +38,10 @@ spmv_csr_kernel(int rows, const int *__restrict__ rowPtr, const int *__restrict_
     __syncthreads();
   }
   const int lane = threadIdx.x % TPR;
+  // the lanes of MY row only: groups of one warp leave the row loop (or skip empty rows)
+  // independently, so a full-warp mask would name lanes that never arrive
+  const unsigned groupMask =
+      TPR == 32 ? 0xffffffffu : (((1u << TPR) - 1u) << ((threadIdx.x & 31) / TPR * TPR));
   const int groupsPerBlock = kThreads / TPR;
   for (int row = blockIdx.x * groupsPerBlock + threadIdx.x / TPR; row < rows;
        row += gridDim.x * groupsPerBlock) {
@@ -45,7 +49,7 @@ spmv_csr_kernel(int rows, const int *__restrict__ rowPtr, const int *__restrict_
     T acc = 0;
     for (int j = begin + lane; j < end; j += TPR) acc += __ldg(val + j) * x[__ldg(colInd + j)];
 #pragma unroll
-    for (int off = TPR / 2; off > 0; off /= 2) acc += __shfl_down_sync(0xffffffffu, acc, off, TPR);
+    for (int off = TPR / 2; off > 0; off /= 2) acc += __shfl_down_sync(groupMask, acc, off, TPR);
     if (lane == 0) y[row] = accumulate ? y[row] + acc : acc;
   }
 }
@@ -139,6 +143,10 @@ spmv_fused_all_kernel(TzbGatherPutArgs a, const int *__restrict__ sendIdx, int r
   }
   // (2) local product
   const int lane = threadIdx.x % TPR;
+  // the lanes of MY row only: groups of one warp leave the row loop (or skip empty rows)
+  // independently, so a full-warp mask would name lanes that never arrive
+  const unsigned groupMask =
+      TPR == 32 ? 0xffffffffu : (((1u << TPR) - 1u) << ((threadIdx.x & 31) / TPR * TPR));
   const int groupsPerBlock = kThreads / TPR;
   const int row0 = blockIdx.x * groupsPerBlock + threadIdx.x / TPR;
   const int stride = gridDim.x * groupsPerBlock;
@@ -147,7 +155,7 @@ spmv_fused_all_kernel(TzbGatherPutArgs a, const int *__restrict__ sendIdx, int r
     T acc = 0;
     for (int j = begin + lane; j < end; j += TPR) acc += __ldg(lVal + j) * x[__ldg(lColInd + j)];
 #pragma unroll
-    for (int off = TPR / 2; off > 0; off /= 2) acc += __shfl_down_sync(0xffffffffu, acc, off, TPR);
+    for (int off = TPR / 2; off > 0; off /= 2) acc += __shfl_down_sync(groupMask, acc, off, TPR);
     if (lane == 0) y[row] = acc;
   }
   // (3) wait for the peers
@@ -160,7 +168,7 @@ spmv_fused_all_kernel(TzbGatherPutArgs a, const int *__restrict__ sendIdx, int r
     T acc = 0;
     for (int j = begin + lane; j < end; j += TPR) acc += __ldg(rVal + j) * rx[__ldg(rColInd + j)];
 #pragma unroll
-    for (int off = TPR / 2; off > 0; off /= 2) acc += __shfl_down_sync(0xffffffffu, acc, off, TPR);
+    for (int off = TPR / 2; off > 0; off /= 2) acc += __shfl_down_sync(groupMask, acc, off, TPR);
     if (lane == 0) y[row] += acc;
   }
 }

@@ -29,6 +29,8 @@ def main():
         h = HaloExchange(comm=comm, nX=24, nY=10, nZ=12, nQ=2, nGhost=3, storage_order=order)
         for style in ("reference", "staged", "direct", "fused_all", "fused_staged", "fused_groups", "fused_mixed", "fused_pipelined"):
             seq = common.fixed_schedule(h.graph(style), h.platform)
+            if rank == 0 and os.environ.get("TZ_WORKER_VERBOSE"):
+                print("halo", order, style, flush=True)
             for _ in range(3):
                 h.fill()
                 comm.barrier()
@@ -43,6 +45,8 @@ def main():
             s = DistributedSpMV(comm=comm, n=n, bw=bw, nnz_per_row=10, dtype=dtype)
             for style in ("reference", "fused", "fused_separate", "fused_all"):
                 seq = common.fixed_schedule(s.graph(style), s.platform)
+                if rank == 0 and os.environ.get("TZ_WORKER_VERBOSE"):
+                    print("spmv", dtype, n, style, flush=True)
                 for _ in range(3):
                     s.fill()
                     comm.barrier()
