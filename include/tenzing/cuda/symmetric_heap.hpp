@@ -43,6 +43,17 @@ public:
   size_t alloc(size_t bytes, size_t align = 256);
   size_t used() const { return used_; }
 
+  // byte offset of a pointer into ANY rank's allocation (the same word on every rank has the
+  // same offset); -1 if the pointer is not in the heap
+  int64_t offset_of(const void *p) const {
+    for (void *b : bases_) {
+      const char *lo = static_cast<const char *>(b);
+      const char *q = static_cast<const char *>(p);
+      if (b && q >= lo && q < lo + bytes_) return int64_t(q - lo);
+    }
+    return -1;
+  }
+
   // zero the local allocation (or a range of it)
   void zero(size_t offset = 0, size_t bytes = size_t(-1));
 

@@ -37,6 +37,7 @@
 
 #include "tenzing/cuda/ops_cuda.hpp"
 #include "tenzing/cuda/symmetric_heap.hpp"
+#include "tenzing/flag_synchronizer.hpp"
 #include "tenzing/graph.hpp"
 #include "tenzing/operation_compound.hpp"
 #include "tenzing_b200.h"
@@ -155,7 +156,7 @@ private:
 };
 
 // A GPU op that runs one box-copy plan per epoch parity (see tenzing_b200.h).
-class BoxCopyOp : public GpuOp {
+class BoxCopyOp : public GpuOp, public HasFlags {
   struct Plan {
     TzbBoxPlanInfo info{};
     std::shared_ptr<void> dev;     // device image
@@ -165,6 +166,7 @@ class BoxCopyOp : public GpuOp {
   std::shared_ptr<std::array<Plan, 2>> plans_; // shared between clones
   bool null_ = false;
   bool issueOrderOnly_ = false;
+  std::vector<uint64_t> published_, awaited_; // flag channels (heap offsets), see set_heap()
 
 public:
   // boxes[parity]: the copies to perform when (epoch & 1) == parity
@@ -173,6 +175,13 @@ public:
             const std::vector<TzbBox> &odd, int elemSize, bool nullDevice = false,
             bool ordered = false);
   void set_issue_order_only(bool v) { issueOrderOnly_ = v; }
+  // translate the boxes' flag pointers into heap offsets so FlagSynchronizer can reason about them
+  void set_flag_channels(std::vector<uint64_t> published, std::vector<uint64_t> awaited) {
+    published_ = std::move(published);
+    awaited_ = std::move(awaited);
+  }
+  std::vector<uint64_t> flags_published() const override { return published_; }
+  std::vector<uint64_t> flags_awaited() const override { return awaited_; }
   bool issue_order_only() const override { return issueOrderOnly_; }
   std::string name() const override { return name_; }
   CLONE_DEF(BoxCopyOp)

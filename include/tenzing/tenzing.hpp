@@ -11,6 +11,7 @@
 #include "tenzing/decision.hpp"
 #include "tenzing/dfs.hpp"
 #include "tenzing/event_synchronizer.hpp"
+#include "tenzing/flag_synchronizer.hpp"
 #include "tenzing/graph.hpp"
 #include "tenzing/init.hpp"
 #include "tenzing/mcts.hpp"

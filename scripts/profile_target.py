@@ -15,7 +15,7 @@ if which == "halo":
     h = HaloExchange(nX=512, nQ=3, nGhost=3, n_streams=1)
     h.fill()
     names = {"direct": ["he_put_dx0_dy0_dz1", "he_put_dx1_dy0_dz0"],
-             "staged": ["he_packput_dx1_dy0_dz0"],
+             "staged": ["he_packput_dx1_dy0_dz0", "he_packput_dx0_dy0_dz1"],
              "fused_all": ["he_put_all"], "fused_staged": ["he_packput_all"]}
     for rep in range(2):
         for style, ops in names.items():
@@ -32,8 +32,9 @@ if which == "halo":
 else:
     s = DistributedSpMV(n=1_000_000, nnz_per_row=10)
     s.fill()
-    seq = common.fixed_schedule(s.graph("fused"), s.platform)
-    for rep in range(3):
-        s.run(seq)
-        torch.cuda.synchronize()
+    for style in ("fused", "fused_all"):
+        seq = common.fixed_schedule(s.graph(style), s.platform)
+        for rep in range(2):
+            s.run(seq)
+            torch.cuda.synchronize()
 print("done")

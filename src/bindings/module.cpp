@@ -509,6 +509,18 @@ PYBIND11_MODULE(_C, m) {
       .def_static("make_syncs", &EventSynchronizer::make_syncs, py::arg("op"), py::arg("graph"),
                   py::arg("path"), py::arg("quiet") = true);
 
+  // cross-rank flag dependencies (device-side synchronisation between GPUs)
+  py::class_<FlagSynchronizer>(m, "FlagSynchronizer")
+      .def_static("is_deadlock_free", &FlagSynchronizer::is_deadlock_free)
+      .def_static("check",
+                  [](const Seq &s) {
+                    std::vector<std::tuple<size_t, std::string, uint64_t>> out;
+                    for (const auto &v : FlagSynchronizer::check(s)) out.emplace_back(v.position, v.op, v.channel);
+                    return out;
+                  })
+      .def_static("add_edges", &FlagSynchronizer::add_edges)
+      .def_static("is_ready", [](const BoundOp &op, const Seq &path) { return FlagSynchronizer::is_ready(op, path); });
+
   // ---- schedule ----
   m.def("remove_redundant_syncs", [](Seq &s) { return Schedule::remove_redundant_syncs(s); });
   m.def("make_schedules",

@@ -340,15 +340,22 @@ public:
 };
 
 // GPU op that waits for a set of local flags (completion of direct puts)
-class WaitFlagsOp : public GpuOp {
+class WaitFlagsOp : public GpuOp, public HasFlags {
   std::string name_;
   const uint64_t *flags_;
   int n_;
   bool null_;
+  std::vector<uint64_t> awaited_;
 
 public:
   WaitFlagsOp(const std::string &name, const uint64_t *flags, int n, bool nullDevice)
       : name_(name), flags_(flags), n_(n), null_(nullDevice) {}
+  void set_channels(const SymmetricHeap &heap) {
+    awaited_.clear();
+    for (int i = 0; i < n_; ++i) awaited_.push_back(uint64_t(heap.offset_of(flags_ + i)));
+  }
+  std::vector<uint64_t> flags_published() const override { return {}; }
+  std::vector<uint64_t> flags_awaited() const override { return awaited_; }
   std::string name() const override { return name_; }
   CLONE_DEF(WaitFlagsOp)
   void run(cudaStream_t) override { THROW_RUNTIME("WaitFlagsOp needs the platform epoch"); }
@@ -397,9 +404,20 @@ struct Builder {
     return b;
   }
 
+  // flag channels (heap offsets) of a box list, for the FlagSynchronizer
+  void annotate(BoxCopyOp &op, const std::vector<TzbBox> &boxes) const {
+    std::vector<uint64_t> pub, wait;
+    for (const TzbBox &bx : boxes) {
+      if (bx.signal) pub.push_back(uint64_t(dom->heap().offset_of(bx.signal)));
+      if (bx.wait) wait.push_back(uint64_t(dom->heap().offset_of(bx.wait)));
+    }
+    op.set_flag_channels(pub, wait);
+  }
   std::shared_ptr<BoxCopyOp> op(const std::string &name, const std::vector<TzbBox> &even,
-                                const std::vector<TzbBox> &odd) const {
-    return std::make_shared<BoxCopyOp>(name, even, odd, es, null);
+                                const std::vector<TzbBox> &odd, bool ordered = false) const {
+    auto o = std::make_shared<BoxCopyOp>(name, even, odd, es, null, ordered);
+    annotate(*o, even); // both parities use the same flag words
+    return o;
   }
   std::shared_ptr<BoxCopyOp> op(const std::string &name, const std::vector<TzbBox> &boxes) const {
     return op(name, boxes, boxes);
@@ -469,8 +487,10 @@ void add_to_graph(Graph<OpBase> &g, const std::shared_ptr<Domain> &dom,
   }
 
   if (style == Style::Direct) {
-    OpPtr wait = std::make_shared<WaitFlagsOp>(
+    auto waitOp = std::make_shared<WaitFlagsOp>(
         "he_wait_puts", dom->flags_base(dom->rank(), style), int(dirs.size()), b.null);
+    waitOp->set_channels(dom->heap());
+    OpPtr wait = waitOp;
     for (const auto &d : dirs) {
       TzbBox box = b.direct_box(d);
       box.signal = dom->flag(dom->neighbor(d), style, -d);
@@ -490,8 +510,10 @@ void add_to_graph(Graph<OpBase> &g, const std::shared_ptr<Domain> &dom,
       boxes.push_back(box);
     }
     OpPtr put = b.op("he_put_all", boxes);
-    OpPtr wait = std::make_shared<WaitFlagsOp>(
+    auto waitOp = std::make_shared<WaitFlagsOp>(
         "he_finish_all", dom->flags_base(dom->rank(), style), int(dirs.size()), b.null);
+    waitOp->set_channels(dom->heap());
+    OpPtr wait = waitOp;
     connect(g, preds, put);
     g.add_edge(put, wait);
     connect(g, wait, succs);
@@ -526,10 +548,8 @@ void add_to_graph(Graph<OpBase> &g, const std::shared_ptr<Domain> &dom,
         }
       if (put[0].empty()) continue;
       // ordered plans: these kernels run beside each other and must share the SMs
-      OpPtr putOp = std::make_shared<BoxCopyOp>(std::string("he_packput_") + gname[grp], put[0], put[1],
-                                                b.es, b.null, true);
-      OpPtr finOp = std::make_shared<BoxCopyOp>(std::string("he_waitunpack_") + gname[grp], fin[0],
-                                                fin[1], b.es, b.null, true);
+      OpPtr putOp = b.op(std::string("he_packput_") + gname[grp], put[0], put[1], true);
+      OpPtr finOp = b.op(std::string("he_waitunpack_") + gname[grp], fin[0], fin[1], true);
       connect(g, preds, putOp);
       // only its own puts precede a group's unpack: ordered plans leave half of every SM free
       // (see tzb_boxcopy_launch), so a later put can always run beside a spinning unpack
@@ -590,8 +610,8 @@ void add_to_graph(Graph<OpBase> &g, const std::shared_ptr<Domain> &dom,
         // the neighbour on side e sends the region it calls -e: follow the PUT order
         fin[p].push_back(b.waitunpack_box(-d, p, style));
       }
-    auto putOp = std::make_shared<BoxCopyOp>("he_packput_pipe", put[0], put[1], b.es, b.null, true);
-    auto finOp = std::make_shared<BoxCopyOp>("he_waitunpack_pipe", fin[0], fin[1], b.es, b.null, true);
+    auto putOp = b.op("he_packput_pipe", put[0], put[1], true);
+    auto finOp = b.op("he_waitunpack_pipe", fin[0], fin[1], true);
     finOp->set_issue_order_only(true);
     connect(g, preds, OpPtr(putOp));
     g.add_edge(OpPtr(putOp), OpPtr(finOp)); // issue order only: the kernels may overlap

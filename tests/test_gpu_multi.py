@@ -10,7 +10,7 @@ pytestmark = pytest.mark.gpu
 HERE = os.path.dirname(os.path.abspath(__file__))
 
 
-def _run(nproc, timeout=420):
+def _run(nproc, timeout=180):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
            "--master-addr", "127.0.0.1", "--master-port", str(29600 + nproc),
            os.path.join(HERE, "multi_gpu_worker.py")]
