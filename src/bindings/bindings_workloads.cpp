@@ -6,6 +6,7 @@
 #include <pybind11/stl.h>
 
 #include "tenzing/halo/halo_exchange.hpp"
+#include "tenzing/spmv/array.hpp"
 #include "tenzing/tenzing.hpp"
 #include "tenzing_b200.h"
 
@@ -116,6 +117,14 @@ void bind_workloads(py::module_ &m) {
       .def("peer_ptr", [](const SymmetricHeap &h, int r) { return reinterpret_cast<uintptr_t>(h.peer(r)); })
       .def("alloc", &SymmetricHeap::alloc, py::arg("bytes"), py::arg("align") = 256)
       .def("zero", &SymmetricHeap::zero, py::arg("offset") = 0, py::arg("bytes") = size_t(-1));
+
+  // ---- NUMA-aware pinned staging ----
+  py::class_<PinnedPool>(m, "PinnedPool")
+      .def(py::init<int>(), py::arg("cuda_device") = -1)
+      .def("numa_node", &PinnedPool::numa_node)
+      .def("bytes_allocated", &PinnedPool::bytes_allocated)
+      .def("get", [](PinnedPool &p, size_t bytes) { return reinterpret_cast<uintptr_t>(p.get(bytes)); })
+      .def("put", [](PinnedPool &p, uintptr_t ptr, size_t bytes) { p.put(reinterpret_cast<void *>(ptr), bytes); });
 
   // ---- halo exchange ----
   py::module_ h = m.def_submodule("halo");

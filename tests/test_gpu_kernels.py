@@ -80,3 +80,20 @@ def test_flag_signal_then_wait_same_stream():
     _C.kernels.flags_wait(flags.data_ptr(), 4, 7, s)
     torch.cuda.synchronize()
     assert flags.cpu().tolist() == [7, 7, 7, 7]
+
+
+def test_pinned_pool_recycles_and_is_usable_for_h2d():
+    from tenzing_b200 import _C
+    from tenzing_b200.utils.tensor import host_tensor
+    pool = _C.PinnedPool()
+    p = pool.get(1 << 20)
+    t = host_tensor(p, (1 << 17,), torch.float64)
+    t.copy_(torch.arange(1 << 17, dtype=torch.float64))
+    d = torch.empty(1 << 17, dtype=torch.float64, device="cuda")
+    d.copy_(t, non_blocking=True)
+    torch.cuda.synchronize()
+    assert torch.equal(d.cpu(), t)
+    pool.put(p, 1 << 20)
+    assert pool.get(1 << 20) == p  # same size class comes back
+    assert pool.bytes_allocated() == 1 << 20
+    assert pool.numa_node() >= -1

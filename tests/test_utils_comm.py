@@ -147,3 +147,14 @@ def test_gloo_world_of_two_runs_the_noop_dfs():
     p = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env)
     assert p.returncode == 0, (p.stdout + p.stderr)[-3000:]
     assert "GLOO_WORKER_OK" in p.stdout, (p.stdout + p.stderr)[-3000:]
+
+
+def test_native_cpp_test_runner():
+    """the C++ checks that mirror the reference's doctest cases (src/apps/tenzing-cpu-tests.cpp)"""
+    exe = os.path.join(os.path.dirname(HERE), "build", "bin", "tenzing-cpu-tests")
+    if not os.path.exists(exe):
+        import build
+        build.build()
+    p = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stdout + p.stderr
+    assert "0 failed" in p.stdout
