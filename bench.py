@@ -155,7 +155,7 @@ def main():
     # the search: MCTS inside every fused implementation style (their decision spaces are small
     # enough to cover well) plus MCTS over the ChoiceOp of ALL styles, reference structure
     # included; the fastest sequence found anywhere is the schedule that gets timed
-    fused = ["fused_all", "fused_staged", "fused_mixed", "fused_pipelined", "fused_groups"]
+    fused = ["fused_all", "fused_staged", "fused_mixed", "fused_pipelined", "fused_groups", "fused_pull"]
     seq_h = find_best(halo, "mcts", fused + ["choice"], args.search_iters)
     halo.fill()
     comm.barrier()
@@ -240,7 +240,7 @@ def main():
                        "parallelism": "3d-block " + "x".join(map(str, halo.domain.rank_grid())),
                        "l2": "256 MB flush buffer written between timed steps",
                        "search": "no search" if args.no_search else
-                       f"MCTS FastMin {args.search_iters} iters per style (5 fused styles + ChoiceOp over all 8)"},
+                       f"MCTS FastMin {args.search_iters} iters per style (6 fused styles + ChoiceOp over all 9)"},
             "schedule": seq_h.names(), "correct": bool(ok_h and ok_s),
             "halo": {"us": round(us_h, 3), "bytes_out_per_rank": bytes_out, "remote_bytes_per_rank": remote,
                      "roofline_us": round(roof_h * 1e6, 3),

@@ -27,6 +27,9 @@
 //   FusedPipelined one put kernel that publishes every region's flag as soon as that region
 //              is complete and one unpack kernel that may run at the same time and follows
 //              region by region (thin regions first): transfer and unpack overlap
+//   FusedPull  receiver driven: after a tiny "my interior is ready" signal, one kernel LOADS every
+//              region straight from the neighbours' grids over NVLink into its own ghost cells
+//              (no staging, no unpack, all stores local) and acknowledges; one wait for the acks
 #pragma once
 
 #include <array>
@@ -71,7 +74,7 @@ template <typename T> std::shared_ptr<T> cuda_make_shared(size_t n) {
 namespace HaloExchange {
 
 enum class StorageOrder { QXYZ, XYZQ };
-enum class Style { Reference, Staged, Direct, FusedAll, FusedStaged, FusedGroups, FusedMixed, FusedPipelined };
+enum class Style { Reference, Staged, Direct, FusedAll, FusedStaged, FusedGroups, FusedMixed, FusedPipelined, FusedPull };
 const char *style_name(Style s);
 
 // MPI-style message tag of a direction (reference: ops_halo_exchange.cu:16-27)
@@ -139,6 +142,9 @@ public:
   // the flags an exchange uses
   uint64_t *flag(int rank, Style style, const Dim3<int> &side) const;
   uint64_t *flags_base(int rank, Style style) const;
+  // second flag set of the pull style ("I have read your data" acknowledgements)
+  uint64_t *ack_flag(int rank, const Dim3<int> &side) const;
+  uint64_t *ack_flags_base(int rank) const;
   int dir_index(const Dim3<int> &d) const;
 
   const std::vector<Dim3<int>> &dirs() const { return dirs_; }
@@ -213,7 +219,8 @@ std::shared_ptr<ChoiceOp> make_choice(const std::shared_ptr<Domain> &dom,
                                                                           Style::FusedStaged,
                                                                           Style::FusedGroups,
                                                                           Style::FusedMixed,
-                                                                          Style::FusedPipelined});
+                                                                          Style::FusedPipelined,
+                                                                          Style::FusedPull});
 
 } // namespace HaloExchange
 } // namespace tenzing

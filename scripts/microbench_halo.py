@@ -15,6 +15,7 @@ import torch  # noqa: E402
 
 from tenzing_b200 import _C  # noqa: E402
 from tenzing_b200.models import HaloExchange  # noqa: E402
+from tenzing_b200.parallel import init_process_group_from_env, make_comm  # noqa: E402
 
 
 def main():
@@ -26,10 +27,20 @@ def main():
     ap.add_argument("--reps", type=int, default=10)
     ap.add_argument("--out", default="")
     ap.add_argument("--l2gran", type=int, default=0)
+    ap.add_argument("--rank-grid", default="", help="e.g. 1,1,2 (under torch.distributed.run)")
+    ap.add_argument("--only", default="", help="comma separated substrings of op names to time")
     args = ap.parse_args()
+    rank, world, _ = init_process_group_from_env()
+    comm = make_comm()
     if args.l2gran:
         print("l2 fetch granularity (err, value):", _C.kernels.set_l2_fetch_granularity(args.l2gran))
-    h = HaloExchange(nX=args.nx, nQ=args.nq, nGhost=3, storage_order=args.order, n_streams=1)
+    rg = [int(v) for v in args.rank_grid.split(",")] if args.rank_grid else None
+    h = HaloExchange(comm=comm, nX=args.nx, nQ=args.nq, nGhost=3, storage_order=args.order, n_streams=1,
+                     rank_grid=rg)
+    quiet = rank != 0
+    if quiet:
+        import builtins
+        builtins.print = lambda *a, **k: None
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     rows = []
     # calibration: plain copies of one face / one whole exchange worth of bytes
@@ -56,11 +67,14 @@ def main():
         for op in g.vertices():
             if op.kind() != "GpuOp" or "wait" in op.name() or "finish" in op.name():
                 continue  # a wait op run alone would spin for a flag nobody publishes
+            if args.only and not any(k in op.name() for k in args.only.split(",")):
+                continue
             bound = _C.BoundGpuOp(op, 0)
             seq = _C.Sequence([bound])
             ts = _C.device_time_steps(seq, h.platform, args.reps, flush.data_ptr(), flush.numel())
             us = sorted(ts)[len(ts) // 2] * 1e6
             d = [int(x[2:]) for x in op.name().split("_")[-3:]] if "_dx" in op.name() else None
+            remote = d is not None and h.domain.neighbor(*d) != h.rank
             nbytes = h.domain.bytes_per_exchange()
             if d is not None:
                 ext = [3 if v else args.nx for v in d]
@@ -68,8 +82,11 @@ def main():
             rows.append({"style": style, "op": op.name(), "us": round(us, 2), "bytes": nbytes,
                          "gbs_rw": round(2 * nbytes / us / 1e3, 1)})
             total += us
-            print(f"{style:13s} {op.name():32s} {us:9.2f} us  {nbytes/1e6:8.2f} MB  {2*nbytes/us/1e3:8.1f} GB/s r+w")
+            where = "remote" if (d is not None and remote) else "local "
+            print(f"{style:13s} {op.name():32s} {where} {us:9.2f} us  {nbytes/1e6:8.2f} MB  {nbytes/us/1e3:8.1f} GB/s payload")
         print(f"{style:13s} {'SUM of put/pack ops':32s} {total:9.2f} us")
+        if args.only:
+            continue
         from tenzing_b200.models import common
         seq = common.fixed_schedule(h.graph(style), h.platform)
         h.platform.provision_events(seq)

@@ -50,7 +50,7 @@ inline int main_impl(int argc, char **argv, const char *defaultStrategy) {
       HaloExchange::Style st = HaloExchange::Style::Staged;
       for (auto s : {HaloExchange::Style::Reference, HaloExchange::Style::Staged,
                      HaloExchange::Style::Direct, HaloExchange::Style::FusedAll,
-                     HaloExchange::Style::FusedStaged, HaloExchange::Style::FusedGroups, HaloExchange::Style::FusedMixed, HaloExchange::Style::FusedPipelined})
+                     HaloExchange::Style::FusedStaged, HaloExchange::Style::FusedGroups, HaloExchange::Style::FusedMixed, HaloExchange::Style::FusedPipelined, HaloExchange::Style::FusedPull})
         if (style == HaloExchange::style_name(s)) st = s;
       HaloExchange::add_to_graph(g, dom, {g.start()}, {g.finish()}, st);
     }

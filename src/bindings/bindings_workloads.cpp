@@ -26,7 +26,7 @@ template <typename T> T *ptr(uintptr_t p) { return reinterpret_cast<T *>(p); }
 
 HaloExchange::Style style_from(const std::string &s) {
   using HaloExchange::Style;
-  for (Style st : {Style::Reference, Style::Staged, Style::Direct, Style::FusedAll, Style::FusedStaged, Style::FusedGroups, Style::FusedMixed, Style::FusedPipelined})
+  for (Style st : {Style::Reference, Style::Staged, Style::Direct, Style::FusedAll, Style::FusedStaged, Style::FusedGroups, Style::FusedMixed, Style::FusedPipelined, Style::FusedPull})
     if (s == HaloExchange::style_name(st)) return st;
   throw std::runtime_error("unknown halo style '" + s + "'");
 }
@@ -179,7 +179,7 @@ void bind_workloads(py::module_ &m) {
   h.def("rank_grid", [](int size) { auto g = HaloExchange::rank_grid(size); return std::vector<int>{g.x, g.y, g.z}; });
   h.def("dir_to_tag", [](int dx, int dy, int dz) { return HaloExchange::dir_to_tag(Dim3<int>(dx, dy, dz)); });
   h.def("styles", [] {
-    return std::vector<std::string>{"reference", "staged", "direct", "fused_all", "fused_staged", "fused_groups", "fused_mixed", "fused_pipelined"};
+    return std::vector<std::string>{"reference", "staged", "direct", "fused_all", "fused_staged", "fused_groups", "fused_mixed", "fused_pipelined", "fused_pull"};
   });
   h.def("add_to_graph", [](Graph<OpBase> &g, const std::shared_ptr<Domain> &dom,
                            const std::vector<OpPtr> &preds, const std::vector<OpPtr> &succs,
@@ -193,7 +193,7 @@ void bind_workloads(py::module_ &m) {
     std::vector<HaloExchange::Style> s;
     for (const auto &x : styles) s.push_back(style_from(x));
     return HaloExchange::make_choice(dom, s);
-  }, py::arg("domain"), py::arg("styles") = std::vector<std::string>{"reference", "staged", "direct", "fused_all", "fused_staged", "fused_groups", "fused_mixed", "fused_pipelined"});
+  }, py::arg("domain"), py::arg("styles") = std::vector<std::string>{"reference", "staged", "direct", "fused_all", "fused_staged", "fused_groups", "fused_mixed", "fused_pipelined", "fused_pull"});
 
   bind_spmv(m);
 }

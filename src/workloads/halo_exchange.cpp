@@ -22,6 +22,7 @@ const char *style_name(Style s) {
   case Style::FusedGroups: return "fused_groups";
   case Style::FusedMixed: return "fused_mixed";
   case Style::FusedPipelined: return "fused_pipelined";
+  case Style::FusedPull: return "fused_pull";
   }
   return "?";
 }
@@ -69,7 +70,7 @@ void Args::set_default_topology(int size) {
 
 // ---------------------------------------------------------------- Domain
 namespace {
-constexpr int kNumStyles = 8;
+constexpr int kNumStyles = 9; // + one extra flag set (acknowledgements of the pull style)
 size_t round_up_sz(size_t v, size_t a) { return (v + a - 1) / a * a; }
 } // namespace
 
@@ -102,7 +103,7 @@ Domain::Domain(std::shared_ptr<Communicator> comm, const Args &args, SymmetricHe
   stagingElems_ = off;
 
   const size_t stagingBytes = stagingElems_ * es;
-  const size_t flagBytes = sizeof(uint64_t) * 27 * kNumStyles;
+  const size_t flagBytes = sizeof(uint64_t) * 27 * (kNumStyles + 1);
   const size_t total = round_up_sz(grid_bytes(), 256) + 3 * round_up_sz(stagingBytes, 256) +
                        round_up_sz(flagBytes, 256) + 4096;
   heap_.reset(new SymmetricHeap(comm, total, memory));
@@ -180,6 +181,14 @@ uint64_t *Domain::flags_base(int rank, Style style) const {
 
 uint64_t *Domain::flag(int rank, Style style, const Dim3<int> &side) const {
   return flags_base(rank, style) + dir_index(side);
+}
+
+uint64_t *Domain::ack_flags_base(int rank) const {
+  return heap_->at<uint64_t>(rank, flagOff_) + size_t(kNumStyles) * 27;
+}
+
+uint64_t *Domain::ack_flag(int rank, const Dim3<int> &side) const {
+  return ack_flags_base(rank) + dir_index(side);
 }
 
 // ---------------------------------------------------------------- BoxCopyOp
@@ -363,6 +372,35 @@ public:
     if (null_ || plat.is_null()) return;
     CUDA_RUNTIME(cudaError_t(tzb_flags_wait(flags_, n_, plat.epoch(), stream)));
   }
+};
+
+// GPU op that publishes the epoch to a list of (peer) flags
+class SignalFlagsOp : public GpuOp, public HasFlags {
+  std::string name_;
+  TzbFlagList list_;
+  bool null_;
+  std::vector<uint64_t> published_;
+
+public:
+  SignalFlagsOp(const std::string &name, const std::vector<uint64_t *> &flags, const SymmetricHeap &heap,
+                bool nullDevice)
+      : name_(name), null_(nullDevice) {
+    if (flags.size() > 32) THROW_RUNTIME("at most 32 flags per signal op");
+    list_.n = int(flags.size());
+    for (size_t i = 0; i < flags.size(); ++i) {
+      list_.flag[i] = flags[i];
+      published_.push_back(uint64_t(heap.offset_of(flags[i])));
+    }
+  }
+  std::string name() const override { return name_; }
+  CLONE_DEF(SignalFlagsOp)
+  void run(cudaStream_t) override { THROW_RUNTIME("SignalFlagsOp needs the platform epoch"); }
+  void run(Platform &plat, cudaStream_t stream) override {
+    if (null_ || plat.is_null()) return;
+    CUDA_RUNTIME(cudaError_t(tzb_flags_signal(&list_, plat.epoch(), stream)));
+  }
+  std::vector<uint64_t> flags_published() const override { return published_; }
+  std::vector<uint64_t> flags_awaited() const override { return {}; }
 };
 
 struct Builder {
@@ -617,6 +655,34 @@ void add_to_graph(Graph<OpBase> &g, const std::shared_ptr<Domain> &dom,
     g.add_edge(OpPtr(putOp), OpPtr(finOp)); // issue order only: the kernels may overlap
     connect(g, OpPtr(putOp), succs);
     connect(g, OpPtr(finOp), succs);
+    return;
+  }
+  if (style == Style::FusedPull) {
+    // 1. tell every neighbour that my interior may be read for this epoch
+    std::vector<uint64_t *> ready;
+    for (const auto &d : dirs) ready.push_back(dom->flag(dom->neighbor(d), style, -d));
+    OpPtr readyOp = std::make_shared<SignalFlagsOp>("he_ready", ready, dom->heap(), b.null);
+    // 2. load every region from the neighbour's grid into my ghost cells; acknowledge
+    std::vector<TzbBox> boxes;
+    for (const auto &e : dirs) {
+      const int nb = dom->neighbor(e);
+      // the neighbour on my side e: its interior cells next to ITS face -e are my ghost cells e
+      TzbBox box = make_box(*dom, dom->grid_of(nb), Side::Grid, dom->send_offset(-e), dom->grid(),
+                            Side::Grid, dom->recv_offset(e), dom->region_extent(e));
+      box.wait = dom->flag(dom->rank(), style, e);
+      box.signal = dom->ack_flag(nb, -e);
+      boxes.push_back(box);
+    }
+    OpPtr pull = b.op("he_pull_all", boxes);
+    // 3. my interior may change again once every neighbour has read it
+    auto waitOp = std::make_shared<WaitFlagsOp>("he_wait_acks", dom->ack_flags_base(dom->rank()),
+                                                int(dirs.size()), b.null);
+    waitOp->set_channels(dom->heap());
+    OpPtr wait = waitOp;
+    connect(g, preds, readyOp);
+    g.add_edge(readyOp, pull);
+    g.add_edge(pull, wait);
+    connect(g, wait, succs);
     return;
   }
   THROW_RUNTIME("unknown halo style");

@@ -12,7 +12,7 @@ from ..parallel import make_comm
 from ..utils.tensor import device_tensor, host_tensor
 from . import common
 
-STYLES = ("reference", "staged", "direct", "fused_all", "fused_staged", "fused_groups", "fused_mixed", "fused_pipelined")
+STYLES = ("reference", "staged", "direct", "fused_all", "fused_staged", "fused_groups", "fused_mixed", "fused_pipelined", "fused_pull")
 
 
 class HaloExchange:

@@ -27,7 +27,7 @@ def main():
     failures = []
     for order in ("XYZQ", "QXYZ"):
         h = HaloExchange(comm=comm, nX=24, nY=10, nZ=12, nQ=2, nGhost=3, storage_order=order)
-        for style in ("reference", "staged", "direct", "fused_all", "fused_staged", "fused_groups", "fused_mixed", "fused_pipelined"):
+        for style in ("reference", "staged", "direct", "fused_all", "fused_staged", "fused_groups", "fused_mixed", "fused_pipelined", "fused_pull"):
             seq = common.fixed_schedule(h.graph(style), h.platform)
             if rank == 0 and os.environ.get("TZ_WORKER_VERBOSE"):
                 print("halo", order, style, flush=True)

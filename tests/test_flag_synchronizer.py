@@ -11,7 +11,7 @@ FS = _C.FlagSynchronizer
 def test_every_searched_schedule_is_deadlock_free():
     h = HaloExchange(nX=8, nQ=1, nGhost=1, neighbors=6, host=True)
     for style in ("staged", "direct", "fused_all", "fused_staged", "fused_groups", "fused_mixed",
-                  "fused_pipelined"):
+                  "fused_pipelined", "fused_pull"):
         seqs = tz.dfs.get_all_sequences(h.graph(style), h.platform, 300, True)
         assert seqs
         for s in seqs:

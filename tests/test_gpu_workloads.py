@@ -7,7 +7,7 @@ pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("order", ["XYZQ", "QXYZ"])
-@pytest.mark.parametrize("style", ["reference", "staged", "direct", "fused_all", "fused_staged", "fused_groups", "fused_mixed", "fused_pipelined"])
+@pytest.mark.parametrize("style", ["reference", "staged", "direct", "fused_all", "fused_staged", "fused_groups", "fused_mixed", "fused_pipelined", "fused_pull"])
 def test_halo_styles_single_rank_periodic(style, order):
     from tenzing_b200.models import HaloExchange, common
     h = HaloExchange(nX=20, nY=12, nZ=9, nQ=3, nGhost=3, storage_order=order)
