@@ -130,18 +130,23 @@ def main():
             torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
         return t.cpu().tolist(), launches
 
+    # implementation styles whose decision space is small enough to enumerate completely
+    SMALL = {"fused_all", "fused_staged", "fused_mixed", "fused_pipelined", "fused_pull",
+             "fused", "fused_separate"}
+
     def find_best(wl, method, styles, iters):
-        """best schedule over the given implementation styles; results are max-reduced over
-        ranks inside the benchmarker, so every rank picks the same winner"""
+        """best schedule over the given implementation styles: exhaustive DFS where the space is
+        small (a few hundred sequences), MCTS (FastMin) elsewhere.  Results are max-reduced over
+        ranks inside the benchmarker, so every rank picks the same winner."""
         if args.no_search:
             return common.fixed_schedule(wl.graph(styles[0]), wl.platform)
-        bo = common.bench_opts(n_iters=5, target_secs=0.002, max_retries=0, check_randomness=False)
+        bo = common.bench_opts(n_iters=3, target_secs=0.002, max_retries=0, check_randomness=False)
         best_seq, best_t = None, float("inf")
         for style in styles:
-            if method == "mcts":
-                res = wl.search("mcts", style=style, iters=iters, bench=bo, strategy="FastMin")
+            if style in SMALL or method == "dfs":
+                res = wl.search("dfs", style=style, bench=bo, max_seqs=1000)
             else:
-                res = wl.search("dfs", style=style, bench=bo, max_seqs=iters)
+                res = wl.search("mcts", style=style, iters=iters, bench=bo, strategy="FastMin")
             seq, br = common.best_of(res)
             if seq is not None and br.pct10 < best_t:
                 best_seq, best_t = seq, br.pct10
@@ -240,7 +245,8 @@ def main():
                        "parallelism": "3d-block " + "x".join(map(str, halo.domain.rank_grid())),
                        "l2": "256 MB flush buffer written between timed steps",
                        "search": "no search" if args.no_search else
-                       f"MCTS FastMin {args.search_iters} iters per style (6 fused styles + ChoiceOp over all 9)"},
+                       f"exhaustive DFS inside the 5 small fused styles, MCTS FastMin {args.search_iters} iters "
+                       "for fused_groups and for the ChoiceOp over all 9 styles"},
             "schedule": seq_h.names(), "correct": bool(ok_h and ok_s),
             "halo": {"us": round(us_h, 3), "bytes_out_per_rank": bytes_out, "remote_bytes_per_rank": remote,
                      "roofline_us": round(roof_h * 1e6, 3),

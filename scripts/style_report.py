@@ -35,6 +35,7 @@ def main():
     ap.add_argument("--halo-styles", default=",".join(HALO_STYLES))
     ap.add_argument("--hand", action="store_true", help="hand-written fused_groups pipelines + put-only times")
     ap.add_argument("--no-spmv", action="store_true")
+    ap.add_argument("--mixed-hand", action="store_true", help="hand schedules over the fused_mixed ops")
     args = ap.parse_args()
     rank, world, _ = init_process_group_from_env()
     comm = make_comm()
@@ -127,6 +128,25 @@ def main():
             torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
         rows.append(dict(workload=f"halo {args.nx}^3 nQ={args.nq}", style="he_packput_all alone",
                          us=round(float(t.median()) * 1e6, 2), ok=True, ops=1, n_gpus=world))
+    if args.mixed_hand:
+        g = halo.graph("flat:fused_mixed")
+        B = lambda n, st: _C.BoundGpuOp(g.find_name(n), st)  # noqa: E731
+        hands = {
+            "thin first, unpack beside thick put": [
+                g.start(), B("he_packput_thin", 0), _C.CudaEventRecord(0, 0), B("he_put_thick", 0),
+                _C.CudaStreamWaitEvent(1, 0), B("he_waitunpack_thin", 1), B("he_wait_thick", 0),
+                _C.CudaEventRecord(1, 0), _C.CudaEventRecord(2, 1), _C.CudaEventSync(1),
+                _C.CudaEventSync(2), g.finish()],
+            "both puts concurrent (DFS best)": [
+                g.start(), B("he_put_thick", 0), B("he_packput_thin", 1), B("he_wait_thick", 0),
+                B("he_waitunpack_thin", 1), _C.CudaEventRecord(1, 0), _C.CudaEventRecord(2, 1),
+                _C.CudaEventSync(1), _C.CudaEventSync(2), g.finish()],
+        }
+        for label, ops in hands.items():
+            us, ok = measure_seq(halo, _C.Sequence(ops))
+            rows.append(dict(workload=f"halo {args.nx}^3 nQ={args.nq}", style="mixed: " + label,
+                             us=round(us, 2), ok=ok, ops=len(ops), n_gpus=world,
+                             items_per_block=os.environ.get("TZB_ITEMS_PER_BLOCK", "resident")))
     del halo
     torch.cuda.empty_cache()
     cases = [] if args.no_spmv else [("spmv band", args.spmv_n, None)]

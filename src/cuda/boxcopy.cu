@@ -13,6 +13,7 @@
 #include <atomic>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -396,12 +397,28 @@ int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t
   // launched from another stream can always become resident next to them
   const bool waits = (info->reserved & 2) != 0, ordered = (info->reserved & 4) != 0;
   const bool vec = (info->reserved & 8) != 0;
+  // Grid size.  Every block works through kItemsPerBlock (4, TZB_ITEMS_PER_BLOCK overrides;
+  // 0 = a resident grid that strides over all items) work items and retires: with short-lived
+  // blocks a kernel launched from another stream gets SM slots as blocks retire, which is what
+  // lets e.g. the unpack of early regions run beside the put of later ones (measured: 288 ->
+  // 244 us for the 8-GPU exchange, profiles/README.md).  Ordered plans always use a resident
+  // grid of half the SM slots: their consumer may spin before the local producer has finished,
+  // so the producer must be guaranteed a place next to it.
+  static const int itemsPerBlock = [] {
+    const char *e = std::getenv("TZB_ITEMS_PER_BLOCK");
+    return e ? std::max(0, std::atoi(e)) : 4;
+  }();
+  auto grid = [&](int cap) {
+    if (itemsPerBlock > 0 && !ordered)
+      return std::max(1, (info->nItems + itemsPerBlock - 1) / itemsPerBlock);
+    return std::min(info->nItems, cap);
+  };
   const int anySignal = info->reserved & 1;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   unsigned *ctr = static_cast<unsigned *>(scratch);
   ++g_launches;
   if (ordered) {
-    const int blocks = std::min(info->nItems, kSMs * (kBlocksPerSM / 2));
+    const int blocks = grid(kSMs * (kBlocksPerSM / 2));
     if (info->elemSize == 8)
       box_copy_sync_kernel<double, kBlocksPerSM / 2><<<blocks, kThreads, 0, s>>>(
           boxes, items, info->nItems, info->nBoxes, anySignal, epoch, ctr);
@@ -410,7 +427,7 @@ int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t
           boxes, items, info->nItems, info->nBoxes, anySignal, epoch, ctr);
   } else if (waits) {
     // strictly ordered after the local producers (graph edge): full occupancy is safe
-    const int blocks = std::min(info->nItems, kSMs * kBlocksPerSM);
+    const int blocks = grid(kSMs * kBlocksPerSM);
     if (info->elemSize == 8)
       box_copy_sync_kernel<double, kBlocksPerSM><<<blocks, kThreads, 0, s>>>(
           boxes, items, info->nItems, info->nBoxes, anySignal, epoch, ctr);
@@ -418,7 +435,7 @@ int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t
       box_copy_sync_kernel<float, kBlocksPerSM><<<blocks, kThreads, 0, s>>>(
           boxes, items, info->nItems, info->nBoxes, anySignal, epoch, ctr);
   } else {
-    const int blocks = std::min(info->nItems, kSMs * kBlocksPerSM);
+    const int blocks = grid(kSMs * kBlocksPerSM);
     if (info->elemSize == 8 && vec)
       box_copy_kernel<double, true><<<blocks, kThreads, 0, s>>>(boxes, items, info->nItems,
                                                                 info->nBoxes, anySignal, epoch, ctr);
