@@ -58,6 +58,22 @@ struct CPU {
   int id = 0;
 };
 
+// Placeholders for "ops own values" (reference keeps the same unused skeletons,
+// platform.hpp:91-128): a value an op produces or consumes, as a scalar or an array.
+struct IValue {
+  virtual ~IValue() = default;
+  virtual size_t bytes() const = 0;
+};
+template <typename T> struct ScalarValue : IValue {
+  T value{};
+  size_t bytes() const override { return sizeof(T); }
+};
+template <typename T> struct ArrayValue : IValue {
+  T *data = nullptr;
+  size_t count = 0;
+  size_t bytes() const override { return count * sizeof(T); }
+};
+
 template <typename T> class Bijection {
   std::map<T, T> fwd_, rev_;
 

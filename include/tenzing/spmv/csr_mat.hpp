@@ -10,6 +10,7 @@
 
 #include <algorithm>
 #include <cstdint>
+#include <cstdio>
 #include <map>
 #include <numeric>
 #include <vector>
@@ -29,7 +30,13 @@ template <typename T> struct ArrayView {
 #ifdef __CUDACC__
   __host__ __device__
 #endif
-  T &operator()(int64_t i) const { return data_[i]; }
+  T &operator()(int64_t i) const {
+#ifdef TENZING_RUNTIME_CHECK_BOUNDS
+    // reference: spmv/array.hpp:36-43 (always on there; opt-in here, it costs registers)
+    if (i < 0 || i >= size_) printf("ArrayView: index %lld out of range [0, %lld)\n", (long long)i, (long long)size_);
+#endif
+    return data_[i];
+  }
 #ifdef __CUDACC__
   __host__ __device__
 #endif

@@ -118,6 +118,46 @@ void bind_workloads(py::module_ &m) {
       .def("alloc", &SymmetricHeap::alloc, py::arg("bytes"), py::arg("align") = 256)
       .def("zero", &SymmetricHeap::zero, py::arg("offset") = 0, py::arg("bytes") = size_t(-1));
 
+  // ---- host-posted P2P ops (the MPI-shaped op library) ----
+  py::class_<P2PTransport, std::shared_ptr<P2PTransport>>(m, "P2PTransport")
+      .def(py::init<bool>(), py::arg("null") = false);
+  py::class_<Request, RequestPtr>(m, "Request").def(py::init<>()).def("wait", &Request::wait);
+  m.def("Isend", [](uintptr_t buf, size_t bytes, uintptr_t peerBuf, uintptr_t peerFlag, RequestPtr req,
+                    std::shared_ptr<P2PTransport> tr, const std::string &name) {
+    Isend::Args a;
+    a.buf = ptr<void>(buf), a.bytes = bytes, a.peerBuf = ptr<void>(peerBuf);
+    a.peerFlag = ptr<uint64_t>(peerFlag), a.request = std::move(req);
+    return std::static_pointer_cast<BoundOp>(std::make_shared<Isend>(a, std::move(tr), name));
+  }, py::arg("buf"), py::arg("bytes"), py::arg("peer_buf"), py::arg("peer_flag"), py::arg("request"),
+     py::arg("transport"), py::arg("name"));
+  m.def("Irecv", [](uintptr_t flag, RequestPtr req, std::shared_ptr<P2PTransport> tr, const std::string &name) {
+    Irecv::Args a;
+    a.flag = ptr<uint64_t>(flag), a.request = std::move(req);
+    return std::static_pointer_cast<BoundOp>(std::make_shared<Irecv>(a, std::move(tr), name));
+  }, py::arg("flag"), py::arg("request"), py::arg("transport"), py::arg("name"));
+  m.def("Wait", [](RequestPtr req, const std::string &name) {
+    return std::static_pointer_cast<BoundOp>(std::make_shared<Wait>(std::move(req), name));
+  });
+  m.def("MultiWait", [](const std::vector<RequestPtr> &reqs, const std::string &name) {
+    auto w = std::make_shared<MultiWait>(name);
+    for (const auto &r : reqs) w->add_request(r);
+    return std::static_pointer_cast<BoundOp>(w);
+  });
+  m.def("OwningWaitall", [](const std::vector<RequestPtr> &reqs, const std::string &name) {
+    auto w = std::make_shared<OwningWaitall>(name);
+    for (const auto &r : reqs) w->add_request(r);
+    return std::static_pointer_cast<BoundOp>(w);
+  });
+  m.def("Ialltoallv", [](uintptr_t sendbuf, const std::vector<size_t> &offs, const std::vector<size_t> &bytes,
+                         const std::vector<uintptr_t> &peerBufs, const std::vector<uintptr_t> &peerFlags,
+                         RequestPtr req, std::shared_ptr<P2PTransport> tr, const std::string &name) {
+    Ialltoallv::Args a;
+    a.sendbuf = ptr<void>(sendbuf), a.sendOffsets = offs, a.sendBytes = bytes, a.request = std::move(req);
+    for (uintptr_t p : peerBufs) a.peerBufs.push_back(ptr<void>(p));
+    for (uintptr_t p : peerFlags) a.peerFlags.push_back(ptr<uint64_t>(p));
+    return std::static_pointer_cast<BoundOp>(std::make_shared<Ialltoallv>(a, std::move(tr), name));
+  });
+
   // ---- NUMA-aware pinned staging ----
   py::class_<PinnedPool>(m, "PinnedPool")
       .def(py::init<int>(), py::arg("cuda_device") = -1)

@@ -1,0 +1,93 @@
+#include "tenzing/ops_comm.hpp"
+
+namespace tenzing {
+
+P2PTransport::P2PTransport(bool nullDevice) : null_(nullDevice) {
+  if (null_) return;
+  CUDA_RUNTIME(cudaStreamCreateWithFlags(&send_, cudaStreamNonBlocking));
+  CUDA_RUNTIME(cudaStreamCreateWithFlags(&recv_, cudaStreamNonBlocking));
+}
+
+P2PTransport::~P2PTransport() {
+  if (send_) cudaStreamDestroy(send_);
+  if (recv_) cudaStreamDestroy(recv_);
+}
+
+Request::~Request() {
+  if (sent) cudaEventDestroy(sent);
+}
+
+void Request::wait() {
+  if (!transport || transport->is_null()) return;
+  if (kind == Kind::Send) {
+    if (sent) CUDA_RUNTIME(cudaEventSynchronize(sent));
+  } else if (kind == Kind::Recv) {
+    CUDA_RUNTIME(cudaError_t(tzb_flags_wait(flag, 1, epoch, transport->recv_stream())));
+    CUDA_RUNTIME(cudaStreamSynchronize(transport->recv_stream()));
+  }
+  kind = Kind::None;
+}
+
+static void mark_sent(Request &r, const std::shared_ptr<P2PTransport> &tr, uint64_t epoch) {
+  r.kind = Request::Kind::Send;
+  r.transport = tr;
+  r.epoch = epoch;
+  if (!r.sent) CUDA_RUNTIME(cudaEventCreateWithFlags(&r.sent, cudaEventDisableTiming));
+  CUDA_RUNTIME(cudaEventRecord(r.sent, tr->send_stream()));
+}
+
+void Isend::run(Platform &plat) {
+  if (tr_->is_null() || plat.is_null()) return;
+  if (args_.bytes)
+    CUDA_RUNTIME(cudaMemcpyAsync(args_.peerBuf, args_.buf, args_.bytes, cudaMemcpyDeviceToDevice,
+                                 tr_->send_stream()));
+  TzbFlagList l;
+  l.n = 1;
+  l.flag[0] = args_.peerFlag;
+  CUDA_RUNTIME(cudaError_t(tzb_flags_signal(&l, plat.epoch(), tr_->send_stream())));
+  if (args_.request) mark_sent(*args_.request, tr_, plat.epoch());
+}
+
+void Irecv::run(Platform &plat) {
+  if (!args_.request) return;
+  args_.request->kind = Request::Kind::Recv;
+  args_.request->transport = tr_;
+  args_.request->flag = args_.flag;
+  args_.request->epoch = plat.epoch();
+}
+
+void Wait::run(Platform &plat) {
+  if (plat.is_null() || !request_) return;
+  request_->wait();
+}
+
+void OwningWaitall::run(Platform &plat) {
+  if (plat.is_null()) return;
+  for (auto &r : reqs_) r->wait();
+}
+
+void MultiWait::run(Platform &plat) {
+  if (plat.is_null()) return;
+  for (auto &r : reqs_) r->wait();
+}
+
+void Ialltoallv::run(Platform &plat) {
+  if (tr_->is_null() || plat.is_null()) return;
+  const size_t n = args_.peerBufs.size();
+  for (size_t p = 0; p < n; ++p) {
+    if (args_.sendBytes[p])
+      CUDA_RUNTIME(cudaMemcpyAsync(args_.peerBufs[p],
+                                   static_cast<const char *>(args_.sendbuf) + args_.sendOffsets[p],
+                                   args_.sendBytes[p], cudaMemcpyDeviceToDevice, tr_->send_stream()));
+  }
+  for (size_t p0 = 0; p0 < n; p0 += 32) {
+    TzbFlagList l;
+    l.n = 0;
+    for (size_t p = p0; p < n && p < p0 + 32; ++p)
+      if (args_.peerFlags[p]) l.flag[l.n++] = args_.peerFlags[p];
+    CUDA_RUNTIME(cudaError_t(tzb_flags_signal(&l, plat.epoch(), tr_->send_stream())));
+  }
+  if (args_.request) mark_sent(*args_.request, tr_, plat.epoch());
+}
+
+} // namespace tenzing

@@ -98,3 +98,60 @@ def test_mcts_search_on_device_halo():
     h.fill()
     h.run(seq)
     assert h.check()
+
+
+def test_host_posted_p2p_ops_in_a_searched_graph():
+    """Isend / Irecv / Wait (reference: ops_mpi.hpp) over the peer-memory transport: a producer
+    kernel fills a buffer, the host posts the send to "the peer" (this rank itself), the receive
+    completes through the flag, a consumer kernel reads the landed data.  The solver must insert
+    the GPU->CPU sync before the Isend and nothing after the Wait."""
+    import tenzing_b200 as tz
+    from tenzing_b200 import _C
+    from tenzing_b200.utils.tensor import device_tensor
+    comm = _C.SelfComm()
+    heap = _C.SymmetricHeap(comm, 1 << 20)
+    n = 4096
+    src = device_tensor(heap.local_ptr() + heap.alloc(n * 8), (n,), torch.float64, owner=heap)
+    dst = device_tensor(heap.peer_ptr(0) + heap.alloc(n * 8), (n,), torch.float64, owner=heap)
+    flag_off = heap.alloc(8)
+    out = torch.zeros(n, dtype=torch.float64, device="cuda")
+    tr = _C.P2PTransport()
+    sreq, rreq = _C.Request(), _C.Request()
+    plat = tz.Platform.make_n_streams(2)
+
+    def produce(stream):
+        with torch.cuda.stream(torch.cuda.ExternalStream(stream)):
+            src.copy_(torch.arange(n, dtype=torch.float64, device="cuda") + float(plat.epoch()))
+
+    def consume(stream):
+        with torch.cuda.stream(torch.cuda.ExternalStream(stream)):
+            out.copy_(dst * 2)
+
+    fill = tz.PyGpuOp("fill", produce)
+    use = tz.PyGpuOp("use", consume)
+    isend = _C.Isend(src.data_ptr(), n * 8, dst.data_ptr(), heap.peer_ptr(0) + flag_off, sreq, tr, "isend")
+    irecv = _C.Irecv(heap.local_ptr() + flag_off, rreq, tr, "irecv")
+    wsend, wrecv = _C.Wait(sreq, "wait_send"), _C.Wait(rreq, "wait_recv")
+    g = tz.Graph()
+    g.start_then(fill)
+    g.then(fill, isend)
+    g.start_then(irecv)
+    g.then(isend, wsend)
+    g.then(isend, wrecv)
+    g.then(irecv, wrecv)
+    g.then(irecv, wsend)
+    g.then(wrecv, use)
+    g.then_finish(use)
+    g.then_finish(wsend)
+    seqs = tz.dfs.get_all_sequences(g, plat, 50, True)
+    assert seqs
+    for seq in seqs[:10]:
+        names = seq.names()
+        i = names.index("isend")
+        assert any(o.kind() == "CudaEventSync" for o in list(seq)[:i])  # fill -> isend needs the host
+        plat.provision_events(seq)
+        seq.run(plat)
+        plat.synchronize()
+        torch.cuda.synchronize()
+        exp = (torch.arange(n, dtype=torch.float64, device="cuda") + float(plat.epoch())) * 2
+        assert torch.equal(out, exp)
