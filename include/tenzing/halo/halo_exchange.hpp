@@ -114,7 +114,8 @@ public:
 
   // grid geometry, ghost cells included
   Dim3<int> extent() const { return ext_; }          // cells per dimension incl. ghosts
-  size_t row_elems() const { return rowElems_; }     // XYZQ: padded row length in elements
+  size_t row_elems() const { return rowElems_; }     // padded row length in elements
+  size_t x_origin() const { return xOrigin_; }       // elements before cell x = 0 in every row
   size_t grid_elems() const { return gridElems_; }
   size_t grid_bytes() const { return gridElems_ * size_t(args_.elemSize); }
   void *grid() const { return heap_->at<char>(rank(), gridOff_); }
@@ -154,7 +155,7 @@ private:
   std::unique_ptr<SymmetricHeap> heap_;
   std::vector<Dim3<int>> dirs_;
   Dim3<int> ext_;
-  size_t rowElems_ = 0, gridElems_ = 0;
+  size_t rowElems_ = 0, gridElems_ = 0, xOrigin_ = 0;
   size_t gridOff_ = 0, sendOff_ = 0, recvOff_[2] = {0, 0}, flagOff_ = 0;
   std::array<int, 27> dirIndex_{};
   std::array<size_t, 27> slotOff_{}; // element offset of each direction's slot inside a staging area

@@ -202,6 +202,7 @@ void bind_workloads(py::module_ &m) {
       .def("size", &Domain::size)
       .def("extent", [](const Domain &d) { auto e = d.extent(); return std::vector<int>{e.x, e.y, e.z}; })
       .def("row_elems", &Domain::row_elems)
+      .def("x_origin", &Domain::x_origin)
       .def("grid_elems", &Domain::grid_elems)
       .def("grid_bytes", &Domain::grid_bytes)
       .def("grid_ptr", [](const Domain &d) { return reinterpret_cast<uintptr_t>(d.grid()); })

@@ -85,8 +85,14 @@ Domain::Domain(std::shared_ptr<Communicator> comm, const Args &args, SymmetricHe
   const size_t es = size_t(args_.elemSize);
   const size_t pitch = args_.pitch ? args_.pitch : es;
   if (pitch % es) THROW_RUNTIME("pitch must be a multiple of the element size");
-  const size_t rowUnpadded =
-      (args_.storageOrder == StorageOrder::XYZQ ? size_t(ext_.x) : size_t(ext_.x) * args_.nQ) * es;
+  // Rows are laid out so that the first INTERIOR cell of every row is 16-byte aligned: the
+  // 4 KB interior runs (y/z faces, staging copies) can then be moved with 16-byte accesses on
+  // both sides and cross NVLink as whole sectors, and each 24-byte ghost / send piece of an
+  // x-face sits inside one 32-byte sector, next to its partner in the same 128-byte line.
+  const size_t cellElems = args_.storageOrder == StorageOrder::XYZQ ? 1 : size_t(args_.nQ);
+  xOrigin_ = 0;
+  while (((xOrigin_ + size_t(g) * cellElems) * es) % 16) ++xOrigin_;
+  const size_t rowUnpadded = (xOrigin_ + size_t(ext_.x) * cellElems) * es;
   rowElems_ = round_up_sz(rowUnpadded, pitch) / es;
   gridElems_ = rowElems_ * size_t(ext_.y) * size_t(ext_.z) *
                (args_.storageOrder == StorageOrder::XYZQ ? size_t(args_.nQ) : size_t(1));
@@ -125,7 +131,7 @@ std::array<int64_t, 4> Domain::strides() const {
 
 size_t Domain::index(int x, int y, int z, int q) const {
   const auto s = strides();
-  return size_t(x * s[0] + y * s[1] + z * s[2] + q * s[3]);
+  return xOrigin_ + size_t(x * s[0] + y * s[1] + z * s[2] + q * s[3]);
 }
 
 Dim3<int> Domain::region_extent(const Dim3<int> &d) const {
@@ -243,7 +249,8 @@ TzbBox make_box(const Domain &dom, const void *src, Side srcSide, const Dim3<int
   TzbBox b;
   std::memset(&b, 0, sizeof(b));
   auto grid_base = [&](const void *p, const Dim3<int> &o) {
-    return static_cast<const char *>(p) + size_t(o.x * gs[0] + o.y * gs[1] + o.z * gs[2]) * es;
+    return static_cast<const char *>(p) +
+           (dom.x_origin() + size_t(o.x * gs[0] + o.y * gs[1] + o.z * gs[2])) * es;
   };
   b.src = srcSide == Side::Grid ? grid_base(src, srcOff) : static_cast<const char *>(src);
   b.dst = const_cast<char *>(dstSide == Side::Grid ? grid_base(dst, dstOff) : static_cast<const char *>(dst));

@@ -50,9 +50,10 @@ class HaloExchange:
         """view of the grid as [nQ, EZ, EY, EX] (a strided view for QXYZ)"""
         ex, ey, ez = self.domain.extent()
         nq = self.args.nQ
+        o = self.domain.x_origin()  # rows start with `o` padding elements (alignment)
         if self.args.storageOrder == "XYZQ":
-            return self.grid[:, :, :, :ex]
-        return self.grid[:, :, :ex * nq].reshape(ez, ey, ex, nq).permute(3, 0, 1, 2)
+            return self.grid[:, :, :, o:o + ex]
+        return self.grid[:, :, o:o + ex * nq].unflatten(2, (ex, nq)).permute(3, 0, 1, 2)
 
     def _global_pattern(self, wrap):
         """value of every cell (ghosts included) as if the global periodic field were known"""

@@ -89,7 +89,10 @@ def test_spmv_graphs_have_the_reference_shape():
 def test_halo_geometry_and_graph_structure():
     h = HaloExchange(nX=8, nY=6, nZ=4, nQ=2, nGhost=2, host=True)
     d = h.domain
-    assert d.extent() == [12, 10, 8] and d.row_elems() == 16  # 12 doubles padded to 128 B
+    # 12 cells + 0 origin elements (ghost radius 2 is already 16-byte aligned), padded to 128 B
+    assert d.extent() == [12, 10, 8] and d.row_elems() == 16 and d.x_origin() == 0
+    odd = HaloExchange(nX=8, nQ=1, nGhost=3, host=True).domain
+    assert odd.x_origin() == 1 and (odd.index(3, 0, 0, 0) * 8) % 16 == 0
     assert len(d.dirs()) == 26
     # faces + edges + corners, all quantities, 8 bytes each
     faces = 2 * (2 * 6 * 4 + 8 * 2 * 4 + 8 * 6 * 2)
