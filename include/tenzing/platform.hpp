@@ -27,6 +27,7 @@
 namespace tenzing {
 
 class Communicator;
+class DeviceBarrier;
 
 #define TENZING_ID_HANDLE(NAME)                                                                    \
   class NAME {                                                                                     \
@@ -170,6 +171,7 @@ private:
   std::unique_ptr<CudaEventPool> pool_;
   std::shared_ptr<Communicator> comm_;
   uint64_t epoch_ = 0;
+  std::shared_ptr<DeviceBarrier> deviceBarrier_;
 
 public:
   std::vector<Stream> streams_; // the streams decisions may bind GPU ops to
@@ -217,6 +219,10 @@ public:
   uint64_t epoch() const { return epoch_; }
   uint64_t next_epoch() { return ++epoch_; }
   void set_epoch(uint64_t e) { epoch_ = e; }
+
+  // optional GPU-side all-rank barrier the device-timed benchmarkers use to line up their start
+  void set_device_barrier(std::shared_ptr<DeviceBarrier> b) { deviceBarrier_ = std::move(b); }
+  const std::shared_ptr<DeviceBarrier> &device_barrier() const { return deviceBarrier_; }
 
   // block the host until every stream of the platform is idle
   void synchronize() const;

@@ -3,6 +3,7 @@
 #pragma once
 
 #include "tenzing/argparse.hpp"
+#include "tenzing/cuda/device_barrier.hpp"
 #include "tenzing/driver.hpp"
 #include "tenzing/halo/halo_exchange.hpp"
 
@@ -56,6 +57,7 @@ inline int main_impl(int argc, char **argv, const char *defaultStrategy) {
     }
     Platform plat = Platform::make_n_streams(streams, ctx.comm,
                                              ctx.haveGpu ? Platform::Device::Cuda : Platform::Device::Null);
+    if (ctx.haveGpu && ctx.size > 1) plat.set_device_barrier(std::make_shared<DeviceBarrier>(ctx.comm));
     DeviceBenchmarker bench;
     mcts::Opts opts;
     opts.nIters = size_t(mctsIters);

@@ -9,6 +9,7 @@
 #include "op_cast.hpp"
 #include <pybind11/stl.h>
 
+#include "tenzing/cuda/device_barrier.hpp"
 #include "tenzing/tenzing.hpp"
 
 namespace py = pybind11;
@@ -275,6 +276,13 @@ PYBIND11_MODULE(_C, m) {
       .def("comm", &Platform::comm_ptr)
       .def("epoch", &Platform::epoch)
       .def("next_epoch", &Platform::next_epoch)
+      .def("enable_device_barrier",
+           [](Platform &p) {
+             if (!p.is_null() && !p.device_barrier())
+               p.set_device_barrier(std::make_shared<DeviceBarrier>(p.comm_ptr()));
+           },
+           py::call_guard<py::gil_scoped_release>(),
+           "collective: line up measurement starts with a GPU-side all-rank barrier")
       .def("synchronize", &Platform::synchronize, py::call_guard<py::gil_scoped_release>());
 
   // ---- ops ----
@@ -604,6 +612,7 @@ PYBIND11_MODULE(_C, m) {
             CUDA_RUNTIME(cudaMemsetAsync(reinterpret_cast<void *>(flushPtr), i & 0xff, flushBytes, s0));
           plat.synchronize();
           plat.comm().barrier();
+          if (plat.device_barrier()) plat.device_barrier()->enqueue(s0);
           CUDA_RUNTIME(cudaEventRecord(start, s0));
           for (int k = 1; k < plat.num_streams(); ++k)
             CUDA_RUNTIME(cudaStreamWaitEvent(plat.cuda_stream(plat.streams_[size_t(k)]), start, 0));

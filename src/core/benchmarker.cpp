@@ -10,6 +10,7 @@
 
 #include "tenzing/communicator.hpp"
 #include "tenzing/cuda/cuda_runtime.hpp"
+#include "tenzing/cuda/device_barrier.hpp"
 #include "tenzing/numeric.hpp"
 #include "tenzing/operation_serdes.hpp"
 #include "tenzing/randomness.hpp"
@@ -131,6 +132,7 @@ double DeviceBenchmarker::timed_run(Sequence<BoundOp> &order, Platform &plat, si
   plat.comm().barrier();
   // start: recorded on stream 0, every other stream starts behind it
   cudaStream_t s0 = plat.cuda_stream(plat.streams_[0]);
+  if (plat.device_barrier()) plat.device_barrier()->enqueue(s0); // line the ranks up on the GPUs
   CUDA_RUNTIME(cudaEventRecord(starts_[0], s0));
   for (int i = 1; i < ns; ++i)
     CUDA_RUNTIME(cudaStreamWaitEvent(plat.cuda_stream(plat.streams_[i]), starts_[0], 0));

@@ -3,7 +3,10 @@ from .. import _C
 
 
 def make_platform(comm, n_streams=2, null=False):
-    return _C.Platform.make_n_streams(n_streams, comm, null)
+    plat = _C.Platform.make_n_streams(n_streams, comm, null)
+    if not null and comm.size() > 1:
+        plat.enable_device_barrier()  # measurements start together on all GPUs
+    return plat
 
 
 def bench_opts(n_iters=50, target_secs=0.01, max_retries=2, check_randomness=True):
