@@ -103,7 +103,8 @@ def main():
     ap.add_argument("--nq", type=int, default=3)
     ap.add_argument("--spmv-n", type=int, default=1_000_000)
     ap.add_argument("--search-iters", type=int, default=30)
-    ap.add_argument("--no-search", action="store_true", help="use the fused_staged schedule as is")
+    ap.add_argument("--no-search", action="store_true", help="use a fixed fused schedule as is")
+    ap.add_argument("--search-budget", type=float, default=40.0, help="wall-clock seconds for the halo search")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)
@@ -134,17 +135,27 @@ def main():
     SMALL = {"fused_all", "fused_staged", "fused_mixed", "fused_pipelined", "fused_pull",
              "fused", "fused_separate"}
 
-    def find_best(wl, method, styles, iters):
+    def find_best(wl, method, styles, iters, budget_s):
         """best schedule over the given implementation styles: exhaustive DFS where the space is
         small (a few hundred sequences), MCTS (FastMin) elsewhere.  Results are max-reduced over
-        ranks inside the benchmarker, so every rank picks the same winner."""
+        ranks inside the benchmarker, so every rank picks the same winner.  The search is set-up,
+        not the timed region, but it is kept inside a wall-clock budget: once rank 0 sees the
+        budget spent, the remaining styles are skipped (all ranks agree through a broadcast)."""
         if args.no_search:
             return common.fixed_schedule(wl.graph(styles[0]), wl.platform)
         bo = common.bench_opts(n_iters=3, target_secs=0.002, max_retries=0, check_randomness=False)
         best_seq, best_t = None, float("inf")
+        t0 = time.time()
         for style in styles:
+            spent = torch.tensor([time.time() - t0], dtype=torch.float64, device=dev)
+            if world > 1:
+                torch.distributed.broadcast(spent, src=0)
+            if best_seq is not None and float(spent.item()) > budget_s:
+                break
+            left = max(2.0, budget_s - float(spent.item()))
             if style in SMALL or method == "dfs":
-                res = wl.search("dfs", style=style, bench=bo, max_seqs=1000)
+                # ~6 ms per evaluated sequence: never enumerate more than the budget allows
+                res = wl.search("dfs", style=style, bench=bo, max_seqs=int(min(1000, left / 0.006)))
             else:
                 res = wl.search("mcts", style=style, iters=iters, bench=bo, strategy="FastMin")
             seq, br = common.best_of(res)
@@ -160,8 +171,9 @@ def main():
     # the search: MCTS inside every fused implementation style (their decision spaces are small
     # enough to cover well) plus MCTS over the ChoiceOp of ALL styles, reference structure
     # included; the fastest sequence found anywhere is the schedule that gets timed
-    fused = ["fused_all", "fused_staged", "fused_mixed", "fused_pipelined", "fused_groups", "fused_pull"]
-    seq_h = find_best(halo, "mcts", fused + ["choice"], args.search_iters)
+    # most promising styles first, so a spent budget drops the least promising ones
+    fused = ["fused_mixed", "fused_staged", "fused_all", "fused_pipelined", "fused_groups", "fused_pull"]
+    seq_h = find_best(halo, "mcts", fused + ["choice"], args.search_iters, args.search_budget)
     halo.fill()
     comm.barrier()
     halo.run(seq_h)
@@ -205,7 +217,7 @@ def main():
     # ---------------- secondary: distributed SpMV ----------------
     spmv = DistributedSpMV(comm=comm, n=args.spmv_n, nnz_per_row=10)
     spmv.fill()
-    seq_s = find_best(spmv, "dfs", ["fused", "fused_separate", "fused_all"], 64)
+    seq_s = find_best(spmv, "dfs", ["fused", "fused_all", "fused_separate"], 64, args.search_budget / 2)
     spmv.fill()
     comm.barrier()
     spmv.run(seq_s)

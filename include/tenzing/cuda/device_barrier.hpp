@@ -7,6 +7,9 @@
 
 #include <memory>
 
+#include <cuda_runtime_api.h>
+
+#include "tenzing/cuda/cuda_runtime.hpp"
 #include "tenzing/cuda/symmetric_heap.hpp"
 #include "tenzing_b200.h"
 

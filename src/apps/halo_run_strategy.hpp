@@ -57,7 +57,7 @@ inline int main_impl(int argc, char **argv, const char *defaultStrategy) {
     }
     Platform plat = Platform::make_n_streams(streams, ctx.comm,
                                              ctx.haveGpu ? Platform::Device::Cuda : Platform::Device::Null);
-    if (ctx.haveGpu && ctx.size > 1) plat.set_device_barrier(std::make_shared<DeviceBarrier>(ctx.comm));
+    if (ctx.haveGpu && ctx.size > 1 && std::getenv("TENZING_DEVICE_BARRIER")) plat.set_device_barrier(std::make_shared<DeviceBarrier>(ctx.comm));
     DeviceBenchmarker bench;
     mcts::Opts opts;
     opts.nIters = size_t(mctsIters);

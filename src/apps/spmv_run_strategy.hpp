@@ -69,7 +69,7 @@ template <typename Scalar> int run(const Config &c, driver::Context &ctx, bool m
   Graph<OpBase> g = make_graph<Scalar>(spmv, c.style);
   Platform plat = Platform::make_n_streams(c.streams, ctx.comm,
                                            ctx.haveGpu ? Platform::Device::Cuda : Platform::Device::Null);
-  if (ctx.haveGpu && ctx.size > 1) plat.set_device_barrier(std::make_shared<DeviceBarrier>(ctx.comm));
+  if (ctx.haveGpu && ctx.size > 1 && std::getenv("TENZING_DEVICE_BARRIER")) plat.set_device_barrier(std::make_shared<DeviceBarrier>(ctx.comm));
   DeviceBenchmarker bench;
   Benchmark::Opts bo;
   bo.nIters = size_t(c.benchIters);

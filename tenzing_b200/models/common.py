@@ -1,11 +1,14 @@
 """Shared search / replay helpers for the workload front ends."""
+import os
+
 from .. import _C
 
 
 def make_platform(comm, n_streams=2, null=False):
     plat = _C.Platform.make_n_streams(n_streams, comm, null)
-    if not null and comm.size() > 1:
-        plat.enable_device_barrier()  # measurements start together on all GPUs
+    # opt-in: line up measurement starts with a GPU-side all-rank barrier (see DeviceBarrier)
+    if not null and comm.size() > 1 and os.environ.get("TENZING_DEVICE_BARRIER") == "1":
+        plat.enable_device_barrier()
     return plat
 
 
