@@ -260,6 +260,9 @@ public:
   }
 };
 
+template <typename Scalar>
+TzbGatherPutArgs make_put_args(const RowPartSpmv<Scalar> &s, St<Scalar> style, int parity);
+
 // gather fused with the put into every peer's rx, then one flag per rank
 template <typename Scalar> class PackPut : public GpuOp {
   SpmvPtr<Scalar> s_;
@@ -272,25 +275,7 @@ public:
   void run(cudaStream_t) override { THROW_RUNTIME("PackPut needs the platform epoch"); }
   void run(Platform &plat, cudaStream_t st) override {
     if (s_->null_device() || plat.is_null()) return;
-    const int np = s_->size(), me = s_->rank(), parity = int(plat.epoch() & 1);
-    TzbGatherPutArgs a;
-    std::memset(&a, 0, sizeof(a));
-    a.nPeers = np;
-    // one slot per rank, in rank order; ranks that get no data still get the flag so the
-    // handshake is all-to-all and nobody can run more than one epoch ahead of anybody
-    size_t k = 0;
-    const auto &sp = s_->send_params();
-    int displ = 0;
-    for (int r = 0; r < np; ++r) {
-      a.displ[r] = displ;
-      a.peerFlag[r] = s_->flag(r, style_, me);
-      if (k < sp.size() && sp[k].peer == r) {
-        a.peerDst[r] = s_->rx(r, parity) + sp[k].dstDispl;
-        displ += sp[k].count;
-        ++k;
-      }
-    }
-    a.displ[np] = displ;
+    const TzbGatherPutArgs a = make_put_args(*s_, style_, int(plat.epoch() & 1));
     CUDA_RUNTIME(k_gather_put(&a, s_->x_send_idx(), s_->lx(), plat.epoch(), s_->counter(), st));
   }
 };
