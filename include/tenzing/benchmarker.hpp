@@ -107,6 +107,34 @@ public:
                               const Benchmark::Opts &opts = Benchmark::Opts()) override;
 };
 
+// Timeline simulation of a sequence: a "fake backend" like the reference's CSV replay
+// (benchmarker.hpp:43-57), but predictive.  The host issues ops one after the other
+// (`launchCost` each; CudaEventSync blocks it), every stream executes its ops in order, a
+// CudaEventRecord captures the time its stream reaches it, a CudaStreamWaitEvent delays its
+// stream until that time.  Op durations come from a table keyed by op name (e.g. measured by
+// scripts/microbench_halo.py).  Lets search strategies be studied and tested without a GPU.
+class SimBenchmarker : public Benchmarker {
+public:
+  struct Model {
+    std::unordered_map<std::string, double> gpuSeconds; // GPU op name -> duration
+    std::unordered_map<std::string, double> cpuSeconds; // CPU op name -> host time
+    double defaultGpuSeconds = 10e-6;
+    double defaultCpuSeconds = 0;
+    double launchCost = 3e-6; // host time to issue any op
+    // when two GPU ops overlap in time their durations are stretched by this factor per
+    // concurrent op beyond the first (0 = perfect overlap, 1 = they share the machine equally)
+    double contention = 0;
+  };
+  explicit SimBenchmarker(Model m) : model_(std::move(m)) {}
+  // simulated wall time of one execution of the sequence
+  double simulate(const Sequence<BoundOp> &order) const;
+  Benchmark::Result benchmark(Sequence<BoundOp> &order, Platform &plat,
+                              const Benchmark::Opts &opts = Benchmark::Opts()) override;
+
+private:
+  Model model_;
+};
+
 // one CSV row: idx|pct01|pct10|pct50|pct90|pct99|stddev|<op json>|...
 std::string csv_row(size_t idx, const Benchmark::Result &r, const Sequence<BoundOp> &seq);
 

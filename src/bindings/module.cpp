@@ -594,6 +594,21 @@ PYBIND11_MODULE(_C, m) {
       }, py::return_value_policy::take_ownership)
       .def("num_rows", [](const CsvBenchmarker &b) { return b.rows().size(); });
   py::class_<PyBenchmarker, Benchmarker>(m, "PyBenchmarker").def(py::init<py::object>());
+  py::class_<SimBenchmarker, Benchmarker>(m, "SimBenchmarker")
+      .def(py::init([](const std::unordered_map<std::string, double> &gpu,
+                       const std::unordered_map<std::string, double> &cpu, double defaultGpu,
+                       double defaultCpu, double launchCost, double contention) {
+             SimBenchmarker::Model mod;
+             mod.gpuSeconds = gpu, mod.cpuSeconds = cpu;
+             mod.defaultGpuSeconds = defaultGpu, mod.defaultCpuSeconds = defaultCpu;
+             mod.launchCost = launchCost, mod.contention = contention;
+             return new SimBenchmarker(mod);
+           }),
+           py::arg("gpu_seconds") = std::unordered_map<std::string, double>{},
+           py::arg("cpu_seconds") = std::unordered_map<std::string, double>{},
+           py::arg("default_gpu_seconds") = 10e-6, py::arg("default_cpu_seconds") = 0.0,
+           py::arg("launch_cost") = 3e-6, py::arg("contention") = 0.0)
+      .def("simulate", &SimBenchmarker::simulate);
 
   // device-timed steps with an L2 flush between them (bench.py): returns seconds per step
   m.def(

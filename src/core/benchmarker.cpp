@@ -4,6 +4,7 @@
 #include <chrono>
 #include <cmath>
 #include <fstream>
+#include <map>
 #include <numeric>
 #include <random>
 #include <sstream>
@@ -211,6 +212,59 @@ Result CsvBenchmarker::benchmark(Sequence<BoundOp> &order, Platform &, const Opt
   auto it = byKey_.find(canonical_key(order));
   if (it == byKey_.end()) THROW_RUNTIME("no CSV row matches sequence: " << order.desc());
   return data_[it->second].res;
+}
+
+// ---- timeline simulation ----
+double SimBenchmarker::simulate(const Sequence<BoundOp> &order) const {
+  double host = 0;                               // host clock
+  std::map<int, double> streamReady;             // stream id -> time its last op finishes
+  std::map<int, double> eventTime;               // event id -> time it fires
+  struct Running {
+    double start, end;
+  };
+  std::vector<Running> running;                  // GPU ops placed so far (for contention)
+  auto lookup = [](const std::unordered_map<std::string, double> &m, const std::string &k, double d) {
+    auto it = m.find(k);
+    return it == m.end() ? d : it->second;
+  };
+  for (const auto &op : order) {
+    host += model_.launchCost;
+    if (auto g = std::dynamic_pointer_cast<BoundGpuOp>(op)) {
+      const int s = g->stream().id();
+      double start = std::max(host, streamReady[s]);
+      double dur = lookup(model_.gpuSeconds, g->name(), model_.defaultGpuSeconds);
+      if (model_.contention > 0) {
+        int overlapping = 0;
+        for (const auto &r : running)
+          if (r.end > start) ++overlapping;
+        dur *= 1.0 + model_.contention * overlapping;
+      }
+      streamReady[s] = start + dur;
+      running.push_back(Running{start, start + dur});
+    } else if (auto cer = std::dynamic_pointer_cast<CudaEventRecord>(op)) {
+      eventTime[cer->event().id()] = std::max(host, streamReady[cer->stream().id()]);
+    } else if (auto w = std::dynamic_pointer_cast<CudaStreamWaitEvent>(op)) {
+      double &ready = streamReady[w->stream().id()];
+      ready = std::max(ready, eventTime[w->event().id()]);
+    } else if (auto ces = std::dynamic_pointer_cast<CudaEventSync>(op)) {
+      host = std::max(host, eventTime[ces->event().id()]);
+    } else if (auto ss = std::dynamic_pointer_cast<StreamSync>(op)) {
+      host = std::max(host, streamReady[ss->stream().id()]);
+    } else if (auto sw = std::dynamic_pointer_cast<StreamWait>(op)) {
+      double &ready = streamReady[sw->waiter().id()];
+      ready = std::max(ready, std::max(host, streamReady[sw->waitee().id()]));
+    } else {
+      host += lookup(model_.cpuSeconds, op->name(), model_.defaultCpuSeconds);
+    }
+  }
+  return host;
+}
+
+Result SimBenchmarker::benchmark(Sequence<BoundOp> &order, Platform &, const Opts &) {
+  const double t = simulate(order);
+  Result r;
+  r.pct01 = r.pct10 = r.pct50 = r.pct90 = r.pct99 = t;
+  return r;
 }
 
 // ---- cost model ----
