@@ -1,0 +1,13 @@
+"""The smallest program: Start -> op1 -> Finish (reference: test/test_noop_graph.cpp)."""
+import tenzing_b200 as tz
+
+g = tz.Graph()
+op1 = tz.NoOp("op1")
+g.start_then(op1)
+g.then_finish(op1)
+plat = tz.Platform.make_null(1)          # ids only: runs without a GPU
+state = tz.State(g)
+print("sequence:", state.sequence().names())
+for d in state.get_decisions(plat):
+    print("decision:", d.desc())
+print("all sequences:", [s.names() for s in tz.dfs.get_all_sequences(g, plat)])

@@ -43,6 +43,7 @@ struct Opts {
   bool expandRollout = true;  // keep the nodes a rollout passes through
   uint64_t seed = 0;
   bool removeRedundantSyncs = true;
+  size_t maxTreeNodes = 0;    // stop (Stop::large_tree) once the tree holds this many nodes; 0 = no limit
   Benchmark::Opts benchOpts;
 };
 

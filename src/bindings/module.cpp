@@ -680,6 +680,7 @@ PYBIND11_MODULE(_C, m) {
       .def_readwrite("expand_rollout", &mcts::Opts::expandRollout)
       .def_readwrite("seed", &mcts::Opts::seed)
       .def_readwrite("remove_redundant_syncs", &mcts::Opts::removeRedundantSyncs)
+      .def_readwrite("max_tree_nodes", &mcts::Opts::maxTreeNodes)
       .def_readwrite("bench_opts", &mcts::Opts::benchOpts);
   py::class_<mcts::SimResult>(mc, "SimResult")
       .def_readonly("path", &mcts::SimResult::path)

@@ -458,6 +458,8 @@ Result explore(const Graph<OpBase> &g, Platform &plat, Benchmarker &benchmarker,
   for (size_t iter = 0; opts.nIters == 0 || iter < opts.nIters; ++iter) {
     Stop stop;
     if (rank == 0 && root->fullyVisited_) stop = Stop(true, Stop::Reason::full_tree);
+    if (rank == 0 && !stop && opts.maxTreeNodes && root->size() >= opts.maxTreeNodes)
+      stop = Stop(true, Stop::Reason::large_tree);
     stop.bcast(0, comm);
     if (stop) {
       TENZING_INFO("mcts: stop (" << stop.c_str() << ") after " << iter << " iterations");

@@ -237,3 +237,33 @@ def test_search_with_gpu_ops_on_a_null_platform_uses_streams_as_ids():
     assert best.bench_result.pct10 == 1.0
     allseq = tz.dfs.get_all_sequences(g, plat, -1, True)
     assert min(cost(s) for s in allseq) == 1.0
+
+
+def test_mcts_stops_on_a_large_tree():
+    g = fast_slow_graph()
+    plat = tz.Platform.make_null(1)
+    opts = _C.mcts.Opts()
+    opts.n_iters = 10_000
+    opts.max_tree_nodes = 60
+    res = _C.mcts.explore(g, plat, tz.PyBenchmarker(fast_slow_cost), "FastMin", opts)
+    assert 0 < len(res.sim_results) < 60
+
+
+def test_interrupt_dumps_the_partial_results():
+    """SIGINT during a search makes rank 0 print the rows collected so far and exit(1)
+    (reference: src/trap.cpp:11-35 + the solvers' register_handler calls)"""
+    import os
+    import signal
+    import subprocess
+    import sys
+    import time as _t
+    here = os.path.dirname(os.path.abspath(__file__))
+    p = subprocess.Popen([sys.executable, os.path.join(here, "trap_worker.py")], stdout=subprocess.PIPE,
+                         stderr=subprocess.PIPE, text=True)
+    assert p.stdout.readline().strip() == "READY"
+    _t.sleep(1.0)
+    p.send_signal(signal.SIGINT)
+    out, _ = p.communicate(timeout=60)
+    assert p.returncode == 1
+    rows = [line for line in out.splitlines() if "|" in line]
+    assert len(rows) > 10 and rows[0].startswith("0|") and '{"name":"Start"}' in rows[0]
