@@ -1,5 +1,9 @@
 """The smallest program: Start -> op1 -> Finish (reference: test/test_noop_graph.cpp)."""
-import tenzing_b200 as tz
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import tenzing_b200 as tz  # noqa: E402
 
 g = tz.Graph()
 op1 = tz.NoOp("op1")

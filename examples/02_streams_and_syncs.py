@@ -1,6 +1,10 @@
 """Three kernels k1 -> {k2, k3} on two streams: what the solver enumerates, and how a timeline
 simulation ranks the schedules (no GPU needed)."""
-import tenzing_b200 as tz
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import tenzing_b200 as tz  # noqa: E402
 
 k1, k2, k3 = (tz.EmptyGpuOp(n) for n in ("k1", "k2", "k3"))
 g = tz.Graph()

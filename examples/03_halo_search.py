@@ -1,7 +1,11 @@
 """Search the halo-exchange schedule on the GPUs this process group has (run under
 torch.distributed.run for more than one), print the best schedule and the rules the
 post-processor extracts from the search log."""
-import torch
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch  # noqa: E402
 
 from tenzing_b200.models import HaloExchange, common
 from tenzing_b200.parallel import init_process_group_from_env, make_comm
