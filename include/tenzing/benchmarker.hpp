@@ -128,6 +128,12 @@ public:
   explicit SimBenchmarker(Model m) : model_(std::move(m)) {}
   // simulated wall time of one execution of the sequence
   double simulate(const Sequence<BoundOp> &order) const;
+  // per op of the sequence: (start, end) on its timeline - GPU ops on their stream, everything
+  // else on the host.  Used to check that a schedule respects the program's dependencies.
+  struct Span {
+    double start, end;
+  };
+  std::vector<Span> timeline(const Sequence<BoundOp> &order) const;
   Benchmark::Result benchmark(Sequence<BoundOp> &order, Platform &plat,
                               const Benchmark::Opts &opts = Benchmark::Opts()) override;
 

@@ -608,7 +608,12 @@ PYBIND11_MODULE(_C, m) {
            py::arg("cpu_seconds") = std::unordered_map<std::string, double>{},
            py::arg("default_gpu_seconds") = 10e-6, py::arg("default_cpu_seconds") = 0.0,
            py::arg("launch_cost") = 3e-6, py::arg("contention") = 0.0)
-      .def("simulate", &SimBenchmarker::simulate);
+      .def("simulate", &SimBenchmarker::simulate)
+      .def("timeline", [](const SimBenchmarker &b, const Seq &s) {
+        std::vector<std::pair<double, double>> out;
+        for (const auto &sp : b.timeline(s)) out.emplace_back(sp.start, sp.end);
+        return out;
+      });
 
   // device-timed steps with an L2 flush between them (bench.py): returns seconds per step
   m.def(

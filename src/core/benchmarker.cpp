@@ -216,6 +216,15 @@ Result CsvBenchmarker::benchmark(Sequence<BoundOp> &order, Platform &, const Opt
 
 // ---- timeline simulation ----
 double SimBenchmarker::simulate(const Sequence<BoundOp> &order) const {
+  const std::vector<Span> t = timeline(order);
+  double end = 0;
+  for (const Span &s : t) end = std::max(end, s.end);
+  // the sequence is over when the host has issued (and waited through) its last op
+  return t.empty() ? 0 : t.back().end;
+}
+
+std::vector<SimBenchmarker::Span> SimBenchmarker::timeline(const Sequence<BoundOp> &order) const {
+  std::vector<Span> spans;
   double host = 0;                               // host clock
   std::map<int, double> streamReady;             // stream id -> time its last op finishes
   std::map<int, double> eventTime;               // event id -> time it fires
@@ -228,6 +237,7 @@ double SimBenchmarker::simulate(const Sequence<BoundOp> &order) const {
     return it == m.end() ? d : it->second;
   };
   for (const auto &op : order) {
+    const double issued = host;
     host += model_.launchCost;
     if (auto g = std::dynamic_pointer_cast<BoundGpuOp>(op)) {
       const int s = g->stream().id();
@@ -241,6 +251,8 @@ double SimBenchmarker::simulate(const Sequence<BoundOp> &order) const {
       }
       streamReady[s] = start + dur;
       running.push_back(Running{start, start + dur});
+      spans.push_back(Span{start, start + dur});
+      continue;
     } else if (auto cer = std::dynamic_pointer_cast<CudaEventRecord>(op)) {
       eventTime[cer->event().id()] = std::max(host, streamReady[cer->stream().id()]);
     } else if (auto w = std::dynamic_pointer_cast<CudaStreamWaitEvent>(op)) {
@@ -256,8 +268,9 @@ double SimBenchmarker::simulate(const Sequence<BoundOp> &order) const {
     } else {
       host += lookup(model_.cpuSeconds, op->name(), model_.defaultCpuSeconds);
     }
+    spans.push_back(Span{issued, host});
   }
-  return host;
+  return spans;
 }
 
 Result SimBenchmarker::benchmark(Sequence<BoundOp> &order, Platform &, const Opts &) {
