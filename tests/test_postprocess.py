@@ -54,3 +54,15 @@ def test_feature_pruning_drops_constant_and_duplicate_columns():
     assert cols == ["u", "v"] and Xp.shape == (3, 2)
     X = np.array([[1, 0], [0, 1]], dtype=bool)  # a column and its negation
     assert postprocess.prune_features(X, ["p", "not p"])[1] == ["p"]
+
+
+def test_cli_runs_without_a_gpu(capsys):
+    """python -m tenzing_b200.cli: reproducibility header + CSV, like the reference's executables"""
+    import json
+    from tenzing_b200 import cli
+    assert cli.main(["spmv", "--solver", "dfs", "-m", "300", "--max-seqs", "4", "--style", "fused",
+                     "--null"]) == 0
+    out = capsys.readouterr().out.splitlines()
+    assert set(json.loads(out[0])) == {"args", "hash", "major", "minor", "patch"}
+    assert out[1] == '{"dfs__Opts":{"maxSeqs":4}}'
+    assert len([l for l in out[2:] if "|" in l]) == 4
