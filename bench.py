@@ -40,7 +40,7 @@ class ClockSampler:
             self.f = open(self.path, "w")
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--query-gpu={CLOCK_QUERY}", "--format=csv,noheader,nounits",
-                 "-lms", "100", "-i", str(self.gpu)], stdout=self.f, stderr=subprocess.DEVNULL)
+                 "-lms", "20", "-i", str(self.gpu)], stdout=self.f, stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
 

@@ -267,3 +267,28 @@ def test_interrupt_dumps_the_partial_results():
     assert p.returncode == 1
     rows = [line for line in out.splitlines() if "|" in line]
     assert len(rows) > 10 and rows[0].startswith("0|") and '{"name":"Start"}' in rows[0]
+
+
+def test_tree_dumps_graph_dumps_and_csv_file_replay(tmp_path):
+    g = fast_slow_graph()
+    plat = tz.Platform.make_null(1)
+    opts = _C.mcts.Opts()
+    opts.n_iters = 30
+    opts.dump_tree = True
+    opts.dump_tree_prefix = str(tmp_path / "tree_")
+    res = _C.mcts.explore(g, plat, tz.PyBenchmarker(fast_slow_cost), "AvgTime", opts)
+    # iterations 0..9, 10, 20 (reference: mcts.hpp:302-303)
+    dumped = sorted(int(p.name[5:-4]) for p in tmp_path.glob("tree_*.dot"))
+    assert dumped == list(range(10)) + [10, 20]
+    assert (tmp_path / "tree_20.dot").read_text().startswith("digraph D {")
+    g.dump_graphviz(str(tmp_path / "graph.dot"))
+    assert "f0" in (tmp_path / "graph.dot").read_text()
+    # a results file on disk, with the reproducibility header in front, replays
+    path = tmp_path / "results.csv"
+    path.write_text(_C.reproduce_header(["prog"]) + "\n" + res.csv())
+    replay = tz.CsvBenchmarker(str(path), g)
+    assert replay.num_rows() == 30
+    r0 = res.sim_results[0]
+    assert replay.benchmark(r0.path, plat).pct10 == pytest.approx(r0.bench_result.pct10)
+    with pytest.raises(RuntimeError):
+        replay.benchmark(tz.Sequence([g.start(), g.finish()]), plat)
