@@ -509,7 +509,7 @@ Result explore(const Graph<OpBase> &g, Platform &plat, Benchmarker &benchmarker,
       TENZING_COUNTER_OP(mcts, BACKPROP_TIME, += counters::now() - t);
       TENZING_COUNTER_OP(mcts, ITERS, += 1);
       if (opts.dumpTree &&
-          (iter < 10 || (iter < 50 && iter % 10 == 0) || (iter < 100 && iter % 25 == 0))) {
+          (iter < 10 || (iter < 50 && iter % 10 == 0) || (iter >= 50 && iter < 100 && iter % 25 == 0))) {
         dump_graphviz(opts.dumpTreePrefix + std::to_string(iter) + ".dot", *root, &strategy);
       }
     }
