@@ -182,6 +182,8 @@ PYBIND11_MODULE(_C, m) {
     return d;
   });
   m.def("reset_counters", &counters::reset);
+  // parse + dump through the built-in JSON value (format tests)
+  m.def("json_roundtrip", [](const std::string &text) { return Json::parse(text).dump(); });
 
   py::class_<Equivalence>(m, "Equivalence")
       .def("__bool__", [](const Equivalence &e) { return bool(e); })
@@ -585,7 +587,17 @@ PYBIND11_MODULE(_C, m) {
            },
            py::arg("seq"), py::arg("plat"), py::arg("opts") = Benchmark::Opts(),
            py::call_guard<py::gil_scoped_release>());
-  py::class_<EmpiricalBenchmarker, Benchmarker>(m, "EmpiricalBenchmarker").def(py::init<>());
+  py::class_<EmpiricalBenchmarker, Benchmarker>(m, "EmpiricalBenchmarker")
+      .def(py::init<>())
+      // several sequences measured interleaved, in a fresh random order per iteration
+      .def("benchmark_batch",
+           [](EmpiricalBenchmarker &b, const std::vector<Seq> &seqs, Platform &p, const Benchmark::Opts &o) {
+             std::vector<Schedule> scheds(seqs.size());
+             for (size_t i = 0; i < seqs.size(); ++i) scheds[i].order = seqs[i];
+             return b.benchmark(scheds, p, o);
+           },
+           py::arg("seqs"), py::arg("plat"), py::arg("opts") = Benchmark::Opts(),
+           py::call_guard<py::gil_scoped_release>());
   py::class_<DeviceBenchmarker, EmpiricalBenchmarker>(m, "DeviceBenchmarker").def(py::init<>());
   py::class_<CsvBenchmarker, Benchmarker>(m, "CsvBenchmarker")
       .def(py::init<const std::string &, const G &>())

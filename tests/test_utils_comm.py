@@ -158,3 +158,41 @@ def test_native_cpp_test_runner():
     p = subprocess.run([exe], capture_output=True, text=True, timeout=300)
     assert p.returncode == 0, p.stdout + p.stderr
     assert "0 failed" in p.stdout
+
+
+def test_json_value_round_trips_and_sorts_keys():
+    rt = _C.json_roundtrip
+    assert rt('{"b": 1, "a": [true, null, "x\\n", 1.5, -3]}') == '{"a":[true,null,"x\\n",1.5,-3],"b":1}'
+    assert (rt('{"name":"CER-after-yl","event":0,"kind":"CudaEventRecord","stream":1}') ==
+            '{"event":0,"kind":"CudaEventRecord","name":"CER-after-yl","stream":1}')
+    assert rt("[]") == "[]" and rt("{}") == "{}" and rt(" 1e-05 ") == "1e-05"
+    assert rt('"\\u00e9\\t"') == '"é\\t"'
+    for bad in ('{"a":}', "[1,", '{"a" 1}', "tru"):
+        with pytest.raises(RuntimeError):
+            rt(bad)
+
+
+def test_batch_benchmark_interleaves_sequences():
+    import time
+    g = tz.Graph()
+    fast = tz.PyCpuOp("fast", lambda: time.sleep(0.001))
+    slow = tz.PyCpuOp("slow", lambda: time.sleep(0.004))
+    plat = tz.Platform.make_null(1)
+    s_fast = tz.Sequence([g.start(), fast, g.finish()])
+    s_slow = tz.Sequence([g.start(), slow, g.finish()])
+    opts = tz.BenchOpts(n_iters=6, max_retries=0, target_secs=0.0, check_randomness=False)
+    r_fast, r_slow = tz.EmpiricalBenchmarker().benchmark_batch([s_fast, s_slow], plat, opts)
+    assert 0.0009 < r_fast.pct50 < 0.003 < r_slow.pct50 < 0.01
+
+
+def test_op_helpers():
+    k = tz.EmptyGpuOp("k")
+    plat = tz.Platform.make_null(3)
+    var = _C.make_platform_variations(plat, k)
+    assert [v.stream() for v in var] == [0, 1, 2]
+    n = tz.NoOp("n")
+    assert [v.name() for v in _C.make_platform_variations(plat, n)] == ["n"]
+    assert _C.unbound_contains(var, k) and not _C.unbound_contains(var, tz.EmptyGpuOp("other"))
+    uniq = _C.keep_uniques([var[0], var[1], tz.BoundGpuOp(k, 0), n, tz.NoOp("n")])
+    assert [u.desc() for u in uniq] == ["k(s0)", "k(s1)", "n"]
+    assert _C.contains([k, n], tz.NoOp("n")) and not _C.contains([k], n)
