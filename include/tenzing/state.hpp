@@ -21,6 +21,7 @@ namespace SDP {
 class State {
   std::shared_ptr<const Graph<OpBase>> graph_;
   Sequence<BoundOp> sequence_;
+  mutable std::string keyCache_; // canonical_key() is asked for by frontier() and by the solvers
 
 public:
   // initial state: sequence = [Start]

@@ -54,6 +54,7 @@ State State::apply(const Decision &d) const {
   switch (d.kind()) {
   case Decision::Kind::ExecuteOp: {
     State r(*this);
+    r.keyCache_.clear();
     r.sequence_.push_back(static_cast<const ExecuteOp &>(d).op);
     return r;
   }
@@ -91,6 +92,7 @@ bool State::is_terminal() const {
 // sequence first, then graph vertices in name order, one renumbering of streams
 // and events across both (so sequence and graph agree on the renaming)
 std::string State::canonical_key() const {
+  if (!keyCache_.empty()) return keyCache_;
   std::map<int, int> sMap, eMap;
   auto relabel = [](std::map<int, int> &m, int id) {
     auto it = m.find(id);
@@ -125,6 +127,7 @@ std::string State::canonical_key() const {
     for (const auto &n : succNames) key += n + ",";
     key += "|";
   }
+  keyCache_ = key;
   return key;
 }
 
