@@ -98,7 +98,6 @@ def main():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours")
-    ap.add_argument("--workload", default="halo", choices=["halo", "spmv"])
     ap.add_argument("--nx", type=int, default=512)
     ap.add_argument("--nq", type=int, default=3)
     ap.add_argument("--spmv-n", type=int, default=1_000_000)

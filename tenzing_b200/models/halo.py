@@ -91,8 +91,6 @@ class HaloExchange:
         g = a.nGhost
         pat = self._global_pattern(wrap=True)
         out = torch.full_like(pat, -1)
-        lo = (slice(0, g), slice(g, None), slice(None))
-
         def rng(d, n):
             return slice(0, g) if d < 0 else (slice(g + n, g + n + g) if d > 0 else slice(g, g + n))
 
@@ -100,7 +98,6 @@ class HaloExchange:
         for dx, dy, dz in self.domain.dirs():
             s = (slice(None), rng(dz, a.nZ), rng(dy, a.nY), rng(dx, a.nX))
             out[s] = pat[s]
-        del lo
         return out
 
     def check(self):
