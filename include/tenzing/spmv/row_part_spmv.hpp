@@ -119,6 +119,13 @@ public:
 template <typename Scalar>
 std::shared_ptr<ChoiceOp> make_spmv_choice(const std::shared_ptr<RowPartSpmv<Scalar>> &spmv);
 
+// Root-held matrix -> one row block per rank (reference: send_matrix / receive_matrix,
+// row_part_spmv.cuh:18-90, four MPI_Isend + Probe/Recv per peer).  Rank `root` passes the whole
+// matrix, the others pass nullptr; every rank gets its get_partition() block with global
+// column ids.  Blocks travel as broadcasts (set-up only), so any Communicator will do.
+template <typename Scalar>
+CsrMat<int, Scalar> distribute_rows(Communicator &comm, const CsrMat<int, Scalar> *whole, int root = 0);
+
 // convenience: band matrix block generated in place on every rank
 template <typename Scalar>
 std::shared_ptr<RowPartSpmv<Scalar>>

@@ -3,6 +3,7 @@
 #include "op_cast.hpp"
 #include <pybind11/stl.h>
 
+#include "tenzing/spmv/mtx_reader.hpp"
 #include "tenzing/spmv/row_part_spmv.hpp"
 #include "tenzing/tenzing.hpp"
 
@@ -78,6 +79,21 @@ template <typename Scalar> void bind_one(py::module_ &m, const char *suffix) {
         },
         py::arg("comm"), py::arg("n"), py::arg("bw"), py::arg("nnz_per_row") = 10,
         py::arg("seed") = 0, py::arg("host") = false, py::call_guard<py::gil_scoped_release>());
+  // matrix from a MatrixMarket file: rank 0 reads it and hands every rank its row block
+  const std::string mtx = std::string("make_mtx_spmv") + suffix;
+  m.def(mtx.c_str(),
+        [](std::shared_ptr<Communicator> comm, const std::string &path, bool host) {
+          if (!comm) comm = std::make_shared<SelfComm>();
+          CsrMat<int, Scalar> whole;
+          if (comm->rank() == 0) whole = MtxReader<int, Scalar>(path).read_csr();
+          int64_t n = whole.num_rows();
+          comm->bcast(&n, sizeof(n), 0);
+          CsrMat<int, Scalar> mine = distribute_rows<Scalar>(*comm, comm->rank() == 0 ? &whole : nullptr, 0);
+          return std::make_shared<R>(comm, mine, n,
+                                     host ? SymmetricHeap::Memory::Host : SymmetricHeap::Memory::Device);
+        },
+        py::arg("comm"), py::arg("path"), py::arg("host") = false,
+        py::call_guard<py::gil_scoped_release>());
   const std::string rows = std::string("random_band_rows") + suffix;
   m.def(rows.c_str(),
         [](int64_t n, int64_t bw, int nnzPerRow, int64_t rb, int64_t re, uint64_t seed) {

@@ -145,6 +145,48 @@ template <typename Scalar> size_t RowPartSpmv<Scalar>::hbm_bytes() const {
 }
 
 template <typename Scalar>
+CsrMat<int, Scalar> distribute_rows(Communicator &comm, const CsrMat<int, Scalar> *whole, int root) {
+  const int me = comm.rank(), np = comm.size();
+  int64_t dims[2] = {0, 0};
+  if (me == root) {
+    if (!whole) THROW_RUNTIME("distribute_rows: the root must pass the matrix");
+    dims[0] = whole->num_rows(), dims[1] = whole->num_cols();
+  }
+  comm.bcast(dims, sizeof(dims), root);
+  CsrMat<int, Scalar> mine;
+  for (int r = 0; r < np; ++r) {
+    const Range rg = get_partition(dims[0], r, np);
+    // root serialises block r: [nnz][rowPtr...][colInd...][val...]
+    std::string buf;
+    if (me == root) {
+      const CsrMat<int, Scalar> blk = whole->retain_rows(rg.lb, rg.ub);
+      const int64_t nnz = blk.nnz();
+      buf.append(reinterpret_cast<const char *>(&nnz), sizeof(nnz));
+      buf.append(reinterpret_cast<const char *>(blk.rowPtr_.data()), blk.rowPtr_.size() * sizeof(int));
+      buf.append(reinterpret_cast<const char *>(blk.colInd_.data()), blk.colInd_.size() * sizeof(int));
+      buf.append(reinterpret_cast<const char *>(blk.val_.data()), blk.val_.size() * sizeof(Scalar));
+    }
+    buf = comm.bcast_string(buf, root);
+    if (r != me) continue;
+    const char *p = buf.data();
+    int64_t nnz = 0;
+    std::memcpy(&nnz, p, sizeof(nnz));
+    p += sizeof(nnz);
+    mine = CsrMat<int, Scalar>(rg.extent(), dims[1]);
+    std::memcpy(mine.rowPtr_.data(), p, mine.rowPtr_.size() * sizeof(int));
+    p += mine.rowPtr_.size() * sizeof(int);
+    mine.colInd_.resize(size_t(nnz));
+    mine.val_.resize(size_t(nnz));
+    std::memcpy(mine.colInd_.data(), p, size_t(nnz) * sizeof(int));
+    p += size_t(nnz) * sizeof(int);
+    std::memcpy(mine.val_.data(), p, size_t(nnz) * sizeof(Scalar));
+  }
+  return mine;
+}
+template CsrMat<int, double> distribute_rows<double>(Communicator &, const CsrMat<int, double> *, int);
+template CsrMat<int, float> distribute_rows<float>(Communicator &, const CsrMat<int, float> *, int);
+
+template <typename Scalar>
 std::shared_ptr<RowPartSpmv<Scalar>> make_band_spmv(std::shared_ptr<Communicator> comm, int64_t n,
                                                     int64_t bw, int nnzPerRow, uint64_t seed,
                                                     SymmetricHeap::Memory memory) {

@@ -27,6 +27,7 @@ def main(argv=None):
     ap.add_argument("--max-seqs", type=int, default=15000)
     ap.add_argument("--matrix-m", "-m", type=int, default=150000)
     ap.add_argument("--random", action="store_true", help="uniformly random columns (bw = m)")
+    ap.add_argument("--matrix-file", default=None, help="MatrixMarket file instead of a synthetic matrix")
     ap.add_argument("--fp32", action="store_true")
     ap.add_argument("--n", "-n", type=int, default=512, help="halo: interior cells per dimension per rank")
     ap.add_argument("--nq", type=int, default=3)
@@ -47,7 +48,7 @@ def main(argv=None):
     if args.workload == "spmv":
         wl = DistributedSpMV(comm=comm, n=args.matrix_m, bw=args.matrix_m if args.random else None,
                              dtype=torch.float32 if args.fp32 else torch.float64, host=host,
-                             n_streams=args.streams)
+                             n_streams=args.streams, matrix_file=args.matrix_file)
     else:
         wl = HaloExchange(comm=comm, nX=args.n, nQ=args.nq, nGhost=args.ghost,
                           neighbors=args.neighbors, host=host, n_streams=args.streams)

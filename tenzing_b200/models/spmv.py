@@ -25,7 +25,9 @@ def _csr_from_dict(d, dtype):
 
 class DistributedSpMV:
     def __init__(self, comm=None, n=1_000_000, bw=None, nnz_per_row=10, seed=0,
-                 dtype=torch.float64, host=False, n_streams=2):
+                 dtype=torch.float64, host=False, n_streams=2, matrix_file=None):
+        """matrix_file: a MatrixMarket file (square, coordinate format) read by rank 0 and
+        distributed by row blocks; otherwise a synthetic band / random matrix is generated"""
         self.comm = comm if comm is not None else make_comm()
         size = self.comm.size()
         if bw is None:
@@ -34,7 +36,11 @@ class DistributedSpMV:
         self.np_dtype = np.float64 if dtype == torch.float64 else np.float32
         sfx = "F64" if dtype == torch.float64 else "F32"
         self._sfx = sfx
-        self.spmv = getattr(_C.spmv, "make_band_spmv" + sfx)(self.comm, n, bw, nnz_per_row, seed, host)
+        if matrix_file:
+            self.spmv = getattr(_C.spmv, "make_mtx_spmv" + sfx)(self.comm, matrix_file, host)
+            self.n = self.spmv.global_rows()
+        else:
+            self.spmv = getattr(_C.spmv, "make_band_spmv" + sfx)(self.comm, n, bw, nnz_per_row, seed, host)
         self.platform = common.make_platform(self.comm, n_streams, null=host)
         rows = self.spmv.local_rows()
         view = host_tensor if host else device_tensor

@@ -165,3 +165,28 @@ def test_schedules_round_trip_through_json_for_workload_graphs():
     seq = res.sim_results[0].path
     assert replay.benchmark(seq, plat).pct10 == float(len(seq))
     assert common.fixed_schedule(h.graph("staged"), plat).names()[-1] == "Finish"
+
+
+def test_matrix_market_file_is_read_on_root_and_distributed(tmp_path):
+    import scipy.io
+    import scipy.sparse as sp
+    rng = np.random.default_rng(3)
+    n = 57
+    A = sp.random(n, n, density=0.15, random_state=rng, format="coo") + sp.identity(n)
+    path = str(tmp_path / "a.mtx")
+    scipy.io.mmwrite(path, A.tocoo())
+    A = A.tocsr()
+    x = DistributedSpMV.x_value(np.arange(n, dtype=np.int64))
+    y_ref = A @ x
+    seen = {}
+
+    def body(rank, comm):
+        s = DistributedSpMV(comm=comm, matrix_file=path, host=True)
+        lb, ub = s.spmv.row_range()
+        assert s.n == n and (lb, ub) == _C.spmv.get_partition(n, rank, 3)
+        assert np.allclose(s.expected(), y_ref[lb:ub], rtol=1e-12)
+        seen[rank] = s.spmv.local_nnz() + s.spmv.remote_nnz()
+        comm.barrier()
+
+    _C.loopback_run(3, body)
+    assert sum(seen.values()) == A.nnz
