@@ -10,7 +10,7 @@
 // Data plane: every rank's grid, staging buffers and flag words live in a
 // SymmetricHeap, so "send" is a kernel storing into the neighbour's memory
 // over NVLink and "receive complete" is a flag word written by the neighbour.
-// Four implementation styles are offered to the search as alternatives:
+// These implementation styles are offered to the search as alternatives:
 //   Reference  pack -> isend -> (irecv) -> wait -> unpack, host driven: the
 //              reference's op structure with copy-engine peer copies standing
 //              in for CUDA-aware MPI (the baseline, not the product)

@@ -115,7 +115,7 @@ public:
   CLONE_DEF(SpMV)
 };
 
-// ChoiceOp "spmv" over the three styles
+// ChoiceOp "spmv" over the four styles
 template <typename Scalar>
 std::shared_ptr<ChoiceOp> make_spmv_choice(const std::shared_ptr<RowPartSpmv<Scalar>> &spmv);
 
