@@ -21,6 +21,7 @@
 #include "tenzing/graph.hpp"
 #include "tenzing/platform.hpp"
 #include "tenzing/schedule.hpp"
+#include "tenzing/reproduce.hpp"
 #include "tenzing/sequence.hpp"
 
 namespace tenzing {
@@ -89,9 +90,12 @@ public:
   Benchmark::Result benchmark(Sequence<BoundOp> &order, Platform &plat,
                               const Benchmark::Opts &opts = Benchmark::Opts()) override;
   const std::vector<DataRow> &rows() const { return data_; }
+  // reproduce header found in the file (valid == false if there was none)
+  const reproduce::Header &producer() const { return producer_; }
 
 private:
   CsvBenchmarker() = default;
+  reproduce::Header producer_;
   void load(std::istream &is, const Graph<OpBase> &g);
   std::vector<DataRow> data_;
   std::unordered_map<std::string, size_t> byKey_; // canonical key -> row

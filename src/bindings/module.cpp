@@ -138,6 +138,20 @@ std::vector<int> op_events(const OpBase &op) {
 using G = Graph<OpBase>;
 using Seq = Sequence<BoundOp>;
 
+// reproduce::Header -> dict (None if the line was not a header)
+py::object header_to_py(const reproduce::Header &h) {
+  if (!h.valid) return py::none();
+  py::dict d;
+  d["args"] = h.args;
+  d["hash"] = h.hash;
+  d["major"] = h.major;
+  d["minor"] = h.minor;
+  d["patch"] = h.patch;
+  d["version"] = h.version();
+  d["same_build"] = h.same_build();
+  return d;
+}
+
 } // namespace
 
 PYBIND11_MODULE(_C, m) {
@@ -148,6 +162,8 @@ PYBIND11_MODULE(_C, m) {
   m.def("init", [] { tenzing::init(); });
   m.def("version_string", &reproduce::version_string);
   m.def("reproduce_header", &reproduce::header_json);
+  m.def("parse_reproduce_header",
+        [](const std::string &line) { return header_to_py(reproduce::parse_header(line)); });
   m.def("set_verbosity", &log::set_verbosity);
   m.def("set_log_rank", &log::set_rank);
   m.def("avg", [](const std::vector<double> &v) { return avg(v); });
@@ -604,7 +620,10 @@ PYBIND11_MODULE(_C, m) {
       .def_static("from_text", [](const std::string &t, const G &g) {
         return new CsvBenchmarker(CsvBenchmarker::from_text(t, g));
       }, py::return_value_policy::take_ownership)
-      .def("num_rows", [](const CsvBenchmarker &b) { return b.rows().size(); });
+      .def("num_rows", [](const CsvBenchmarker &b) { return b.rows().size(); })
+      .def("producer", [](const CsvBenchmarker &b) -> py::object {
+        return header_to_py(b.producer());
+      });
   py::class_<PyBenchmarker, Benchmarker>(m, "PyBenchmarker").def(py::init<py::object>());
   py::class_<SimBenchmarker, Benchmarker>(m, "SimBenchmarker")
       .def(py::init([](const std::unordered_map<std::string, double> &gpu,

@@ -164,7 +164,16 @@ void CsvBenchmarker::load(std::istream &is, const Graph<OpBase> &g) {
   size_t lineNo = 0;
   while (std::getline(is, line)) {
     ++lineNo;
-    if (line.empty() || line[0] == '{' || line[0] == '#') continue; // reproduce / opts headers
+    if (line.empty() || line[0] == '#') continue;
+    if (line[0] == '{') { // reproduce header (or another JSON header line, which is skipped)
+      const reproduce::Header h = reproduce::parse_header(line);
+      if (h.valid && !producer_.valid) {
+        producer_ = h;
+        if (!h.same_build())
+          TENZING_INFO("csv written by build " << h.version() << ", this is " << reproduce::version_string());
+      }
+      continue;
+    }
     std::vector<std::string> cols;
     {
       std::stringstream ss(line);

@@ -121,6 +121,41 @@ std::string header_json(const std::vector<std::string> &args) {
   j["patch"] = TENZING_VERSION_PATCH;
   return j.dump();
 }
+bool Header::same_build() const {
+  return valid && major == TENZING_VERSION_MAJOR && minor == TENZING_VERSION_MINOR &&
+         patch == TENZING_VERSION_PATCH && hash == TENZING_VERSION_HASH;
+}
+std::string Header::version() const {
+  return std::to_string(major) + "." + std::to_string(minor) + "." + std::to_string(patch) + "-" + hash;
+}
+Header make_header(const std::vector<std::string> &args) {
+  Header h;
+  h.args = args;
+  h.hash = TENZING_VERSION_HASH;
+  h.major = TENZING_VERSION_MAJOR;
+  h.minor = TENZING_VERSION_MINOR;
+  h.patch = TENZING_VERSION_PATCH;
+  h.valid = true;
+  return h;
+}
+Header parse_header(const std::string &line) {
+  Header h;
+  try {
+    const Json j = Json::parse(line);
+    if (!j.is_object() || !j.contains("args") || !j.contains("hash") || !j.contains("major") ||
+        !j.contains("minor") || !j.contains("patch"))
+      return h;
+    for (const Json &a : j.at("args").as_array()) h.args.push_back(a.as_string());
+    h.hash = j.at("hash").as_string();
+    h.major = int(j.at("major").as_int());
+    h.minor = int(j.at("minor").as_int());
+    h.patch = int(j.at("patch").as_int());
+    h.valid = true;
+  } catch (const std::exception &) {
+    h = Header();
+  }
+  return h;
+}
 void dump_with_cli(int argc, char **argv) {
   std::vector<std::string> args;
   for (int i = 0; i < argc; ++i) args.emplace_back(argv[i]);

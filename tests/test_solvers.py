@@ -288,6 +288,13 @@ def test_tree_dumps_graph_dumps_and_csv_file_replay(tmp_path):
     path.write_text(_C.reproduce_header(["prog"]) + "\n" + res.csv())
     replay = tz.CsvBenchmarker(str(path), g)
     assert replay.num_rows() == 30
+    prod = replay.producer()
+    assert prod["args"] == ["prog"] and prod["same_build"] and prod["version"] == _C.version_string()
+    assert tz.CsvBenchmarker.from_text(res.csv(), g).producer() is None
+    assert _C.parse_reproduce_header('{"not": "a header"}') is None
+    assert _C.parse_reproduce_header("12|3|4") is None
+    other = _C.parse_reproduce_header('{"args":["a","b"],"hash":"deadbeef","major":9,"minor":0,"patch":1}')
+    assert other["version"] == "9.0.1-deadbeef" and not other["same_build"]
     r0 = res.sim_results[0]
     assert replay.benchmark(r0.path, plat).pct10 == pytest.approx(r0.bench_result.pct10)
     with pytest.raises(RuntimeError):
