@@ -54,9 +54,13 @@ def generate():
     if not os.path.exists(vh) or open(vh).read() != content:
         open(vh, "w").write(content)
 
-    cxxflags = f"-std=c++17 -O2 -g1 -fPIC -Wall -Wextra -Wno-unused-parameter {inc} -include {vh}"
+    # optional debug macros, e.g. TENZING_DEFINES="TENZING_RUNTIME_SANITY_CHECKS TENZING_RUNTIME_CHECK_BOUNDS"
+    # (graph invariants after every rewrite / device-side bounds checks in ArrayView)
+    defs = " ".join("-D" + d for d in os.environ.get("TENZING_DEFINES", "").split())
+    cxxflags = (f"-std=c++17 -O2 -g1 -fPIC -Wall -Wextra -Wno-unused-parameter {inc} -include {vh} "
+                f"{defs}").rstrip()
     nvccflags = (f"-std=c++17 -O3 {ARCH_FLAGS} -lineinfo -Xcompiler -fPIC "
-                 f"--expt-relaxed-constexpr -Xptxas -v {inc} -include {vh}")
+                 f"--expt-relaxed-constexpr -Xptxas -v {inc} -include {vh} {defs}").rstrip()
     ldflags = f"-L{CUDA_HOME}/lib64 -lcudart_static -ldl -lrt -lpthread"
 
     lib_cpp = sorted(glob.glob(f"{ROOT}/src/core/*.cpp") + glob.glob(f"{ROOT}/src/solvers/*.cpp") +

@@ -190,6 +190,82 @@ public:
       if (v.alive && v.op->name() == name) return {true, ops_of(v.succs)};
     return {false, {}};
   }
+  std::pair<bool, std::vector<op_t>> preds_find_name(const std::string &name) const {
+    for (const auto &v : v_)
+      if (v.alive && v.op->name() == name) return {true, ops_of(v.preds)};
+    return {false, {}};
+  }
+
+  // Structural invariants every well-formed program graph satisfies: adjacency lists mirror
+  // each other and name live vertices only, the indexes point at the right vertices, nothing
+  // enters Start or leaves Finish, the graph is acyclic, and every live vertex lies on a path
+  // Start -> ... -> Finish.  Returns an empty string if all hold, else the first violation.
+  // Builds with TENZING_RUNTIME_SANITY_CHECKS run it after every rewrite (reference:
+  // CMakeLists.txt always defines that macro; here it is an option, off by default).
+  std::string validate() const {
+    const vid_t n = static_cast<vid_t>(v_.size());
+    std::ostringstream err;
+    auto live = [&](vid_t i) { return i >= 0 && i < n && v_[i].alive; };
+    for (vid_t i = 0; i < n; ++i) {
+      if (!v_[i].alive) continue;
+      for (vid_t s : v_[i].succs) {
+        if (!live(s)) { err << v_[i].op->desc() << " has a dead successor"; return err.str(); }
+        if (std::find(v_[s].preds.begin(), v_[s].preds.end(), i) == v_[s].preds.end()) {
+          err << "edge " << v_[i].op->desc() << " -> " << v_[s].op->desc() << " has no mirror";
+          return err.str();
+        }
+      }
+      for (vid_t p : v_[i].preds) {
+        if (!live(p)) { err << v_[i].op->desc() << " has a dead predecessor"; return err.str(); }
+        if (std::find(v_[p].succs.begin(), v_[p].succs.end(), i) == v_[p].succs.end()) {
+          err << "edge " << v_[p].op->desc() << " -> " << v_[i].op->desc() << " has no mirror";
+          return err.str();
+        }
+      }
+      auto it = index_.find(v_[i].op->uid());
+      if (it == index_.end() || it->second != i) {
+        err << v_[i].op->desc() << " is not indexed";
+        return err.str();
+      }
+    }
+    if (!live(start_) || !live(finish_)) return "Start or Finish missing";
+    if (!v_[start_].preds.empty()) return "an edge enters Start";
+    if (!v_[finish_].succs.empty()) return "an edge leaves Finish";
+    // Kahn: all live vertices must come out, and only Start may have no predecessor
+    std::vector<int> indeg(n, 0);
+    std::vector<vid_t> ready;
+    size_t nLive = 0, seen = 0;
+    for (vid_t i = 0; i < n; ++i) {
+      if (!v_[i].alive) continue;
+      ++nLive;
+      indeg[i] = int(v_[i].preds.size());
+      if (indeg[i] == 0) {
+        if (i != start_) { err << v_[i].op->desc() << " is not reachable from Start"; return err.str(); }
+        ready.push_back(i);
+      }
+      if (v_[i].succs.empty() && i != finish_) {
+        err << v_[i].op->desc() << " does not lead to Finish";
+        return err.str();
+      }
+    }
+    while (!ready.empty()) {
+      vid_t i = ready.back();
+      ready.pop_back();
+      ++seen;
+      for (vid_t s : v_[i].succs)
+        if (--indeg[s] == 0) ready.push_back(s);
+    }
+    if (seen != nLive) return "the graph has a cycle";
+    return "";
+  }
+  void sanity_check(const char *where) const {
+#ifdef TENZING_RUNTIME_SANITY_CHECKS
+    const std::string e = validate();
+    if (!e.empty()) THROW_RUNTIME("graph invariant broken after " << where << ": " << e);
+#else
+    (void)where;
+#endif
+  }
 
   // ---- rewrites ----
   // deep copy: every op is cloned
@@ -220,6 +296,7 @@ public:
   Graph clone_but_replace(const op_t &dst, const op_t &src) const {
     Graph g(*this);
     g.replace(src, dst);
+    g.sanity_check("clone_but_replace");
     return g;
   }
   // copy with vertex `op` replaced by the interior of `sub`:
@@ -256,6 +333,7 @@ public:
       if (s == sub.finish_)
         for (vid_t p : myPreds)
           for (vid_t q : mySuccs) g.add_edge(p, q);
+    g.sanity_check("clone_but_expand");
     return g;
   }
   // remove a vertex and its edges

@@ -400,6 +400,11 @@ PYBIND11_MODULE(_C, m) {
       .def("add_edge", [](G &g, const OpPtr &a, const OpPtr &b) { g.add_edge(a, b); })
       .def("vertex_size", &G::vertex_size)
       .def("edge_size", &G::edge_size)
+      .def("validate", &G::validate,
+           "'' if the structural invariants hold (mirrored edges, indexes, acyclic, every vertex on a "
+           "Start..Finish path), else the first violation")
+      .def("preds_find_name", &G::preds_find_name)
+      .def("succs_find_name", &G::succs_find_name)
       .def("contains", &G::contains)
       .def("contains_unbound", &G::contains_unbound)
       .def("find", &G::find)

@@ -230,3 +230,38 @@ def test_use_streams_enumerators():
     for full in _C.use_streams(g, [0, 1]):
         assert sum(_C.is_equivalent_stream_mapping(full, c) for c in canon) == 1
     del keys
+
+
+def test_validate_reports_structural_violations():
+    """Graph.validate(): the invariants TENZING_RUNTIME_SANITY_CHECKS builds assert after rewrites."""
+    g = tz.Graph()
+    a, b, c = tz.NoOp("a"), tz.NoOp("b"), tz.NoOp("c")
+    g.start_then(a)
+    g.then(a, b)
+    g.then_finish(b)
+    assert g.validate() == ""
+    assert g.preds_find_name("b") == (True, [a])
+    assert g.succs_find_name("a") == (True, [b])
+    assert g.preds_find_name("nope") == (False, [])
+    # a vertex that leads nowhere
+    g.then(a, c)
+    assert "does not lead to Finish" in g.validate()
+    g.then_finish(c)
+    assert g.validate() == ""
+    # expansion and replacement keep the invariants
+    sub = tz.Graph()
+    x, y = tz.NoOp("x"), tz.NoOp("y")
+    sub.start_then(x)
+    sub.then(x, y)
+    sub.then_finish(y)
+    assert g.clone_but_expand(b, sub).validate() == ""
+    assert g.clone_but_replace(tz.NoOp("b2"), b).validate() == ""
+    # a cycle
+    g.then(b, a)
+    assert g.validate() == "the graph has a cycle"
+    # erasing the only path to Finish
+    h = tz.Graph()
+    h.start_then(a)
+    h.then_finish(a)
+    h.erase(a)
+    assert h.validate() != ""

@@ -190,3 +190,27 @@ def test_matrix_market_file_is_read_on_root_and_distributed(tmp_path):
 
     _C.loopback_run(3, body)
     assert sum(seen.values()) == A.nnz
+
+
+def test_every_workload_graph_and_rewrite_keeps_the_graph_invariants():
+    """Graph.validate() on every implementation style, and along a random walk through the
+    decision tree (expand / choose / assign-stream rewrites) of the choice graphs."""
+    import random
+    h = HaloExchange(nX=8, nQ=1, nGhost=1, neighbors=6, host=True)
+    s = DistributedSpMV(n=300, nnz_per_row=6, host=True)
+    from tenzing_b200.models import halo as halo_mod, spmv as spmv_mod
+    for wl, styles in ((h, halo_mod.STYLES), (s, spmv_mod.STYLES)):
+        for style in styles + ("choice",):
+            g = wl.graph(style)
+            assert g.validate() == "", (style, g.validate())
+        plat = tz.Platform.make_null(2)
+        rng = random.Random(7)
+        for walk in range(4):
+            st = tz.State(wl.graph("choice"))
+            for _ in range(400):
+                ds = st.get_decisions(plat)
+                if not ds:
+                    break
+                st = st.apply(rng.choice(ds))
+                assert st.graph().validate() == ""
+            assert not st.get_decisions(plat), "walk did not reach a terminal state"
