@@ -155,9 +155,13 @@ def test_native_cpp_test_runner():
     if not os.path.exists(exe):
         import build
         build.build()
-    p = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    p = subprocess.run([exe, "-tc=*[cpu]*"], capture_output=True, text=True, timeout=300)
     assert p.returncode == 0, p.stdout + p.stderr
-    assert "0 failed" in p.stdout
+    assert "0 failed" in p.stdout and "[FAIL]" not in p.stdout
+    listed = subprocess.run([exe, "-ltc"], capture_output=True, text=True, timeout=60).stdout.split("\n")
+    assert len([l for l in listed if l.strip()]) >= 20
+    one = subprocess.run([exe, "-tc=numeric*"], capture_output=True, text=True, timeout=60)
+    assert one.returncode == 0 and "1 cases" in one.stdout
 
 
 def test_json_value_round_trips_and_sorts_keys():
@@ -196,3 +200,87 @@ def test_op_helpers():
     uniq = _C.keep_uniques([var[0], var[1], tz.BoundGpuOp(k, 0), n, tz.NoOp("n")])
     assert [u.desc() for u in uniq] == ["k(s0)", "k(s1)", "n"]
     assert _C.contains([k, n], tz.NoOp("n")) and not _C.contains([k], n)
+
+
+def test_comm_op_library_on_a_null_platform():
+    """Isend / Irecv / Wait / MultiWait / OwningWaitall / Ialltoallv (reference: mpi/ops_mpi.hpp:17-191)
+    are host ops the solver can schedule; with a null transport they only exercise the structure:
+    posts before waits, names kept, JSON round trip through the broadcast format."""
+    tr = _C.P2PTransport(True)
+    plat = tz.Platform.make_null(1)
+    reqs = [_C.Request() for _ in range(4)]
+    isend = _C.Isend(0, 64, 0, 0, reqs[0], tr, "isend")
+    irecv = _C.Irecv(0, reqs[1], tr, "irecv")
+    a2a = _C.Ialltoallv(0, [0, 64], [64, 32], [0, 0], [0, 0], reqs[2], tr, "a2a")
+    wait = _C.Wait(reqs[0], "wait_send")
+    multi = _C.MultiWait([reqs[1], reqs[2]], "wait_many")
+    owning = _C.OwningWaitall([reqs[3]], "wait_owned")
+    g = tz.Graph()
+    for post in (isend, irecv, a2a):
+        g.start_then(post)
+        for w in (wait, multi, owning):
+            g.then(post, w)      # all posts before any wait
+    for w in (wait, multi, owning):
+        g.then_finish(w)
+    assert g.validate() == ""
+    seqs = tz.dfs.get_all_sequences(g, plat, 1000, True)
+    assert len(seqs) == 36           # 3! orders of the posts x 3! orders of the waits
+    for seq in seqs:
+        names = seq.names()
+        assert max(names.index(p) for p in ("isend", "irecv", "a2a")) < \
+            min(names.index(w) for w in ("wait_send", "wait_many", "wait_owned"))
+        seq.run(plat)                # null transport: nothing to copy, nothing to wait for
+    back = _C.sequence_from_json(seqs[0].to_json(g), g)
+    assert back.names() == seqs[0].names()
+    assert all(op.kind() == "CpuOp" or op.name() in ("Start", "Finish") for op in back)
+
+
+def _tzrun():
+    exe = os.path.join(os.path.dirname(HERE), "build", "bin", "tzrun")
+    if not os.path.exists(exe):
+        import build
+        build.build()
+    return exe
+
+
+def test_tzrun_sets_the_rank_environment_and_returns_the_first_failure():
+    exe = _tzrun()
+    p = subprocess.run([exe, "-n", "3", "--port", "31999", "sh", "-c",
+                        'echo "$RANK/$WORLD_SIZE/$LOCAL_RANK/$MASTER_ADDR/$MASTER_PORT"'],
+                       capture_output=True, text=True, timeout=60)
+    assert p.returncode == 0
+    assert sorted(p.stdout.split()) == [f"{r}/3/{r}/127.0.0.1/31999" for r in range(3)]
+    assert subprocess.run([exe], capture_output=True).returncode == 64      # usage
+
+
+def test_tzrun_does_not_hang_when_a_rank_dies():
+    """A dead rank would leave the others waiting in a collective forever (reference: "a rank
+    failure hangs the job"); the launcher ends them after the grace period."""
+    import time
+    exe = _tzrun()
+    t0 = time.time()
+    p = subprocess.run([exe, "-n", "2", "--grace", "1", "sh", "-c",
+                        'if [ "$RANK" = 1 ]; then exit 3; fi; exec sleep 120'],
+                       capture_output=True, text=True, timeout=60)
+    assert p.returncode == 3
+    assert time.time() - t0 < 30
+    assert "rank 1 ended with code 3" in p.stderr
+
+
+def test_tzrun_forwards_signals_to_the_ranks():
+    """SIGABRT from the batch system must reach rank 0's handler (partial CSV dump)."""
+    import signal
+    import time
+    exe = _tzrun()
+    p = subprocess.Popen([exe, "-n", "2", "sh", "-c",
+                          "trap 'echo dumped-$RANK; kill $S; exit 0' ABRT; sleep 120 & S=$!; wait"],
+                         stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    time.sleep(1.0)
+    p.send_signal(signal.SIGABRT)      # this exact process, not a pattern
+    try:
+        out, _ = p.communicate(timeout=30)
+    finally:
+        if p.poll() is None:
+            p.kill()
+    assert p.returncode == 0
+    assert sorted(out.split()) == ["dumped-0", "dumped-1"]
