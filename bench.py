@@ -156,7 +156,9 @@ def main():
                 # ~6 ms per evaluated sequence: never enumerate more than the budget allows
                 res = wl.search("dfs", style=style, bench=bo, max_seqs=int(min(1000, left / 0.006)))
             else:
-                res = wl.search("mcts", style=style, iters=iters, bench=bo, strategy="FastMin")
+                # cache: rollouts that collapse to the same cleaned schedule are measured once
+                res = wl.search("mcts", style=style, iters=iters, bench=bo, strategy="FastMin",
+                                cache=True)
             seq, br = common.best_of(res)
             if seq is not None and br.pct10 < best_t:
                 best_seq, best_t = seq, br.pct10

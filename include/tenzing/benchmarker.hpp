@@ -101,6 +101,41 @@ private:
   std::unordered_map<std::string, size_t> byKey_; // canonical key -> row
 };
 
+// Replays recorded results and (optionally) remembers new ones, asking the wrapped benchmarker
+// only when it has to.  Sequences are identified up to stream/event renaming (canonical key).
+//  * resume: preload the CSV of an interrupted search and run the solver again with the same
+//    seed.  Recorded results are handed out per sequence in the order they were recorded, each
+//    once, so the search retraces the interrupted run exactly without touching the GPU and
+//    starts measuring where that run stopped (the reference cannot resume a search: SURVEY 5.4);
+//  * reuse = true: a sequence that has a result (replayed or measured) is never measured
+//    again.  MCTS rollouts that differ only in redundant synchronisation collapse to one
+//    sequence after cleaning, so a budgeted search stops paying for the same schedule twice.
+// Every rank must hold the same recorded results (same preloaded file), so that all ranks
+// agree on whether a sequence is measured (a collective) or looked up.
+class CachingBenchmarker : public Benchmarker {
+public:
+  explicit CachingBenchmarker(Benchmarker &inner, bool reuse = true) : inner_(inner), reuse_(reuse) {}
+  void preload(const Sequence<BoundOp> &seq, const Benchmark::Result &r);
+  void preload(const CsvBenchmarker &csv);
+  Benchmark::Result benchmark(Sequence<BoundOp> &order, Platform &plat,
+                              const Benchmark::Opts &opts = Benchmark::Opts()) override;
+  size_t hits() const { return hits_; }       // answered without measuring
+  size_t misses() const { return misses_; }   // measured
+  size_t size() const { return known_.size(); } // distinct sequences with a result
+  size_t pending() const { return pending_; } // recorded results not handed out yet
+
+private:
+  struct Entry {
+    Benchmark::Result first;                 // what `reuse` hands out
+    std::vector<Benchmark::Result> recorded; // preloaded results, in order
+    size_t next = 0;                         // next recorded result to hand out
+  };
+  Benchmarker &inner_;
+  bool reuse_;
+  std::unordered_map<std::string, Entry> known_; // canonical key -> results
+  size_t hits_ = 0, misses_ = 0, pending_ = 0;
+};
+
 class ModelBenchmarker : public Benchmarker {
   std::function<double(const Sequence<BoundOp> &)> model_;
 

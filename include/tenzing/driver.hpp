@@ -7,6 +7,7 @@
 #include <cstdlib>
 #include <iostream>
 #include <memory>
+#include <string>
 
 #include "tenzing/tenzing.hpp"
 
@@ -41,6 +42,34 @@ inline Context start(int &argc, char **&argv) {
   return c;
 }
 
+// --resume <csv> / --cache / --seed, shared by the search drivers: wraps the driver's
+// benchmarker in a CachingBenchmarker (see benchmarker.hpp).  With --resume and the same
+// --seed (and the same --cache setting) a search retraces the interrupted run from its CSV and
+// continues measuring where that run stopped; the file must be visible to every rank.
+struct Resume {
+  std::string csv;  // results of an earlier run of the same command ("" = none)
+  bool cache = false;
+  int seed = 0;
+  template <typename Parser> void add_options(Parser &p) {
+    p.add_option(csv, "--resume", "", "results CSV of an interrupted run to continue from");
+    p.add_flag(cache, "--cache", "", "never measure the same schedule twice");
+    p.add_option(seed, "--seed", "", "seed of the search");
+  }
+  bool active() const { return cache || !csv.empty(); }
+  // the benchmarker the solver should use; `holder` keeps the wrapper alive
+  Benchmarker &wrap(Benchmarker &inner, const Graph<OpBase> &g,
+                    std::unique_ptr<CachingBenchmarker> &holder) const {
+    if (!active()) return inner;
+    holder.reset(new CachingBenchmarker(inner, cache));
+    if (!csv.empty()) {
+      CsvBenchmarker prior(csv, g);
+      holder->preload(prior);
+      TENZING_INFO("resume: " << prior.rows().size() << " rows, " << holder->size()
+                              << " distinct schedules from " << csv);
+    }
+    return *holder;
+  }
+};
 
 } // namespace driver
 } // namespace tenzing

@@ -28,6 +28,8 @@ inline int main_impl(int argc, char **argv, const char *defaultStrategy) {
   p.add_option(style, "--style", "", "choice|reference|staged|direct|fused_all|fused_staged");
   p.add_flag(noExpandRollout, "--no-expand-rollout");
   p.add_flag(qxyz, "--qxyz", "", "QXYZ storage order (default XYZQ as in the reference example)");
+  driver::Resume resume;
+  resume.add_options(p);
   p.no_unrecognized();
   if (!p.parse(argc, argv)) {
     std::cerr << p.help();
@@ -58,8 +60,11 @@ inline int main_impl(int argc, char **argv, const char *defaultStrategy) {
     Platform plat = Platform::make_n_streams(streams, ctx.comm,
                                              ctx.haveGpu ? Platform::Device::Cuda : Platform::Device::Null);
     if (ctx.haveGpu && ctx.size > 1 && std::getenv("TENZING_DEVICE_BARRIER")) plat.set_device_barrier(std::make_shared<DeviceBarrier>(ctx.comm));
-    DeviceBenchmarker bench;
+    DeviceBenchmarker device;
+    std::unique_ptr<CachingBenchmarker> cached;
+    Benchmarker &bench = resume.wrap(device, g, cached);
     mcts::Opts opts;
+    opts.seed = uint64_t(resume.seed);
     opts.nIters = size_t(mctsIters);
     opts.expandRollout = !noExpandRollout;
     opts.benchOpts.nIters = size_t(benchIters);

@@ -23,6 +23,7 @@ struct Config {
   bool fp32 = false;
   std::string style = "choice";
   std::string strategy;
+  driver::Resume resume;
 };
 
 inline bool parse(Config &c, int &argc, char **argv, bool mcts) {
@@ -38,6 +39,7 @@ inline bool parse(Config &c, int &argc, char **argv, bool mcts) {
   p.add_option(c.style, "--style", "", "choice|reference|fused|fused_separate");
   p.add_flag(c.random, "--random", "", "uniformly random columns instead of a band");
   p.add_flag(c.fp32, "--fp32", "", "fp32 values (the reference's type) instead of fp64");
+  c.resume.add_options(p);
   p.no_unrecognized();
   if (!p.parse(argc, argv)) {
     std::cerr << p.help();
@@ -70,11 +72,14 @@ template <typename Scalar> int run(const Config &c, driver::Context &ctx, bool m
   Platform plat = Platform::make_n_streams(c.streams, ctx.comm,
                                            ctx.haveGpu ? Platform::Device::Cuda : Platform::Device::Null);
   if (ctx.haveGpu && ctx.size > 1 && std::getenv("TENZING_DEVICE_BARRIER")) plat.set_device_barrier(std::make_shared<DeviceBarrier>(ctx.comm));
-  DeviceBenchmarker bench;
+  DeviceBenchmarker device;
+  std::unique_ptr<CachingBenchmarker> cached;
+  Benchmarker &bench = c.resume.wrap(device, g, cached);
   Benchmark::Opts bo;
   bo.nIters = size_t(c.benchIters);
   if (mcts) {
     mcts::Opts opts;
+    opts.seed = uint64_t(c.resume.seed);
     opts.nIters = size_t(c.mctsIters);
     opts.expandRollout = !c.noExpandRollout;
     opts.benchOpts = bo;

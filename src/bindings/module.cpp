@@ -630,6 +630,15 @@ PYBIND11_MODULE(_C, m) {
         return header_to_py(b.producer());
       });
   py::class_<PyBenchmarker, Benchmarker>(m, "PyBenchmarker").def(py::init<py::object>());
+  py::class_<CachingBenchmarker, Benchmarker>(m, "CachingBenchmarker")
+      .def(py::init<Benchmarker &, bool>(), py::arg("inner"), py::arg("reuse") = true,
+           py::keep_alive<1, 2>())
+      .def("preload", [](CachingBenchmarker &b, const Seq &s, const Benchmark::Result &r) { b.preload(s, r); })
+      .def("preload_csv", [](CachingBenchmarker &b, const CsvBenchmarker &c) { b.preload(c); })
+      .def("hits", &CachingBenchmarker::hits)
+      .def("misses", &CachingBenchmarker::misses)
+      .def("size", &CachingBenchmarker::size)
+      .def("pending", &CachingBenchmarker::pending);
   py::class_<SimBenchmarker, Benchmarker>(m, "SimBenchmarker")
       .def(py::init([](const std::unordered_map<std::string, double> &gpu,
                        const std::unordered_map<std::string, double> &cpu, double defaultGpu,

@@ -1,6 +1,7 @@
 #include "tenzing/benchmarker.hpp"
 
 #include <algorithm>
+#include <charconv>
 #include <chrono>
 #include <cmath>
 #include <fstream>
@@ -151,10 +152,20 @@ double DeviceBenchmarker::timed_run(Sequence<BoundOp> &order, Platform &plat, si
 }
 
 // ---- CSV replay ----
+namespace {
+// shortest text that reads back as exactly the same double: a results file must reproduce
+// the search that wrote it when it is replayed (CachingBenchmarker)
+std::string exact(double v) {
+  char buf[40];
+  auto res = std::to_chars(buf, buf + sizeof(buf), v);
+  return std::string(buf, res.ptr);
+}
+} // namespace
+
 std::string csv_row(size_t idx, const Result &r, const Sequence<BoundOp> &seq) {
   std::ostringstream ss;
-  ss << idx << "|" << r.pct01 << "|" << r.pct10 << "|" << r.pct50 << "|" << r.pct90 << "|"
-     << r.pct99 << "|" << r.stddev;
+  ss << idx << "|" << exact(r.pct01) << "|" << exact(r.pct10) << "|" << exact(r.pct50) << "|"
+     << exact(r.pct90) << "|" << exact(r.pct99) << "|" << exact(r.stddev);
   for (const auto &op : seq) ss << "|" << op->json().dump();
   return ss.str();
 }
@@ -215,6 +226,44 @@ CsvBenchmarker CsvBenchmarker::from_text(const std::string &text, const Graph<Op
   std::istringstream is(text);
   b.load(is, g);
   return b;
+}
+
+// ---- result cache / replay ----
+void CachingBenchmarker::preload(const Sequence<BoundOp> &seq, const Result &r) {
+  auto ins = known_.emplace(canonical_key(seq), Entry{});
+  Entry &e = ins.first->second;
+  if (ins.second) e.first = r;
+  e.recorded.push_back(r);
+  ++pending_;
+}
+
+void CachingBenchmarker::preload(const CsvBenchmarker &csv) {
+  for (const auto &row : csv.rows()) preload(row.seq, row.res);
+}
+
+Result CachingBenchmarker::benchmark(Sequence<BoundOp> &order, Platform &plat, const Opts &opts) {
+  const std::string key = canonical_key(order);
+  auto it = known_.find(key);
+  if (it != known_.end()) {
+    Entry &e = it->second;
+    if (e.next < e.recorded.size()) { // retrace the recorded run
+      ++hits_;
+      --pending_;
+      return e.recorded[e.next++];
+    }
+    if (reuse_) {
+      ++hits_;
+      return e.first;
+    }
+  }
+  ++misses_;
+  const Result r = inner_.benchmark(order, plat, opts);
+  if (it == known_.end()) {
+    Entry e;
+    e.first = r;
+    known_.emplace(key, std::move(e));
+  }
+  return r;
 }
 
 Result CsvBenchmarker::benchmark(Sequence<BoundOp> &order, Platform &, const Opts &) {

@@ -9,7 +9,7 @@ from ._C import (  # noqa: F401
     ChoiceOp, CompoundOp, CudaEventRecord, CudaStreamWaitEvent, CudaEventSync,
     StreamWait, StreamSync, ExecuteOp, ExpandOp, ChooseOp, AssignOpStream,
     EventSynchronizer, BenchOpts, BenchResult, EmpiricalBenchmarker, DeviceBenchmarker,
-    CsvBenchmarker, PyBenchmarker, SimBenchmarker, FlagSynchronizer, SelfComm, SocketComm, PyComm, dfs, mcts,
+    CsvBenchmarker, PyBenchmarker, SimBenchmarker, CachingBenchmarker, FlagSynchronizer, SelfComm, SocketComm, PyComm, dfs, mcts,
 )
 
 __version__ = _C.__version__

@@ -37,6 +37,13 @@ def main(argv=None):
     ap.add_argument("--style", default="choice")
     ap.add_argument("--no-expand-rollout", action="store_true")
     ap.add_argument("--null", action="store_true", help="no GPU: enumerate/search on ids only")
+    ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--resume", default=None, metavar="CSV",
+                    help="results CSV of an interrupted run of the same command: with the same "
+                         "--seed the search replays it from the file and continues measuring "
+                         "where it stopped (every rank must see the same file)")
+    ap.add_argument("--cache", action="store_true",
+                    help="never measure the same schedule twice in this run")
     args = ap.parse_args(argv)
 
     _C.init()
@@ -59,11 +66,12 @@ def main(argv=None):
                                   check_randomness=False)
     if args.solver == "dfs":
         res = wl.search("dfs", style=args.style, benchmarker=benchmarker, bench=bench,
-                        max_seqs=args.max_seqs)
+                        max_seqs=args.max_seqs, resume_csv=args.resume, cache=args.cache)
     else:
         res = wl.search("mcts", style=args.style, benchmarker=benchmarker, bench=bench,
                         iters=args.mcts_iters, strategy=args.strategy,
-                        expand_rollout=not args.no_expand_rollout)
+                        expand_rollout=not args.no_expand_rollout, seed=args.seed,
+                        resume_csv=args.resume, cache=args.cache)
     if rank == 0:
         sys.stdout.write(res.csv())
     if world > 1:

@@ -17,8 +17,27 @@ def bench_opts(n_iters=50, target_secs=0.01, max_retries=2, check_randomness=Tru
                         check_randomness=check_randomness)
 
 
+def with_cache(benchmarker, graph, resume_csv=None, cache=False):
+    """Wrap `benchmarker` in a CachingBenchmarker when asked to.
+
+    resume_csv: path (or text) of the results CSV of an earlier, interrupted run of the same
+    search: with the same seed (and the same `cache` setting) the solver retraces that run from
+    the file and continues where it stopped.  cache=True: never measure a schedule twice.
+    Every rank must be given the same file."""
+    if not resume_csv and not cache:
+        return benchmarker
+    cb = _C.CachingBenchmarker(benchmarker, reuse=bool(cache))
+    if resume_csv:
+        if os.path.exists(resume_csv):
+            prior = _C.CsvBenchmarker(resume_csv, graph)
+        else:
+            prior = _C.CsvBenchmarker.from_text(resume_csv, graph)
+        cb.preload_csv(prior)
+    return cb
+
+
 def search_mcts(graph, platform, benchmarker=None, iters=50, strategy="FastMin", bench=None,
-                seed=0, expand_rollout=True, dump_tree_prefix=None):
+                seed=0, expand_rollout=True, dump_tree_prefix=None, resume_csv=None, cache=False):
     """MCTS over `graph`; returns _C.mcts.Result (rank 0 holds the tree; every rank gets results)."""
     opts = _C.mcts.Opts()
     opts.n_iters = iters
@@ -28,18 +47,18 @@ def search_mcts(graph, platform, benchmarker=None, iters=50, strategy="FastMin",
         opts.dump_tree = True
         opts.dump_tree_prefix = dump_tree_prefix
     opts.bench_opts = bench or bench_opts()
-    benchmarker = benchmarker or _C.DeviceBenchmarker()
+    benchmarker = with_cache(benchmarker or _C.DeviceBenchmarker(), graph, resume_csv, cache)
     return _C.mcts.explore(graph, platform, benchmarker, strategy, opts)
 
 
 def search_dfs(graph, platform, benchmarker=None, max_seqs=-1, bench=None,
-               remove_redundant_syncs=True):
+               remove_redundant_syncs=True, resume_csv=None, cache=False):
     """Exhaustive search; returns _C.dfs.Result."""
     opts = _C.dfs.Opts()
     opts.max_seqs = max_seqs
     opts.remove_redundant_syncs = remove_redundant_syncs
     opts.bench_opts = bench or bench_opts()
-    benchmarker = benchmarker or _C.DeviceBenchmarker()
+    benchmarker = with_cache(benchmarker or _C.DeviceBenchmarker(), graph, resume_csv, cache)
     return _C.dfs.explore(graph, platform, benchmarker, opts)
 
 

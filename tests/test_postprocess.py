@@ -66,3 +66,20 @@ def test_cli_runs_without_a_gpu(capsys):
     assert set(json.loads(out[0])) == {"args", "hash", "major", "minor", "patch"}
     assert out[1] == '{"dfs__Opts":{"maxSeqs":4}}'
     assert len([l for l in out[2:] if "|" in l]) == 4
+
+
+def test_cli_resumes_an_interrupted_search(capsys, tmp_path):
+    """--resume: the second run retraces the first one's rows (same sequences, same numbers)
+    from the file and only measures the additional iterations."""
+    from tenzing_b200 import cli
+    base = ["halo", "--solver", "mcts", "-n", "8", "--nq", "1", "--ghost", "1", "--neighbors", "6",
+            "--style", "fused_mixed", "--null", "--seed", "3", "-b", "2"]
+    assert cli.main(base + ["-i", "6"]) == 0
+    first = capsys.readouterr().out
+    path = tmp_path / "first.csv"
+    path.write_text(first)
+    assert cli.main(base + ["-i", "9", "--resume", str(path)]) == 0
+    second = capsys.readouterr().out
+    rows = lambda text: [l.split("|", 1)[1] for l in text.splitlines() if l[:1].isdigit()]
+    assert len(rows(first)) == 6 and len(rows(second)) == 9
+    assert rows(second)[:6] == rows(first)

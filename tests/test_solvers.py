@@ -299,3 +299,47 @@ def test_tree_dumps_graph_dumps_and_csv_file_replay(tmp_path):
     assert replay.benchmark(r0.path, plat).pct10 == pytest.approx(r0.bench_result.pct10)
     with pytest.raises(RuntimeError):
         replay.benchmark(tz.Sequence([g.start(), g.finish()]), plat)
+
+
+def test_an_interrupted_search_resumes_from_its_csv_without_remeasuring():
+    """CachingBenchmarker: preload the CSV of a 25-iteration run and search again with the same
+    seed for 60 iterations.  The measurement is noisy (every call returns a different time, as on
+    hardware) and the search visits some schedules more than once; the first 25 iterations must
+    still retrace the interrupted run exactly, without calling the benchmark function."""
+    g = fast_slow_graph()
+    plat = tz.Platform.make_null(1)
+    calls = []
+
+    def noisy(seq):
+        calls.append(1)
+        return fast_slow_cost(seq) * (1.0 + 0.013 * ((len(calls) * 7919) % 101) / 101.0)
+
+    def run(iters, bench):
+        opts = _C.mcts.Opts()
+        opts.n_iters = iters
+        opts.seed = 5
+        return _C.mcts.explore(g, plat, bench, "FastMin", opts)
+
+    first = run(25, tz.PyBenchmarker(noisy))
+    assert len(calls) == 25
+    rows = lambda res: [(r.path.names(), r.bench_result.pct10) for r in res.sim_results]
+
+    # resume without reuse: recorded results are replayed in order, everything else is measured
+    replay = tz.CachingBenchmarker(tz.PyBenchmarker(noisy), reuse=False)
+    replay.preload_csv(tz.CsvBenchmarker.from_text(first.csv(), g))
+    assert replay.pending() == 25
+    resumed = run(60, replay)
+    assert rows(resumed)[:25] == rows(first)            # exact, including the float values
+    assert replay.hits() == 25 and replay.misses() == 35 and replay.pending() == 0
+    assert len(calls) == 25 + 35
+
+    # reuse: no schedule is ever measured twice
+    del calls[:]
+    cache = tz.CachingBenchmarker(tz.PyBenchmarker(noisy), reuse=True)
+    deduped = run(60, cache)
+    distinct = {tuple(n) for n, _ in rows(deduped)}
+    assert len(calls) == cache.misses() == len(distinct) == cache.size()
+    assert cache.hits() == 60 - len(distinct)
+    by_seq = {}
+    for n, t in rows(deduped):
+        assert by_seq.setdefault(tuple(n), t) == t      # repeated schedules report the first result
