@@ -33,6 +33,7 @@ struct Dfs {
   ZeroInit<double> ENUMERATE_TIME, DEDUP_TIME, BENCHMARK_TIME;
   ZeroInit<uint64_t> STATES_VISITED, STATES_PRUNED;
 };
+// counters of the calling thread (= of the rank, also when ranks are threads of one process)
 Mcts &mcts();
 Dfs &dfs();
 void reset();

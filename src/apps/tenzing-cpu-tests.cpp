@@ -6,6 +6,7 @@
 //   tenzing-cpu-tests -tc='*graph*'   run the cases whose name matches the glob (* and ?)
 //   tenzing-cpu-tests -ltc            list the case names
 // Exit code = number of failed checks (0 = success).
+#include <atomic>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -18,7 +19,7 @@
 
 using namespace tenzing;
 
-static int g_failed = 0, g_checks = 0;
+static std::atomic<int> g_failed{0}, g_checks{0}; // CHECK is also used inside rank threads
 #define CHECK(cond)                                                                                \
   do {                                                                                             \
     ++g_checks;                                                                                    \
@@ -569,7 +570,7 @@ int main(int argc, char **argv) {
       std::printf("%s\n", c.name);
       continue;
     }
-    const int before = g_failed;
+    const int before = g_failed.load();
     try {
       c.fn();
     } catch (const std::exception &e) {
@@ -577,9 +578,9 @@ int main(int argc, char **argv) {
       std::fprintf(stderr, "FAILED %s: uncaught exception: %s\n", c.name, e.what());
     }
     ++ran;
-    std::printf("[%s] %s\n", g_failed == before ? " ok " : "FAIL", c.name);
+    std::printf("[%s] %s\n", g_failed.load() == before ? " ok " : "FAIL", c.name);
   }
   if (list) return 0;
-  std::printf("%d cases, %d checks, %d failed\n", ran, g_checks, g_failed);
-  return g_failed;
+  std::printf("%d cases, %d checks, %d failed\n", ran, g_checks.load(), g_failed.load());
+  return g_failed.load();
 }

@@ -18,7 +18,7 @@ namespace tenzing {
 
 namespace log {
 int &rank_ref() {
-  static int r = 0;
+  static thread_local int r = 0; // per thread: ranks may be threads (LoopbackWorld)
   return r;
 }
 int &verbosity_ref() {
@@ -64,12 +64,13 @@ bool compound_test(const std::vector<double> &v) { return runs_test(v); }
 
 // ---- counters ----
 namespace counters {
+// per thread: ranks may be threads of one process (LoopbackWorld), and each rank counts its own
 Mcts &mcts() {
-  static Mcts m;
+  static thread_local Mcts m;
   return m;
 }
 Dfs &dfs() {
-  static Dfs d;
+  static thread_local Dfs d;
   return d;
 }
 void reset() {
