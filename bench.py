@@ -14,69 +14,12 @@ import argparse
 import json
 import os
 import statistics
-import subprocess
 import sys
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 os.environ.setdefault("TENZING_ACK_NOTICE", "1")
-
-CLOCK_QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
-               "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-               "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
-
-
-class ClockSampler:
-    """nvidia-smi sampling during the timed region (B200_PROFILING.md recipe)"""
-
-    def __init__(self, gpu_index):
-        self.gpu = gpu_index
-        self.proc = None
-        self.path = f"/tmp/tz_clocks_{os.getpid()}.csv"
-
-    def start(self):
-        try:
-            self.f = open(self.path, "w")
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={CLOCK_QUERY}", "--format=csv,noheader,nounits",
-                 "-lms", "20", "-i", str(self.gpu)], stdout=self.f, stderr=subprocess.DEVNULL)
-        except Exception:
-            self.proc = None
-
-    def stop(self):
-        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
-        if not self.proc:
-            return out
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except Exception:
-            self.proc.kill()
-        self.f.close()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for line in open(self.path):
-            c = [x.strip() for x in line.split(",")]
-            if len(c) < 9:
-                continue
-            try:
-                sm.append(float(c[1]))
-                mx.append(float(c[2]))
-            except ValueError:
-                continue
-            for n, v in zip(names, c[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
-        if sm:
-            out = {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
-                   "samples": len(sm)}
-        try:
-            os.remove(self.path)
-        except OSError:
-            pass
-        return out
-
 
 def reference_arm(args):
     """The reference is a CMake/C++ project that needs MPI (find_package(MPI REQUIRED)) and a
@@ -113,6 +56,7 @@ def main():
     from tenzing_b200.parallel import init_process_group_from_env, make_comm
     from tenzing_b200.models import HaloExchange, DistributedSpMV, common
     from tenzing_b200 import _C, ops
+    from tenzing_b200.utils.clocks import ClockSampler
 
     rank, world, local = init_process_group_from_env()
     comm = make_comm()
@@ -183,9 +127,12 @@ def main():
     ok_h = halo.check()
     search_s = time.time() - t_setup
 
+    # SM clock / throttle reasons: sampled from before the timed region until after the
+    # end-to-end loop (NVML thread + nvidia-smi -lms 20; start() returns once a sample exists)
     sampler = ClockSampler(torch.cuda.current_device())
     if rank == 0:
         sampler.start()
+    comm.barrier()
     times_h, launches_h = timed(halo, seq_h, args.steps, args.warmup)
 
     # ---------------- end to end through the public API ----------------
