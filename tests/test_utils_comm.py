@@ -284,3 +284,33 @@ def test_tzrun_forwards_signals_to_the_ranks():
             p.kill()
     assert p.returncode == 0
     assert sorted(out.split()) == ["dumped-0", "dumped-1"]
+
+
+@pytest.mark.timeout(120)
+def test_cached_search_stays_in_lock_step_across_ranks():
+    """MCTS through a CachingBenchmarker around the collective EmpiricalBenchmarker in a world of
+    two: every rank must skip (or take) the same measurements, or the barriers inside the
+    benchmarker would dead-lock."""
+    out = {}
+
+    def body(rank, comm):
+        g = tz.Graph()
+        for n in ("a", "b", "c"):
+            o = tz.NoOp(n)
+            g.start_then(o)
+            g.then_finish(o)
+        plat = tz.Platform.make_null(1, comm)
+        cache = tz.CachingBenchmarker(tz.EmpiricalBenchmarker(), reuse=True)
+        opts = _C.mcts.Opts()
+        opts.n_iters = 20
+        opts.seed = 1
+        opts.bench_opts = _C.BenchOpts(n_iters=2, max_retries=0, target_secs=1e-5, check_randomness=False)
+        res = _C.mcts.explore(g, plat, cache, "Random", opts)
+        out[rank] = (cache.hits(), cache.misses(), [r.path.names() for r in res.sim_results],
+                     [r.bench_result.pct10 for r in res.sim_results])
+        comm.barrier()
+
+    _C.loopback_run(2, body)
+    assert out[0] == out[1]                      # same hits, same misses, same rows, same numbers
+    hits, misses, rows, _ = out[0]
+    assert misses == len({tuple(r) for r in rows}) <= 6 and hits + misses == len(rows)
