@@ -19,6 +19,7 @@
 #include <cstring>
 #include <memory>
 #include <mutex>
+#include <stdexcept>
 #include <string>
 #include <vector>
 
@@ -58,6 +59,11 @@ public:
 };
 
 // shared state of an in-process world; create one, then one LoopbackComm per thread
+// thrown out of a collective when another rank of the (thread) world has failed
+struct LoopbackAborted : std::runtime_error {
+  LoopbackAborted() : std::runtime_error("LoopbackWorld: another rank failed, collective abandoned") {}
+};
+
 class LoopbackWorld {
   friend class LoopbackComm;
   const int size_;
@@ -65,13 +71,17 @@ class LoopbackWorld {
   std::condition_variable cv_;
   int arrived_ = 0;
   uint64_t generation_ = 0;
+  bool aborted_ = false; // a rank left with an exception: collectives throw instead of waiting
   std::vector<const void *> src_;
   std::vector<void *> dst_;
 
 public:
   explicit LoopbackWorld(int size) : size_(size), src_(size), dst_(size) {}
   int size() const { return size_; }
-  // run body(rank, comm) on `size` threads and join; rethrows the first exception
+  // run body(rank, comm) on `size` threads and join; rethrows the first exception.  When a
+  // rank's body throws, the ranks waiting in a collective are released with an exception too
+  // (a failed rank must not hang the others).
+  void abort();
   static void run(int size, const std::function<void(int, std::shared_ptr<Communicator>)> &body);
 };
 

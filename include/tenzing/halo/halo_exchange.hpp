@@ -171,6 +171,10 @@ class BoxCopyOp : public GpuOp, public HasFlags {
   };
   std::string name_;
   std::shared_ptr<std::array<Plan, 2>> plans_; // shared between clones
+  // host-memory domains keep the boxes themselves: Platform::host_execution() runs them
+  std::shared_ptr<std::array<std::vector<TzbBox>, 2>> hostBoxes_;
+  int elemSize_ = 8;
+  bool ordered_ = false;
   bool null_ = false;
   bool issueOrderOnly_ = false;
   std::vector<uint64_t> published_, awaited_; // flag channels (heap offsets), see set_heap()

@@ -43,6 +43,7 @@ struct Request {
   cudaEvent_t sent = nullptr;     // Send: recorded after copy + flag publish
   const uint64_t *flag = nullptr; // Recv: local flag word to wait for
   uint64_t epoch = 0;
+  bool host = false;              // posted under Platform::host_execution(): no CUDA involved
   ~Request();
   void wait(); // host blocks until the request is complete
 };

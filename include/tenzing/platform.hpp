@@ -171,6 +171,7 @@ private:
   std::unique_ptr<CudaEventPool> pool_;
   std::shared_ptr<Communicator> comm_;
   uint64_t epoch_ = 0;
+  bool hostExec_ = false;
   std::shared_ptr<DeviceBarrier> deviceBarrier_;
 
 public:
@@ -219,6 +220,12 @@ public:
   uint64_t epoch() const { return epoch_; }
   uint64_t next_epoch() { return ++epoch_; }
   void set_epoch(uint64_t e) { epoch_ = e; }
+
+  // Null platform only: execute the ops' host restatement (tenzing/host_exec.hpp) on the
+  // calling thread instead of skipping them, for workloads whose memory is a host-mode
+  // SymmetricHeap.  Sequences then really run - payload, flags, epochs - without a GPU.
+  void set_host_execution(bool on) { hostExec_ = on; }
+  bool host_execution() const { return hostExec_ && is_null(); }
 
   // optional GPU-side all-rank barrier the device-timed benchmarkers use to line up their start
   void set_device_barrier(std::shared_ptr<DeviceBarrier> b) { deviceBarrier_ = std::move(b); }

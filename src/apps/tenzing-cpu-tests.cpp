@@ -549,6 +549,153 @@ TEST_CASE("halo geometry and graphs of every style [cpu]") {
 }
 
 // ---------------------------------------------------------------------------------------------
+// host execution: the workloads really run, ranks are threads (this is what TSan checks)
+// ---------------------------------------------------------------------------------------------
+
+namespace {
+
+// a complete sequence: always the k-th decision offered (k varies the schedule)
+Sequence<BoundOp> walk(const Graph<OpBase> &g, const Platform &plat, size_t k) {
+  SDP::State st(g);
+  for (;;) {
+    auto ds = st.get_decisions(plat);
+    if (ds.empty()) break;
+    st = st.apply(*ds[k % ds.size()]);
+  }
+  Sequence<BoundOp> seq = st.sequence();
+  Schedule::remove_redundant_syncs(seq);
+  return seq;
+}
+
+double cell_value(const Dim3<int> &global, const Dim3<int> &G, int q, int nQ) {
+  auto wrap = [](int v, int n) { return ((v % n) + n) % n; };
+  const int64_t cell = (int64_t(wrap(global.z, G.z)) * G.y + wrap(global.y, G.y)) * G.x + wrap(global.x, G.x);
+  return double(cell * nQ + q);
+}
+
+// interior <- global id, ghosts <- -1
+void halo_fill(const HaloExchange::Domain &dom) {
+  const auto &a = dom.args();
+  const Dim3<int> c = a.rankToCoord(dom.rank());
+  const Dim3<int> G(a.rankGrid.x * a.nX, a.rankGrid.y * a.nY, a.rankGrid.z * a.nZ);
+  double *grid = static_cast<double *>(dom.grid());
+  const Dim3<int> e = dom.extent();
+  const int g = a.nGhost;
+  for (int q = 0; q < a.nQ; ++q)
+    for (int z = 0; z < e.z; ++z)
+      for (int y = 0; y < e.y; ++y)
+        for (int x = 0; x < e.x; ++x) {
+          const bool interior = x >= g && x < g + a.nX && y >= g && y < g + a.nY && z >= g && z < g + a.nZ;
+          const Dim3<int> global(c.x * a.nX + x - g, c.y * a.nY + y - g, c.z * a.nZ + z - g);
+          grid[dom.index(x, y, z, q)] = interior ? cell_value(global, G, q, a.nQ) : -1.0;
+        }
+}
+
+// every cell (ghosts included) holds the periodic global field
+int halo_mismatches(const HaloExchange::Domain &dom) {
+  const auto &a = dom.args();
+  const Dim3<int> c = a.rankToCoord(dom.rank());
+  const Dim3<int> G(a.rankGrid.x * a.nX, a.rankGrid.y * a.nY, a.rankGrid.z * a.nZ);
+  const double *grid = static_cast<const double *>(dom.grid());
+  const Dim3<int> e = dom.extent();
+  const int g = a.nGhost;
+  int bad = 0;
+  for (int q = 0; q < a.nQ; ++q)
+    for (int z = 0; z < e.z; ++z)
+      for (int y = 0; y < e.y; ++y)
+        for (int x = 0; x < e.x; ++x) {
+          const Dim3<int> global(c.x * a.nX + x - g, c.y * a.nY + y - g, c.z * a.nZ + z - g);
+          if (grid[dom.index(x, y, z, q)] != cell_value(global, G, q, a.nQ)) ++bad;
+        }
+  return bad;
+}
+
+} // namespace
+
+TEST_CASE("halo exchange executes on the host: 8 thread ranks, every style, three epochs [cpu]") {
+  using namespace HaloExchange;
+  std::atomic<int> bad{0}, runs{0};
+  LoopbackWorld::run(8, [&](int, std::shared_ptr<Communicator> comm) {
+    Args args;
+    args.nX = 6, args.nY = 5, args.nZ = 4, args.nQ = 2, args.nGhost = 2;
+    args.set_default_topology(comm->size());
+    auto dom = std::make_shared<Domain>(comm, args, SymmetricHeap::Memory::Host);
+    Platform plat = Platform::make_null(2, comm);
+    plat.set_host_execution(true);
+    for (Style st : {Style::Reference, Style::Staged, Style::Direct, Style::FusedAll, Style::FusedStaged,
+                     Style::FusedGroups, Style::FusedMixed, Style::FusedPipelined, Style::FusedPull}) {
+      Graph<OpBase> g;
+      add_to_graph(g, dom, {g.start()}, {g.finish()}, st);
+      for (size_t k = 0; k < 2; ++k) {
+        Sequence<BoundOp> seq = walk(g, plat, k);
+        halo_fill(*dom);
+        comm->barrier();
+        for (int epoch = 0; epoch < 3; ++epoch) run_sequence(seq, plat);
+        comm->barrier();
+        bad += halo_mismatches(*dom);
+        ++runs;
+        comm->barrier();
+      }
+    }
+  });
+  CHECK(bad.load() == 0);
+  CHECK(runs.load() == 8 * 9 * 2);
+}
+
+TEST_CASE("distributed spmv executes on the host: 4 thread ranks, every style [cpu]") {
+  std::atomic<int> bad{0};
+  LoopbackWorld::run(4, [&](int rank, std::shared_ptr<Communicator> comm) {
+    using R = RowPartSpmv<double>;
+    const int64_t n = 203;
+    for (int64_t bw : {int64_t(60), n}) { // band and all-to-all
+      auto spmv = make_band_spmv<double>(comm, n, bw, 6, 9, SymmetricHeap::Memory::Host);
+      Platform plat = Platform::make_null(2, comm);
+      plat.set_host_execution(true);
+      // x = global column id + 1; the oracle multiplies this rank's rows on the host
+      const Range rr = spmv->row_range();
+      for (int64_t i = 0; i < rr.extent(); ++i) spmv->lx()[i] = double(rr.lb + i + 1);
+      std::vector<double> x(static_cast<size_t>(n));
+      for (int64_t i = 0; i < n; ++i) x[size_t(i)] = double(i + 1);
+      const CsrMat<int, double> mine = random_band_rows<int, double>(n, bw, 6, rr.lb, rr.ub, 9);
+      const std::vector<double> want = mine.multiply(x);
+      for (R::Style st : {R::Style::Reference, R::Style::Fused, R::Style::FusedSeparate, R::Style::FusedAll}) {
+        Graph<OpBase> g;
+        auto op = std::make_shared<SpMV<double>>("spmv", spmv, st);
+        g.start_then(op);
+        g.then_finish(op);
+        for (size_t k = 0; k < 2; ++k) {
+          Sequence<BoundOp> seq = walk(g, plat, k);
+          comm->barrier();
+          for (int epoch = 0; epoch < 3; ++epoch) run_sequence(seq, plat);
+          comm->barrier();
+          for (int64_t i = 0; i < rr.extent(); ++i)
+            if (std::fabs(spmv->ly()[i] - want[size_t(i)]) > 1e-9 * std::fabs(want[size_t(i)]) + 1e-12) ++bad;
+          comm->barrier();
+        }
+      }
+      (void)rank;
+    }
+  });
+  CHECK(bad.load() == 0);
+}
+
+TEST_CASE("a flag nobody publishes makes the wait throw, and the world is released [cpu]") {
+  host::set_wait_timeout_seconds(0.3);
+  bool threw = false;
+  try {
+    LoopbackWorld::run(2, [&](int rank, std::shared_ptr<Communicator> comm) {
+      uint64_t flag = 0;
+      if (rank == 0) host::flags_wait(&flag, 1, 1); // never published
+      comm->barrier();
+    });
+  } catch (const std::exception &e) {
+    threw = std::string(e.what()).find("did not reach epoch") != std::string::npos;
+  }
+  host::set_wait_timeout_seconds(20.0);
+  CHECK(threw);
+}
+
+// ---------------------------------------------------------------------------------------------
 
 int main(int argc, char **argv) {
   setenv("TENZING_ACK_NOTICE", "1", 0);

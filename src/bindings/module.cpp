@@ -10,6 +10,7 @@
 #include <pybind11/stl.h>
 
 #include "tenzing/cuda/device_barrier.hpp"
+#include "tenzing/host_exec.hpp"
 #include "tenzing/tenzing.hpp"
 
 namespace py = pybind11;
@@ -165,6 +166,8 @@ PYBIND11_MODULE(_C, m) {
   m.def("parse_reproduce_header",
         [](const std::string &line) { return header_to_py(reproduce::parse_header(line)); });
   m.def("set_verbosity", &log::set_verbosity);
+  m.def("set_host_wait_timeout", &host::set_wait_timeout_seconds, py::arg("seconds"),
+        "seconds a host-executed flag wait may take before it raises (dead-lock detection)");
   m.def("set_log_rank", &log::set_rank);
   m.def("avg", [](const std::vector<double> &v) { return avg(v); });
   m.def("med", [](const std::vector<double> &v) { return med(v); });
@@ -294,6 +297,10 @@ PYBIND11_MODULE(_C, m) {
       .def("comm", &Platform::comm_ptr)
       .def("epoch", &Platform::epoch)
       .def("next_epoch", &Platform::next_epoch)
+      .def("set_host_execution", &Platform::set_host_execution, py::arg("on") = true,
+           "Null platform + host-memory workloads: execute the ops' host restatement instead of "
+           "skipping them (tenzing/host_exec.hpp)")
+      .def("host_execution", &Platform::host_execution)
       .def("enable_device_barrier",
            [](Platform &p) {
              if (!p.is_null() && !p.device_barrier())

@@ -58,18 +58,39 @@ void LoopbackWorld::run(int size,
         body(r, std::make_shared<LoopbackComm>(world, r));
       } catch (...) {
         errors[r] = std::current_exception();
+        world->abort();
       }
     });
   }
   for (auto &t : threads) t.join();
-  for (auto &e : errors)
-    if (e) std::rethrow_exception(e);
+  // report the root cause, not the "world aborted" that it caused on the other ranks
+  std::exception_ptr first;
+  for (auto &e : errors) {
+    if (!e) continue;
+    bool secondary = false;
+    try {
+      std::rethrow_exception(e);
+    } catch (const LoopbackAborted &) {
+      secondary = true;
+    } catch (...) {
+    }
+    if (!secondary) std::rethrow_exception(e);
+    if (!first) first = e;
+  }
+  if (first) std::rethrow_exception(first);
+}
+
+void LoopbackWorld::abort() {
+  std::lock_guard<std::mutex> lk(mu_);
+  aborted_ = true;
+  cv_.notify_all();
 }
 
 template <typename F>
 void LoopbackComm::rendezvous(const void *src, void *dst, F &&atRendezvous) {
   LoopbackWorld &w = *world_;
   std::unique_lock<std::mutex> lk(w.mu_);
+  if (w.aborted_) throw LoopbackAborted();
   w.src_[rank_] = src;
   w.dst_[rank_] = dst;
   const uint64_t gen = w.generation_;
@@ -79,7 +100,8 @@ void LoopbackComm::rendezvous(const void *src, void *dst, F &&atRendezvous) {
     ++w.generation_;
     w.cv_.notify_all();
   } else {
-    w.cv_.wait(lk, [&] { return w.generation_ != gen; });
+    w.cv_.wait(lk, [&] { return w.generation_ != gen || w.aborted_; });
+    if (w.generation_ == gen) throw LoopbackAborted();
   }
 }
 

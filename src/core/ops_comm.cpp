@@ -1,5 +1,7 @@
 #include "tenzing/ops_comm.hpp"
 
+#include "tenzing/host_exec.hpp"
+
 namespace tenzing {
 
 P2PTransport::P2PTransport(bool nullDevice) : null_(nullDevice) {
@@ -18,6 +20,12 @@ Request::~Request() {
 }
 
 void Request::wait() {
+  if (host) {
+    // a host-executed send was complete when it was posted; a receive polls its flag
+    if (kind == Kind::Recv) host::flags_wait(flag, 1, epoch);
+    kind = Kind::None;
+    return;
+  }
   if (!transport || transport->is_null()) return;
   if (kind == Kind::Send) {
     if (sent) CUDA_RUNTIME(cudaEventSynchronize(sent));
@@ -37,6 +45,16 @@ static void mark_sent(Request &r, const std::shared_ptr<P2PTransport> &tr, uint6
 }
 
 void Isend::run(Platform &plat) {
+  if (plat.host_execution()) {
+    if (args_.bytes) host::copy_bytes(args_.peerBuf, args_.buf, args_.bytes);
+    if (args_.peerFlag) host::flag_signal(args_.peerFlag, plat.epoch());
+    if (args_.request) {
+      args_.request->kind = Request::Kind::Send;
+      args_.request->host = true;
+      args_.request->epoch = plat.epoch();
+    }
+    return;
+  }
   if (tr_->is_null() || plat.is_null()) return;
   if (args_.bytes)
     CUDA_RUNTIME(cudaMemcpyAsync(args_.peerBuf, args_.buf, args_.bytes, cudaMemcpyDeviceToDevice,
@@ -54,26 +72,42 @@ void Irecv::run(Platform &plat) {
   args_.request->transport = tr_;
   args_.request->flag = args_.flag;
   args_.request->epoch = plat.epoch();
+  args_.request->host = plat.host_execution();
 }
 
 void Wait::run(Platform &plat) {
-  if (plat.is_null() || !request_) return;
+  if ((plat.is_null() && !plat.host_execution()) || !request_) return;
   request_->wait();
 }
 
 void OwningWaitall::run(Platform &plat) {
-  if (plat.is_null()) return;
+  if (plat.is_null() && !plat.host_execution()) return;
   for (auto &r : reqs_) r->wait();
 }
 
 void MultiWait::run(Platform &plat) {
-  if (plat.is_null()) return;
+  if (plat.is_null() && !plat.host_execution()) return;
   for (auto &r : reqs_) r->wait();
 }
 
 void Ialltoallv::run(Platform &plat) {
-  if (tr_->is_null() || plat.is_null()) return;
   const size_t n = args_.peerBufs.size();
+  if (plat.host_execution()) {
+    for (size_t p = 0; p < n; ++p)
+      if (args_.sendBytes[p])
+        host::copy_bytes(args_.peerBufs[p],
+                         static_cast<const char *>(args_.sendbuf) + args_.sendOffsets[p],
+                         args_.sendBytes[p]);
+    for (size_t p = 0; p < n; ++p)
+      if (args_.peerFlags[p]) host::flag_signal(args_.peerFlags[p], plat.epoch());
+    if (args_.request) {
+      args_.request->kind = Request::Kind::Send;
+      args_.request->host = true;
+      args_.request->epoch = plat.epoch();
+    }
+    return;
+  }
+  if (tr_->is_null() || plat.is_null()) return;
   for (size_t p = 0; p < n; ++p) {
     if (args_.sendBytes[p])
       CUDA_RUNTIME(cudaMemcpyAsync(args_.peerBufs[p],

@@ -53,7 +53,8 @@ Platform::Platform(std::shared_ptr<Communicator> comm, Device device)
 Platform::Platform(Platform &&o) noexcept
     : device_(o.device_), cStreams_(std::move(o.cStreams_)), owned_(std::move(o.owned_)),
       resourceMap_(std::move(o.resourceMap_)), pool_(std::move(o.pool_)),
-      comm_(std::move(o.comm_)), epoch_(o.epoch_), deviceBarrier_(std::move(o.deviceBarrier_)),
+      comm_(std::move(o.comm_)), epoch_(o.epoch_), hostExec_(o.hostExec_),
+      deviceBarrier_(std::move(o.deviceBarrier_)),
       streams_(std::move(o.streams_)) {
   o.cStreams_.clear();
   o.owned_.clear();

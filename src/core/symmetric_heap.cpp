@@ -33,7 +33,8 @@ SymmetricHeap::SymmetricHeap(std::shared_ptr<Communicator> comm, size_t bytes, M
   Hello mine;
   std::memset(&mine, 0, sizeof(mine));
   mine.pid = int64_t(getpid());
-  mine.hostId = int64_t(gethostid());
+  static const int64_t hostId = int64_t(gethostid()); // once: ranks may be threads
+  mine.hostId = hostId;
   void *base = nullptr;
   if (memory_ == Memory::Host) {
     base = std::calloc(bytes_ ? bytes_ : 1, 1);

@@ -1,4 +1,5 @@
 #include "tenzing/halo/halo_exchange.hpp"
+#include "tenzing/host_exec.hpp"
 
 #include <cstring>
 
@@ -200,7 +201,13 @@ uint64_t *Domain::ack_flag(int rank, const Dim3<int> &side) const {
 // ---------------------------------------------------------------- BoxCopyOp
 BoxCopyOp::BoxCopyOp(const std::string &name, const std::vector<TzbBox> &even,
                      const std::vector<TzbBox> &odd, int elemSize, bool nullDevice, bool ordered)
-    : name_(name), plans_(std::make_shared<std::array<Plan, 2>>()), null_(nullDevice) {
+    : name_(name), plans_(std::make_shared<std::array<Plan, 2>>()), elemSize_(elemSize),
+      ordered_(ordered), null_(nullDevice) {
+  if (null_) {
+    hostBoxes_ = std::make_shared<std::array<std::vector<TzbBox>, 2>>();
+    (*hostBoxes_)[0] = even;
+    (*hostBoxes_)[1] = odd;
+  }
   auto make_plan = ordered ? tzb_boxcopy_plan_ordered : tzb_boxcopy_plan;
   const std::vector<TzbBox> *lists[2] = {&even, &odd};
   for (int p = 0; p < 2; ++p) {
@@ -228,6 +235,11 @@ BoxCopyOp::BoxCopyOp(const std::string &name, const std::vector<TzbBox> &even,
 }
 
 void BoxCopyOp::run(Platform &plat, cudaStream_t stream) {
+  if (null_ && plat.host_execution()) {
+    const auto &boxes = (*hostBoxes_)[size_t(plat.epoch() & 1)];
+    host::boxcopy(boxes.data(), int(boxes.size()), elemSize_, plat.epoch(), ordered_);
+    return;
+  }
   if (null_ || plat.is_null()) return;
   const Plan &plan = (*plans_)[size_t(plat.epoch() & 1)];
   CUDA_RUNTIME(cudaError_t(
@@ -306,10 +318,16 @@ public:
   std::string name() const override { return name_; }
   CLONE_DEF(RefIsend)
   void run(Platform &plat) override {
-    if (tr_->null || plat.is_null()) return;
     const int peer = dom_->neighbor(d_);
     const Dim3<int> side = -d_;
     const size_t bytes = dom_->region_elems(d_) * size_t(dom_->args().elemSize);
+    if (tr_->null && plat.host_execution()) {
+      host::copy_bytes(dom_->recv_staging(peer, int(plat.epoch() & 1), side),
+                       dom_->send_staging(dom_->rank(), d_), bytes);
+      host::flag_signal(dom_->flag(peer, Style::Reference, side), plat.epoch());
+      return;
+    }
+    if (tr_->null || plat.is_null()) return;
     CUDA_RUNTIME(cudaMemcpyAsync(dom_->recv_staging(peer, int(plat.epoch() & 1), side),
                                  dom_->send_staging(dom_->rank(), d_), bytes,
                                  cudaMemcpyDeviceToDevice, tr_->send));
@@ -334,6 +352,10 @@ public:
   std::string name() const override { return name_; }
   CLONE_DEF(RefWaitRecv)
   void run(Platform &plat) override {
+    if (tr_->null && plat.host_execution()) {
+      host::flags_wait(dom_->flag(dom_->rank(), Style::Reference, side_), 1, plat.epoch());
+      return;
+    }
     if (tr_->null || plat.is_null()) return;
     CUDA_RUNTIME(cudaError_t(tzb_flags_wait(dom_->flag(dom_->rank(), Style::Reference, side_), 1,
                                             plat.epoch(), tr_->recv)));
@@ -376,6 +398,10 @@ public:
   CLONE_DEF(WaitFlagsOp)
   void run(cudaStream_t) override { THROW_RUNTIME("WaitFlagsOp needs the platform epoch"); }
   void run(Platform &plat, cudaStream_t stream) override {
+    if (null_ && plat.host_execution()) {
+      host::flags_wait(flags_, n_, plat.epoch());
+      return;
+    }
     if (null_ || plat.is_null()) return;
     CUDA_RUNTIME(cudaError_t(tzb_flags_wait(flags_, n_, plat.epoch(), stream)));
   }
@@ -403,6 +429,10 @@ public:
   CLONE_DEF(SignalFlagsOp)
   void run(cudaStream_t) override { THROW_RUNTIME("SignalFlagsOp needs the platform epoch"); }
   void run(Platform &plat, cudaStream_t stream) override {
+    if (null_ && plat.host_execution()) {
+      host::flags_signal(list_, plat.epoch());
+      return;
+    }
     if (null_ || plat.is_null()) return;
     CUDA_RUNTIME(cudaError_t(tzb_flags_signal(&list_, plat.epoch(), stream)));
   }

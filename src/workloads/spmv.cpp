@@ -1,4 +1,5 @@
 #include "tenzing/spmv/row_part_spmv.hpp"
+#include "tenzing/host_exec.hpp"
 
 #include <cstring>
 #include <set>
@@ -237,6 +238,14 @@ public:
   explicit LocalSpMV(SpmvPtr<Scalar> s) : s_(std::move(s)) {}
   std::string name() const override { return "yl"; }
   CLONE_DEF(LocalSpMV)
+  void run(Platform &plat, cudaStream_t st) override {
+    if (s_->null_device() && plat.host_execution()) {
+      const auto &A = s_->lA();
+      host::spmv_csr(A.rows, A.row_ptr(), A.col_ind(), A.values(), s_->lx(), s_->ly(), false);
+      return;
+    }
+    run(st);
+  }
   void run(cudaStream_t st) override {
     if (s_->null_device()) return;
     const auto &A = s_->lA();
@@ -259,10 +268,18 @@ public:
   CLONE_DEF(RemoteSpMV)
   void run(cudaStream_t) override { THROW_RUNTIME("yr needs the platform epoch"); }
   void run(Platform &plat, cudaStream_t st) override {
-    if (s_->null_device() || plat.is_null()) return;
     const auto &A = s_->rA();
     const Scalar *x = s_->rx(s_->rank(), int(plat.epoch() & 1));
     Scalar *y = intoLy_ ? s_->ly() : s_->ry();
+    if (s_->null_device() && plat.host_execution()) {
+      if (wait_)
+        host::spmv_csr_wait(A.rows, A.row_ptr(), A.col_ind(), A.values(), x, y, intoLy_,
+                            s_->flag(s_->rank(), style_, 0), s_->size(), plat.epoch());
+      else
+        host::spmv_csr(A.rows, A.row_ptr(), A.col_ind(), A.values(), x, y, intoLy_);
+      return;
+    }
+    if (s_->null_device() || plat.is_null()) return;
     if (wait_) {
       CUDA_RUNTIME(tzb::spmv_csr_wait(A.rows, A.row_ptr(), A.col_ind(), A.values(), x, y, intoLy_,
                                       A.nnz_per_row(), s_->flag(s_->rank(), style_, 0), s_->size(),
@@ -282,6 +299,13 @@ public:
   explicit Scatter(SpmvPtr<Scalar> s) : s_(std::move(s)) {}
   std::string name() const override { return "Pack"; }
   CLONE_DEF(Scatter)
+  void run(Platform &plat, cudaStream_t st) override {
+    if (s_->null_device() && plat.host_execution()) {
+      host::gather(s_->num_send(), s_->x_send_idx(), s_->lx(), s_->x_send_buf());
+      return;
+    }
+    run(st);
+  }
   void run(cudaStream_t st) override {
     if (s_->null_device()) return;
     CUDA_RUNTIME(k_gather(s_->num_send(), s_->x_send_idx(), s_->lx(), s_->x_send_buf(), st));
@@ -296,6 +320,13 @@ public:
   explicit VectorAdd(SpmvPtr<Scalar> s) : s_(std::move(s)) {}
   std::string name() const override { return "y"; }
   CLONE_DEF(VectorAdd)
+  void run(Platform &plat, cudaStream_t st) override {
+    if (s_->null_device() && plat.host_execution()) {
+      host::vector_add(int(s_->row_range().extent()), s_->ry(), s_->ly());
+      return;
+    }
+    run(st);
+  }
   void run(cudaStream_t st) override {
     if (s_->null_device()) return;
     CUDA_RUNTIME(k_add(int(s_->row_range().extent()), s_->ry(), s_->ly(), st));
@@ -316,6 +347,11 @@ public:
   CLONE_DEF(PackPut)
   void run(cudaStream_t) override { THROW_RUNTIME("PackPut needs the platform epoch"); }
   void run(Platform &plat, cudaStream_t st) override {
+    if (s_->null_device() && plat.host_execution()) {
+      const TzbGatherPutArgs a = make_put_args(*s_, style_, int(plat.epoch() & 1));
+      host::gather_put(a, s_->x_send_idx(), s_->lx(), plat.epoch());
+      return;
+    }
     if (s_->null_device() || plat.is_null()) return;
     const TzbGatherPutArgs a = make_put_args(*s_, style_, int(plat.epoch() & 1));
     CUDA_RUNTIME(k_gather_put(&a, s_->x_send_idx(), s_->lx(), plat.epoch(), s_->counter(), st));
@@ -356,12 +392,20 @@ public:
   CLONE_DEF(FusedAllSpMV)
   void run(cudaStream_t) override { THROW_RUNTIME("SpMVAll needs the platform epoch"); }
   void run(Platform &plat, cudaStream_t st) override {
-    if (s_->null_device() || plat.is_null()) return;
+    const bool hostExec = s_->null_device() && plat.host_execution();
+    if (!hostExec && (s_->null_device() || plat.is_null())) return;
     const int parity = int(plat.epoch() & 1);
     const auto style = St<Scalar>::FusedAll;
     const TzbGatherPutArgs a = make_put_args(*s_, style, parity);
     const auto &L = s_->lA();
     const auto &R = s_->rA();
+    if (hostExec) {
+      host::spmv_fused_all(a, s_->x_send_idx(), L.rows, L.row_ptr(), L.col_ind(), L.values(),
+                           R.row_ptr(), R.col_ind(), R.values(), s_->lx(),
+                           static_cast<const Scalar *>(s_->rx(s_->rank(), parity)), s_->ly(),
+                           s_->flag(s_->rank(), style, 0), s_->size(), plat.epoch());
+      return;
+    }
     CUDA_RUNTIME(tzb::spmv_fused_all(&a, s_->x_send_idx(), L.rows, L.row_ptr(), L.col_ind(),
                                      L.values(), R.row_ptr(), R.col_ind(), R.values(), s_->lx(),
                                      s_->rx(s_->rank(), parity), s_->ly(),
@@ -394,8 +438,16 @@ public:
   std::string name() const override { return "PostSend"; }
   CLONE_DEF(PostSend)
   void run(Platform &plat) override {
-    if (tr_->null || plat.is_null()) return;
     const int parity = int(plat.epoch() & 1), me = s_->rank();
+    if (tr_->null && plat.host_execution()) {
+      for (const auto &p : s_->send_params())
+        host::copy_bytes(s_->rx(p.peer, parity) + p.dstDispl, s_->x_send_buf() + p.displ,
+                         size_t(p.count) * sizeof(Scalar));
+      for (int r = 0; r < s_->size(); ++r)
+        host::flag_signal(s_->flag(r, St<Scalar>::Reference, me), plat.epoch());
+      return;
+    }
+    if (tr_->null || plat.is_null()) return;
     for (const auto &p : s_->send_params())
       CUDA_RUNTIME(cudaMemcpyAsync(s_->rx(p.peer, parity) + p.dstDispl, s_->x_send_buf() + p.displ,
                                    size_t(p.count) * sizeof(Scalar), cudaMemcpyDeviceToDevice,
@@ -429,6 +481,10 @@ public:
   std::string name() const override { return "WaitRecv"; }
   CLONE_DEF(WaitRecv)
   void run(Platform &plat) override {
+    if (tr_->null && plat.host_execution()) {
+      host::flags_wait(s_->flag(s_->rank(), St<Scalar>::Reference, 0), s_->size(), plat.epoch());
+      return;
+    }
     if (tr_->null || plat.is_null()) return;
     CUDA_RUNTIME(cudaError_t(tzb_flags_wait(s_->flag(s_->rank(), St<Scalar>::Reference, 0), s_->size(),
                                             plat.epoch(), tr_->recv)));

@@ -1,0 +1,155 @@
+"""The workloads EXECUTED on the CPU (tenzing/host_exec.hpp): host-memory symmetric heap, Null
+platform with host execution on, ranks as threads of one process.  Payload really moves into the
+neighbour's memory, epoch flags are published with release and polled with acquire semantics,
+staging is double buffered by epoch parity - the device protocol, minus the device.  Every
+implementation style, several searched schedules per style, several epochs per schedule, checked
+against the same oracles as the GPU tests."""
+import random
+
+import pytest
+import torch
+
+import tenzing_b200 as tz
+from tenzing_b200 import _C
+from tenzing_b200.models import DistributedSpMV, HaloExchange, common
+from tenzing_b200.models import halo as halo_mod
+from tenzing_b200.models import spmv as spmv_mod
+
+
+def _schedules(wl, style, n, seed):
+    """the fixed schedule plus up to n-1 random complete walks through the decision tree"""
+    g = wl.graph(style)
+    seqs = [common.fixed_schedule(g, wl.platform)]
+    rng = random.Random(seed)          # same seed on every rank: same walks
+    for _ in range(n - 1):
+        st = tz.State(g)
+        while True:
+            ds = st.get_decisions(wl.platform)
+            if not ds:
+                break
+            st = st.apply(rng.choice(ds))
+        seq = st.sequence()
+        _C.remove_redundant_syncs(seq)
+        seqs.append(seq)
+    return seqs
+
+
+def _run_world(size, body):
+    _C.set_host_wait_timeout(10.0)
+    errors = []
+
+    def guarded(rank, comm):
+        try:
+            body(rank, comm)
+        except BaseException as e:     # noqa: BLE001 - reported on the main thread
+            errors.append((rank, repr(e)))
+            raise
+
+    try:
+        _C.loopback_run(size, guarded)
+    finally:
+        _C.set_host_wait_timeout(20.0)
+    assert not errors, errors
+
+
+@pytest.mark.timeout(300)
+@pytest.mark.parametrize("size,grid", [(1, None), (2, None), (4, None), (8, None), (6, (3, 2, 1))])
+def test_halo_exchange_executes_on_the_cpu_in_every_style(size, grid):
+    def body(rank, comm):
+        h = HaloExchange(comm=comm, nX=6, nY=5, nZ=4, nQ=2, nGhost=2, host=True, rank_grid=grid)
+        h.platform.set_host_execution(True)
+        for style in halo_mod.STYLES:
+            for k, seq in enumerate(_schedules(h, style, 3, seed=11)):
+                h.fill()
+                comm.barrier()
+                h.run(seq, 3)          # three epochs: both staging parities, flags keep growing
+                comm.barrier()
+                assert h.check(), (style, k, rank)
+                comm.barrier()
+
+    _run_world(size, body)
+
+
+@pytest.mark.timeout(300)
+@pytest.mark.parametrize("neighbors,order", [(6, "XYZQ"), (18, "QXYZ"), (26, "QXYZ")])
+def test_halo_variants_execute_on_the_cpu(neighbors, order):
+    def body(rank, comm):
+        h = HaloExchange(comm=comm, nX=5, nY=4, nZ=6, nQ=3, nGhost=1, neighbors=neighbors,
+                         storage_order=order, dtype=torch.float32, host=True)
+        h.platform.set_host_execution(True)
+        for style in ("reference", "staged", "direct", "fused_mixed", "fused_pipelined", "fused_pull"):
+            h.fill()
+            comm.barrier()
+            h.run(common.fixed_schedule(h.graph(style), h.platform), 2)
+            comm.barrier()
+            assert h.check(), (style, rank)
+            comm.barrier()
+
+    _run_world(4, body)
+
+
+@pytest.mark.timeout(300)
+@pytest.mark.parametrize("size", [1, 2, 3, 5])
+def test_distributed_spmv_executes_on_the_cpu_in_every_style(size):
+    def body(rank, comm):
+        for bw in (None, 10 ** 9):     # band (neighbours only) and random columns (all-to-all)
+            s = DistributedSpMV(comm=comm, n=403, bw=bw, nnz_per_row=7, seed=3, host=True)
+            s.platform.set_host_execution(True)
+            for style in spmv_mod.STYLES:
+                for k, seq in enumerate(_schedules(s, style, 3, seed=5)):
+                    s.fill()
+                    comm.barrier()
+                    s.run(seq, 3)
+                    comm.barrier()
+                    assert s.check(), (style, k, rank, bw)
+                    comm.barrier()
+
+    _run_world(size, body)
+
+
+@pytest.mark.timeout(120)
+def test_the_searched_choice_graph_executes_and_a_real_search_runs_on_the_cpu():
+    """MCTS over the ChoiceOp of all styles with the wall-clock benchmarker: every schedule the
+    search tries is really executed by both ranks (host execution), and the winner is correct."""
+    def body(rank, comm):
+        h = HaloExchange(comm=comm, nX=6, nQ=1, nGhost=1, neighbors=6, host=True)
+        h.platform.set_host_execution(True)
+        h.fill()
+        bench = common.bench_opts(n_iters=2, target_secs=1e-5, max_retries=0, check_randomness=False)
+        res = h.search("mcts", style="choice", iters=12, benchmarker=_C.EmpiricalBenchmarker(),
+                       bench=bench, seed=2)
+        seq, _ = common.best_of(res)
+        h.fill()
+        comm.barrier()
+        h.run(seq)
+        comm.barrier()
+        assert h.check()
+        comm.barrier()
+
+    _run_world(2, body)
+
+
+@pytest.mark.timeout(120)
+def test_a_wait_nobody_satisfies_raises_instead_of_hanging():
+    """dead-lock detection: a rank that waits for a flag its partner never publishes gets an
+    exception after the time-out, and the partner is released from its barrier with one too"""
+    seen = {}
+
+    def body(rank, comm):
+        h = HaloExchange(comm=comm, nX=4, nQ=1, nGhost=1, neighbors=6, host=True)
+        h.platform.set_host_execution(True)
+        seq = common.fixed_schedule(h.graph("fused_staged"), h.platform)
+        _C.set_host_wait_timeout(0.5)
+        try:
+            if rank == 0:
+                h.run(seq)             # rank 1 never runs: its flags never arrive
+            comm.barrier()
+        except RuntimeError as e:
+            seen[rank] = str(e)
+            raise
+
+    with pytest.raises(RuntimeError):
+        _C.loopback_run(2, body)
+    _C.set_host_wait_timeout(20.0)
+    assert "did not reach epoch" in seen[0]
+    assert "another rank failed" in seen.get(1, "another rank failed")
