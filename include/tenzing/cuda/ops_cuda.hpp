@@ -61,7 +61,7 @@ public:
   std::string unbound_key() const override { return op_->key(); }
   Json json() const override;
   CLONE_DEF(BoundGpuOp)
-  void run(Platform &plat) override { op_->run(plat, plat.cuda_stream(stream_)); }
+  void run(Platform &plat) override;
   const Stream &stream() const { return stream_; }
   std::vector<Stream> get_streams() const override { return {stream_}; }
   GpuOpPtr unbound() const { return op_; }

@@ -28,6 +28,7 @@ namespace tenzing {
 
 class Communicator;
 class DeviceBarrier;
+class HostStreams;
 
 #define TENZING_ID_HANDLE(NAME)                                                                    \
   class NAME {                                                                                     \
@@ -172,7 +173,11 @@ private:
   std::shared_ptr<Communicator> comm_;
   uint64_t epoch_ = 0;
   bool hostExec_ = false;
+  std::shared_ptr<HostStreams> hostStreams_;
   std::shared_ptr<DeviceBarrier> deviceBarrier_;
+
+  static thread_local uint64_t tlsEpoch_;
+  static thread_local bool tlsEpochSet_;
 
 public:
   std::vector<Stream> streams_; // the streams decisions may bind GPU ops to
@@ -217,7 +222,16 @@ public:
   // sequence happens under a new epoch (all ranks advance it in lock step);
   // fused put/wait kernels use it as the flag value and (epoch & 1) as the
   // staging-buffer parity.
-  uint64_t epoch() const { return epoch_; }
+  uint64_t epoch() const { return tlsEpochSet_ ? tlsEpoch_ : epoch_; }
+  // A task that runs later than it was issued (host streams) sees the epoch of its issue, the
+  // way a kernel keeps the epoch it was launched with.
+  struct EpochScope {
+    explicit EpochScope(uint64_t e) {
+      tlsEpoch_ = e;
+      tlsEpochSet_ = true;
+    }
+    ~EpochScope() { tlsEpochSet_ = false; }
+  };
   uint64_t next_epoch() { return ++epoch_; }
   void set_epoch(uint64_t e) { epoch_ = e; }
 
@@ -226,6 +240,10 @@ public:
   // SymmetricHeap.  Sequences then really run - payload, flags, epochs - without a GPU.
   void set_host_execution(bool on) { hostExec_ = on; }
   bool host_execution() const { return hostExec_ && is_null(); }
+  // Host execution with CUDA's concurrency: one worker thread per stream, events as in CUDA
+  // (tenzing/host_streams.hpp).  Without it host-executed GPU ops run inline, in sequence order.
+  void enable_host_streams();
+  HostStreams *host_streams() const { return host_execution() ? hostStreams_.get() : nullptr; }
 
   // optional GPU-side all-rank barrier the device-timed benchmarkers use to line up their start
   void set_device_barrier(std::shared_ptr<DeviceBarrier> b) { deviceBarrier_ = std::move(b); }

@@ -21,6 +21,7 @@
 #include "tenzing/operation_compound.hpp"
 #include "tenzing/operation_serdes.hpp"
 #include "tenzing/host_exec.hpp"
+#include "tenzing/host_streams.hpp"
 #include "tenzing/ops_comm.hpp"
 #include "tenzing/platform.hpp"
 #include "tenzing/randomness.hpp"

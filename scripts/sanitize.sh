@@ -34,5 +34,16 @@ for kind in $kinds; do
     grep "SUMMARY: \|runtime error:" "$out/report.txt" | sort | uniq -c
     exit 1
   fi
+  if [ "$kind" = tsan ]; then
+    # negative control: a graph that lacks an edge between two writers of one buffer MUST be
+    # reported, or the clean result above would mean nothing
+    TENZING_ACK_NOTICE=1 "$out/tests" "-tc=*[tsan-must-report]*" > /dev/null 2> "$out/control.txt" || true
+    if grep -q "ThreadSanitizer: data race" "$out/control.txt"; then
+      echo "negative control: the racy graph is reported, as it must be"
+    else
+      echo "negative control FAILED: ThreadSanitizer did not report the racy graph" >&2
+      exit 1
+    fi
+  fi
 done
 echo "sanitizers: clean"

@@ -10,7 +10,9 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <chrono>
 #include <functional>
+#include <set>
 #include <thread>
 
 #include "tenzing/halo/halo_exchange.hpp"
@@ -642,7 +644,7 @@ TEST_CASE("halo exchange executes on the host: 8 thread ranks, every style, thre
   CHECK(runs.load() == 8 * 9 * 2);
 }
 
-TEST_CASE("distributed spmv executes on the host: 4 thread ranks, every style [cpu]") {
+TEST_CASE("distributed spmv executes on the host: 4 thread ranks, every style, inline and with stream threads [cpu]") {
   std::atomic<int> bad{0};
   LoopbackWorld::run(4, [&](int rank, std::shared_ptr<Communicator> comm) {
     using R = RowPartSpmv<double>;
@@ -650,7 +652,8 @@ TEST_CASE("distributed spmv executes on the host: 4 thread ranks, every style [c
     for (int64_t bw : {int64_t(60), n}) { // band and all-to-all
       auto spmv = make_band_spmv<double>(comm, n, bw, 6, 9, SymmetricHeap::Memory::Host);
       Platform plat = Platform::make_null(2, comm);
-      plat.set_host_execution(true);
+      if (bw == n) plat.enable_host_streams(); // the all-to-all case also with stream threads
+      else plat.set_host_execution(true);
       // x = global column id + 1; the oracle multiplies this rank's rows on the host
       const Range rr = spmv->row_range();
       for (int64_t i = 0; i < rr.extent(); ++i) spmv->lx()[i] = double(rr.lb + i + 1);
@@ -667,6 +670,7 @@ TEST_CASE("distributed spmv executes on the host: 4 thread ranks, every style [c
           Sequence<BoundOp> seq = walk(g, plat, k);
           comm->barrier();
           for (int epoch = 0; epoch < 3; ++epoch) run_sequence(seq, plat);
+          plat.synchronize();
           comm->barrier();
           for (int64_t i = 0; i < rr.extent(); ++i)
             if (std::fabs(spmv->ly()[i] - want[size_t(i)]) > 1e-9 * std::fabs(want[size_t(i)]) + 1e-12) ++bad;
@@ -677,6 +681,107 @@ TEST_CASE("distributed spmv executes on the host: 4 thread ranks, every style [c
     }
   });
   CHECK(bad.load() == 0);
+}
+
+TEST_CASE("streams as threads: halo schedules run concurrently and correctly [cpu]") {
+  using namespace HaloExchange;
+  std::atomic<int> bad{0};
+  std::atomic<uint64_t> tasks{0};
+  LoopbackWorld::run(4, [&](int, std::shared_ptr<Communicator> comm) {
+    Args args;
+    args.nX = 6, args.nY = 5, args.nZ = 4, args.nQ = 2, args.nGhost = 2;
+    args.set_default_topology(comm->size());
+    auto dom = std::make_shared<Domain>(comm, args, SymmetricHeap::Memory::Host);
+    Platform plat = Platform::make_null(2, comm);
+    plat.enable_host_streams();
+    for (Style st : {Style::Reference, Style::Staged, Style::Direct, Style::FusedAll, Style::FusedStaged,
+                     Style::FusedGroups, Style::FusedMixed, Style::FusedPipelined, Style::FusedPull}) {
+      Graph<OpBase> g;
+      add_to_graph(g, dom, {g.start()}, {g.finish()}, st);
+      for (size_t k = 0; k < 3; ++k) {
+        Sequence<BoundOp> seq = walk(g, plat, k); // k = 1, 2 put ops on the second stream
+        halo_fill(*dom);
+        comm->barrier();
+        for (int epoch = 0; epoch < 3; ++epoch) run_sequence(seq, plat);
+        plat.synchronize();
+        comm->barrier();
+        bad += halo_mismatches(*dom);
+        comm->barrier();
+      }
+    }
+    tasks += plat.host_streams()->tasks_done();
+  });
+  CHECK(bad.load() == 0);
+  CHECK(tasks.load() > 0);
+}
+
+TEST_CASE("host streams: event semantics [cpu]") {
+  HostStreams hs(2);
+  std::atomic<int> order{0};
+  int a = -1, b = -1, c = -1;
+  hs.enqueue(0, [&] {
+    std::this_thread::sleep_for(std::chrono::milliseconds(20));
+    a = order++;
+  });
+  hs.record(7, 0);
+  hs.stream_wait(1, 7); // stream 1 continues only after stream 0's first task
+  hs.enqueue(1, [&] { b = order++; });
+  hs.stream_wait(1, 99); // never recorded: a no-op, as in CUDA
+  hs.enqueue(1, [&] { c = order++; });
+  hs.event_sync(7);
+  CHECK(a == 0);
+  hs.sync_all();
+  CHECK(a == 0 && b == 1 && c == 2);
+  // an exception in a task reaches the host at the next synchronisation, nothing hangs
+  hs.enqueue(0, [] { throw std::runtime_error("kernel failed"); });
+  hs.enqueue(0, [&] { a = 100; }); // skipped: the stream has failed
+  hs.record(8, 0);
+  bool threw = false;
+  try {
+    hs.event_sync(8);
+  } catch (const std::exception &e) {
+    threw = std::string(e.what()) == "kernel failed";
+  }
+  CHECK(threw && a == 0);
+  hs.enqueue(0, [&] { a = 5; }); // usable again
+  hs.sync_all();
+  CHECK(a == 5);
+}
+
+// Not tagged [cpu]: scripts/sanitize.sh runs it under ThreadSanitizer and EXPECTS a report.
+// Two ops on different streams write the same buffer and the graph has no edge between them
+// (the reference's SpMV has exactly this defect between yl and yr): every
+// schedule the solver builds is "correct" by its own rules, and only execution can tell.
+TEST_CASE("racy graph: two unordered ops write one buffer [tsan-must-report]") {
+  Platform plat = Platform::make_null(2);
+  plat.enable_host_streams();
+  std::vector<double> buf(4096, 0.0);
+  struct Writer : GpuOp {
+    std::string n;
+    std::vector<double> *b;
+    double v;
+    Writer(std::string name, std::vector<double> *buf, double val) : n(std::move(name)), b(buf), v(val) {}
+    std::string name() const override { return n; }
+    CLONE_DEF(Writer)
+    void run(cudaStream_t) override {
+      for (auto &x : *b) x = v;
+    }
+  };
+  auto w0 = std::make_shared<Writer>("w0", &buf, 1.0);
+  auto w1 = std::make_shared<Writer>("w1", &buf, 2.0);
+  Graph<OpBase> g;
+  g.start_then(w0);
+  g.start_then(w1); // no edge w0 -> w1
+  g.then_finish(w0);
+  g.then_finish(w1);
+  Sequence<BoundOp> seq = walk(g, plat, 1); // binds the two ops to different streams
+  std::set<int> streams;
+  for (const auto &op : seq)
+    if (auto b = std::dynamic_pointer_cast<BoundGpuOp>(op)) streams.insert(b->stream().id());
+  CHECK(streams.size() == 2);
+  for (int i = 0; i < 20; ++i) run_sequence(seq, plat);
+  plat.synchronize();
+  CHECK(buf[0] == 1.0 || buf[0] == 2.0);
 }
 
 TEST_CASE("a flag nobody publishes makes the wait throw, and the world is released [cpu]") {

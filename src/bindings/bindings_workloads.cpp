@@ -103,13 +103,16 @@ void bind_workloads(py::module_ &m) {
 
   // ---- symmetric heap ----
   py::class_<SymmetricHeap, std::shared_ptr<SymmetricHeap>>(m, "SymmetricHeap")
+      // Collective (other ranks may be threads of this process), so the GIL is released - but
+      // only around the C++ constructor: a call_guard on py::init would also cover pybind's
+      // registration of the new instance, which must happen under the GIL.
       .def(py::init([](std::shared_ptr<Communicator> comm, size_t bytes, bool host) {
+             py::gil_scoped_release rel;
              return std::make_shared<SymmetricHeap>(std::move(comm), bytes,
                                                     host ? SymmetricHeap::Memory::Host
                                                          : SymmetricHeap::Memory::Device);
            }),
-           py::arg("comm"), py::arg("bytes"), py::arg("host") = false,
-           py::call_guard<py::gil_scoped_release>()) // collective: other ranks may be threads
+           py::arg("comm"), py::arg("bytes"), py::arg("host") = false)
       .def("rank", &SymmetricHeap::rank)
       .def("size", &SymmetricHeap::size)
       .def("bytes", &SymmetricHeap::bytes)
@@ -192,12 +195,12 @@ void bind_workloads(py::module_ &m) {
                     [](Args &a, const std::vector<int> &g) { a.rankGrid = Dim3<int>(g.at(0), g.at(1), g.at(2)); });
   py::class_<Domain, std::shared_ptr<Domain>>(h, "Domain")
       .def(py::init([](std::shared_ptr<Communicator> comm, const Args &args, bool host) {
+             py::gil_scoped_release rel; // collective; see SymmetricHeap above
              return std::make_shared<Domain>(std::move(comm), args,
                                              host ? SymmetricHeap::Memory::Host
                                                   : SymmetricHeap::Memory::Device);
            }),
-           py::arg("comm"), py::arg("args"), py::arg("host") = false,
-           py::call_guard<py::gil_scoped_release>())
+           py::arg("comm"), py::arg("args"), py::arg("host") = false)
       .def("rank", &Domain::rank)
       .def("size", &Domain::size)
       .def("extent", [](const Domain &d) { auto e = d.extent(); return std::vector<int>{e.x, e.y, e.z}; })

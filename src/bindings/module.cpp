@@ -249,9 +249,12 @@ PYBIND11_MODULE(_C, m) {
       });
   py::class_<SelfComm, Communicator, std::shared_ptr<SelfComm>>(m, "SelfComm").def(py::init<>());
   py::class_<SocketComm, Communicator, std::shared_ptr<SocketComm>>(m, "SocketComm")
-      .def(py::init<int, int, const std::string &, int, double>(), py::arg("rank"), py::arg("size"),
-           py::arg("addr") = "127.0.0.1", py::arg("port") = 29517, py::arg("timeout") = 120.0,
-           py::call_guard<py::gil_scoped_release>())
+      .def(py::init([](int rank, int size, const std::string &addr, int port, double timeout) {
+             py::gil_scoped_release rel; // blocks until every rank has connected
+             return std::make_shared<SocketComm>(rank, size, addr, port, timeout);
+           }),
+           py::arg("rank"), py::arg("size"), py::arg("addr") = "127.0.0.1", py::arg("port") = 29517,
+           py::arg("timeout") = 120.0)
       .def_static("from_env", &SocketComm::from_env, py::arg("port_offset") = 17);
   py::class_<PyComm, Communicator, std::shared_ptr<PyComm>>(m, "PyComm").def(py::init<py::object>());
   // run fn(rank, comm) on `size` threads sharing a LoopbackWorld
@@ -301,6 +304,9 @@ PYBIND11_MODULE(_C, m) {
            "Null platform + host-memory workloads: execute the ops' host restatement instead of "
            "skipping them (tenzing/host_exec.hpp)")
       .def("host_execution", &Platform::host_execution)
+      .def("enable_host_streams", &Platform::enable_host_streams,
+           "host execution with one worker thread per stream and CUDA's event semantics "
+           "(tenzing/host_streams.hpp): ops on different streams run concurrently unless ordered")
       .def("enable_device_barrier",
            [](Platform &p) {
              if (!p.is_null() && !p.device_barrier())

@@ -1,11 +1,28 @@
 #include "tenzing/cuda/ops_cuda.hpp"
 
+#include "tenzing/host_streams.hpp"
+
 namespace tenzing {
 
 Json BoundGpuOp::json() const {
   Json j = op_->json();
   j["stream"] = stream_.id();
   return j;
+}
+
+void BoundGpuOp::run(Platform &plat) {
+  if (HostStreams *hs = plat.host_streams()) {
+    // issue only: the op runs on its stream's thread, under the epoch it was issued with
+    GpuOpPtr op = op_;
+    Platform *p = &plat;
+    const uint64_t epoch = plat.epoch();
+    hs->enqueue(stream_.id(), [op, p, epoch] {
+      Platform::EpochScope scope(epoch);
+      op->run(*p, nullptr);
+    });
+    return;
+  }
+  op_->run(plat, plat.cuda_stream(stream_));
 }
 
 void SyncOpBase::make_name(const char *prefix, const OpSet &preds, const OpSet &succs) {
@@ -30,6 +47,7 @@ Json CudaEventRecord::json() const {
   return j;
 }
 void CudaEventRecord::run(Platform &plat) {
+  if (HostStreams *hs = plat.host_streams()) return hs->record(event_.id(), stream_.id());
   if (plat.is_null()) return;
   CUDA_RUNTIME(cudaEventRecord(plat.cuda_event(event_), plat.cuda_stream(stream_)));
 }
@@ -43,6 +61,7 @@ Json CudaStreamWaitEvent::json() const {
   return j;
 }
 void CudaStreamWaitEvent::run(Platform &plat) {
+  if (HostStreams *hs = plat.host_streams()) return hs->stream_wait(stream_.id(), event_.id());
   if (plat.is_null()) return;
   CUDA_RUNTIME(cudaStreamWaitEvent(plat.cuda_stream(stream_), plat.cuda_event(event_), 0));
 }
@@ -55,6 +74,7 @@ Json CudaEventSync::json() const {
   return j;
 }
 void CudaEventSync::run(Platform &plat) {
+  if (HostStreams *hs = plat.host_streams()) return hs->event_sync(event_.id());
   if (plat.is_null()) return;
   CUDA_RUNTIME(cudaEventSynchronize(plat.cuda_event(event_)));
 }
@@ -69,6 +89,10 @@ Json StreamWait::json() const {
   return j;
 }
 void StreamWait::run(Platform &plat) {
+  if (HostStreams *hs = plat.host_streams()) {
+    hs->record(event_.id(), waitee_.id());
+    return hs->stream_wait(waiter_.id(), event_.id());
+  }
   if (plat.is_null()) return;
   cudaEvent_t e = plat.cuda_event(event_);
   CUDA_RUNTIME(cudaEventRecord(e, plat.cuda_stream(waitee_)));
@@ -83,6 +107,7 @@ Json StreamSync::json() const {
   return j;
 }
 void StreamSync::run(Platform &plat) {
+  if (HostStreams *hs = plat.host_streams()) return hs->stream_sync(stream_.id());
   if (plat.is_null()) return;
   CUDA_RUNTIME(cudaStreamSynchronize(plat.cuda_stream(stream_)));
 }

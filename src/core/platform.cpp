@@ -1,5 +1,7 @@
 #include "tenzing/platform.hpp"
 
+#include "tenzing/host_streams.hpp"
+
 #include "tenzing/communicator.hpp"
 #include "tenzing/cuda/cuda_runtime.hpp"
 #include "tenzing/cuda/ops_cuda.hpp"
@@ -54,7 +56,7 @@ Platform::Platform(Platform &&o) noexcept
     : device_(o.device_), cStreams_(std::move(o.cStreams_)), owned_(std::move(o.owned_)),
       resourceMap_(std::move(o.resourceMap_)), pool_(std::move(o.pool_)),
       comm_(std::move(o.comm_)), epoch_(o.epoch_), hostExec_(o.hostExec_),
-      deviceBarrier_(std::move(o.deviceBarrier_)),
+      hostStreams_(std::move(o.hostStreams_)), deviceBarrier_(std::move(o.deviceBarrier_)),
       streams_(std::move(o.streams_)) {
   o.cStreams_.clear();
   o.owned_.clear();
@@ -112,7 +114,18 @@ void Platform::provision_events(const Sequence<BoundOp> &seq) {
 
 Communicator &Platform::comm() const { return *comm_; }
 
+void Platform::enable_host_streams() {
+  if (!is_null()) THROW_RUNTIME("host streams belong to a Null platform with host execution");
+  hostExec_ = true;
+  if (!hostStreams_ || hostStreams_->num_streams() < num_streams())
+    hostStreams_ = std::make_shared<HostStreams>(num_streams());
+}
+
+thread_local uint64_t Platform::tlsEpoch_ = 0;
+thread_local bool Platform::tlsEpochSet_ = false;
+
 void Platform::synchronize() const {
+  if (HostStreams *hs = host_streams()) hs->sync_all();
   if (is_null()) return;
   for (cudaStream_t s : cStreams_) CUDA_RUNTIME(cudaStreamSynchronize(s));
 }

@@ -107,6 +107,31 @@ def test_distributed_spmv_executes_on_the_cpu_in_every_style(size):
     _run_world(size, body)
 
 
+@pytest.mark.timeout(300)
+@pytest.mark.parametrize("size", [1, 4])
+def test_streams_as_threads_run_the_schedules_concurrently_and_correctly(size):
+    """enable_host_streams(): every platform stream is a worker thread and events behave as in
+    CUDA, so ops bound to different streams really overlap unless the schedule orders them.
+    Random schedules of every style must still produce the oracle's result."""
+    def body(rank, comm):
+        h = HaloExchange(comm=comm, nX=6, nY=5, nZ=4, nQ=2, nGhost=2, host=True)
+        h.platform.enable_host_streams()
+        s = DistributedSpMV(comm=comm, n=301, nnz_per_row=7, seed=3, host=True)
+        s.platform.enable_host_streams()
+        for wl, styles in ((h, halo_mod.STYLES), (s, spmv_mod.STYLES)):
+            for style in styles:
+                for k, seq in enumerate(_schedules(wl, style, 3, seed=23)):
+                    wl.fill()
+                    comm.barrier()
+                    wl.run(seq, 3)
+                    wl.platform.synchronize()
+                    comm.barrier()
+                    assert wl.check(), (style, k, rank)
+                    comm.barrier()
+
+    _run_world(size, body)
+
+
 @pytest.mark.timeout(120)
 def test_the_searched_choice_graph_executes_and_a_real_search_runs_on_the_cpu():
     """MCTS over the ChoiceOp of all styles with the wall-clock benchmarker: every schedule the
