@@ -64,3 +64,57 @@ def test_every_enumerated_schedule_respects_the_program_order(prog):
                 for i in range(n):
                     assert spans[ops[i].name()][1] <= finish_start + 1e-12, \
                         f"Finish before {ops[i].name()} completed in {seq.desc()} (cleaned={cleaned})"
+
+
+def test_schedules_respect_the_program_order_when_really_executed_on_stream_threads():
+    """The same property, checked by execution instead of simulation: streams are worker threads
+    with CUDA's event semantics (Platform.enable_host_streams), ops are Python callables that
+    log when they start and end.  A successor must never start before its predecessor ended."""
+    import threading
+    import time
+    rng = random.Random(2024)
+    checked = 0
+    for trial in range(12):
+        n = rng.randint(3, 6)
+        gpu = [rng.random() < 0.7 for _ in range(n)]
+        edges = [(i, j) for i in range(n) for j in range(i + 1, n) if rng.random() < 0.4]
+        n_streams = rng.randint(2, 3)
+        log, lock = {}, threading.Lock()
+
+        def body(name, dur):
+            def run(*_):
+                t0 = time.perf_counter()
+                time.sleep(dur)
+                with lock:
+                    log[name] = (t0, time.perf_counter())
+            return run
+
+        ops = []
+        for i in range(n):
+            dur = rng.choice([0.0002, 0.001, 0.003])   # predecessors are often the slow ones
+            name = f"{'g' if gpu[i] else 'c'}{i}"
+            ops.append(tz.PyGpuOp(name, body(name, dur)) if gpu[i] else tz.PyCpuOp(name, body(name, dur)))
+        g = tz.Graph()
+        has_pred, has_succ = set(), set()
+        for a, b in edges:
+            g.then(ops[a], ops[b])
+            has_succ.add(a)
+            has_pred.add(b)
+        for i in range(n):
+            if i not in has_pred:
+                g.start_then(ops[i])
+            if i not in has_succ:
+                g.then_finish(ops[i])
+        plat = tz.Platform.make_null(n_streams)
+        plat.enable_host_streams()
+        seqs = tz.dfs.get_all_sequences(g, plat, 400)
+        for seq in rng.sample(seqs, min(5, len(seqs))):
+            _C.remove_redundant_syncs(seq)
+            log.clear()
+            seq.run(plat)
+            plat.synchronize()
+            assert len(log) == n
+            for a, b in edges:
+                assert log[ops[a].name()][1] <= log[ops[b].name()][0], (seq.names(), a, b)
+            checked += 1
+    assert checked >= 30
