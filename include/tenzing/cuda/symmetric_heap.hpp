@@ -3,7 +3,8 @@
 // CUDA-aware MPI).  Ranks in other processes are mapped through
 // CUDA IPC handles exchanged over the Communicator; ranks in the same process
 // (LoopbackComm threads, one GPU each) use peer access.  A host-memory mode
-// backs CPU-only tests of the set-up code.
+// backs CPU-only runs (set-up tests and host execution, tenzing/host_exec.hpp): ranks that
+// are threads share pointers, ranks in other processes are mapped through POSIX shared memory.
 #pragma once
 
 #include <cstddef>
@@ -65,6 +66,9 @@ private:
   size_t used_ = 0;
   std::vector<void *> bases_;
   std::vector<bool> ipcOpened_;
+  std::vector<bool> shmMapped_; // host mode: peers in other processes mapped through /dev/shm
+  bool localShm_ = false;       // host mode: my allocation is a shared-memory segment
+  char shmName_[48] = {0};
 };
 
 } // namespace tenzing

@@ -46,6 +46,24 @@ inline Context start(int &argc, char **&argv) {
 // benchmarker in a CachingBenchmarker (see benchmarker.hpp).  With --resume and the same
 // --seed (and the same --cache setting) a search retraces the interrupted run from its CSV and
 // continues measuring where that run stopped; the file must be visible to every rank.
+// --host-exec [--host-streams]: no GPU, but run the ops for real on the CPU (host-memory heap,
+// tenzing/host_exec.hpp); with --host-streams every stream is a worker thread.
+struct HostExec {
+  bool on = false, streams = false;
+  template <typename Parser> void add_options(Parser &p) {
+    p.add_flag(on, "--host-exec", "", "execute the ops on the CPU (host memory) instead of a GPU");
+    p.add_flag(streams, "--host-streams", "", "with --host-exec: one worker thread per stream");
+  }
+  // call before the workload allocates: host execution needs the host-memory heap
+  void apply(Context &ctx) const {
+    if (on || streams) ctx.haveGpu = false;
+  }
+  void apply(Platform &plat) const {
+    if (streams) plat.enable_host_streams();
+    else if (on) plat.set_host_execution(true);
+  }
+};
+
 struct Resume {
   std::string csv;  // results of an earlier run of the same command ("" = none)
   bool cache = false;

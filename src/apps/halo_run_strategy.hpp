@@ -30,11 +30,14 @@ inline int main_impl(int argc, char **argv, const char *defaultStrategy) {
   p.add_flag(qxyz, "--qxyz", "", "QXYZ storage order (default XYZQ as in the reference example)");
   driver::Resume resume;
   resume.add_options(p);
+  driver::HostExec hostExec;
+  hostExec.add_options(p);
   p.no_unrecognized();
   if (!p.parse(argc, argv)) {
     std::cerr << p.help();
     return 1;
   }
+  hostExec.apply(ctx);
   try {
     HaloExchange::Args args;
     args.nQ = nQ, args.nX = args.nY = args.nZ = n, args.nGhost = nGhost;
@@ -60,6 +63,7 @@ inline int main_impl(int argc, char **argv, const char *defaultStrategy) {
     Platform plat = Platform::make_n_streams(streams, ctx.comm,
                                              ctx.haveGpu ? Platform::Device::Cuda : Platform::Device::Null);
     if (ctx.haveGpu && ctx.size > 1 && std::getenv("TENZING_DEVICE_BARRIER")) plat.set_device_barrier(std::make_shared<DeviceBarrier>(ctx.comm));
+    hostExec.apply(plat);
     DeviceBenchmarker device;
     std::unique_ptr<CachingBenchmarker> cached;
     Benchmarker &bench = resume.wrap(device, g, cached);

@@ -24,6 +24,7 @@ struct Config {
   std::string style = "choice";
   std::string strategy;
   driver::Resume resume;
+  driver::HostExec hostExec;
 };
 
 inline bool parse(Config &c, int &argc, char **argv, bool mcts) {
@@ -40,6 +41,7 @@ inline bool parse(Config &c, int &argc, char **argv, bool mcts) {
   p.add_flag(c.random, "--random", "", "uniformly random columns instead of a band");
   p.add_flag(c.fp32, "--fp32", "", "fp32 values (the reference's type) instead of fp64");
   c.resume.add_options(p);
+  c.hostExec.add_options(p);
   p.no_unrecognized();
   if (!p.parse(argc, argv)) {
     std::cerr << p.help();
@@ -65,6 +67,7 @@ Graph<OpBase> make_graph(const std::shared_ptr<RowPartSpmv<Scalar>> &spmv, const
 }
 
 template <typename Scalar> int run(const Config &c, driver::Context &ctx, bool mcts) {
+  c.hostExec.apply(ctx);
   const auto mem = ctx.haveGpu ? SymmetricHeap::Memory::Device : SymmetricHeap::Memory::Host;
   const int64_t bw = c.random ? c.m : std::max(1, c.m / ctx.size); // reference: spmv.cu:87-88
   auto spmv = make_band_spmv<Scalar>(ctx.comm, c.m, bw, c.nnzPerRow, 0, mem);
@@ -72,6 +75,7 @@ template <typename Scalar> int run(const Config &c, driver::Context &ctx, bool m
   Platform plat = Platform::make_n_streams(c.streams, ctx.comm,
                                            ctx.haveGpu ? Platform::Device::Cuda : Platform::Device::Null);
   if (ctx.haveGpu && ctx.size > 1 && std::getenv("TENZING_DEVICE_BARRIER")) plat.set_device_barrier(std::make_shared<DeviceBarrier>(ctx.comm));
+  c.hostExec.apply(plat);
   DeviceBenchmarker device;
   std::unique_ptr<CachingBenchmarker> cached;
   Benchmarker &bench = c.resume.wrap(device, g, cached);

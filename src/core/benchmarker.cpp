@@ -204,12 +204,13 @@ void CsvBenchmarker::load(std::istream &is, const Graph<OpBase> &g) {
       if (data_.empty()) continue; // a textual column header
       THROW_RUNTIME("csv line " << lineNo << ": bad statistics columns");
     }
+    // the row's ops are resolved together: alternatives of a ChoiceOp may share op names
+    Json ops = Json::array();
     for (size_t c = 7; c < cols.size(); ++c) {
       if (cols[c].empty()) continue; // padded rows
-      BoundOpPtr op;
-      from_json(Json::parse(cols[c]), g, op);
-      row.seq.push_back(op);
+      ops.push_back(Json::parse(cols[c]));
     }
+    from_json(ops, g, row.seq);
     byKey_.emplace(canonical_key(row.seq), data_.size());
     data_.push_back(std::move(row));
   }

@@ -1,8 +1,14 @@
 #include "tenzing/cuda/symmetric_heap.hpp"
 
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
+#include <atomic>
+
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
 #include <unistd.h>
 
 #include "tenzing/cuda/cuda_runtime.hpp"
@@ -29,6 +35,7 @@ SymmetricHeap::SymmetricHeap(std::shared_ptr<Communicator> comm, size_t bytes, M
   size_ = n;
   bases_.assign(size_t(n), nullptr);
   ipcOpened_.assign(size_t(n), false);
+  shmMapped_.assign(size_t(n), false);
 
   Hello mine;
   std::memset(&mine, 0, sizeof(mine));
@@ -37,9 +44,38 @@ SymmetricHeap::SymmetricHeap(std::shared_ptr<Communicator> comm, size_t bytes, M
   mine.hostId = hostId;
   void *base = nullptr;
   if (memory_ == Memory::Host) {
-    base = std::calloc(bytes_ ? bytes_ : 1, 1);
+    // Ranks in other processes (torchrun + gloo, tzrun + sockets) reach this rank's host heap
+    // through POSIX shared memory, so host execution works with one process per rank as well;
+    // ranks that are threads of this process simply use the pointer.
+    int64_t pid = mine.pid;
+    std::vector<int64_t> pids(static_cast<size_t>(n));
+    comm_->allgather(&pid, pids.data(), sizeof(pid));
+    bool otherProcess = false;
+    for (int64_t p : pids) otherProcess = otherProcess || p != pid;
+    if (otherProcess) {
+      static std::atomic<uint64_t> counter{0};
+      std::snprintf(shmName_, sizeof(shmName_), "/tzb_%lld_%llu", static_cast<long long>(pid),
+                    static_cast<unsigned long long>(counter++));
+      const size_t len = bytes_ ? bytes_ : 1;
+      int fd = shm_open(shmName_, O_CREAT | O_EXCL | O_RDWR, 0600);
+      if (fd >= 0 && ftruncate(fd, off_t(len)) == 0) {
+        void *p = mmap(nullptr, len, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+        if (p != MAP_FAILED) {
+          base = p; // fresh shared memory reads as zero
+          localShm_ = true;
+        }
+      }
+      if (fd >= 0) close(fd);
+      if (!localShm_) {
+        if (fd >= 0) shm_unlink(shmName_);
+        shmName_[0] = 0;
+      }
+    }
+    if (!base) base = std::calloc(bytes_ ? bytes_ : 1, 1);
     if (!base) THROW_RUNTIME("SymmetricHeap: host allocation of " << bytes_ << " bytes failed");
     mine.device = -1;
+    static_assert(sizeof(shmName_) <= sizeof(mine.handle), "the name travels in the handle field");
+    std::memcpy(&mine.handle, shmName_, sizeof(shmName_));
   } else {
     int dev = 0;
     CUDA_RUNTIME(cudaGetDevice(&dev));
@@ -74,8 +110,22 @@ SymmetricHeap::SymmetricHeap(std::shared_ptr<Communicator> comm, size_t bytes, M
       }
     } else {
       if (memory_ == Memory::Host) {
-        // dry-run across processes (no GPU): ops are no-ops in this mode and never
-        // dereference a peer pointer, so the peer base stays null
+        // another process: map its shared-memory segment (stays null if it has none, e.g.
+        // on another host - then only dry runs work, ops never dereference a peer pointer)
+        char name[sizeof(shmName_)];
+        std::memcpy(name, &h.handle, sizeof(name));
+        name[sizeof(name) - 1] = 0;
+        if (name[0] && h.hostId == mine.hostId) {
+          int fd = shm_open(name, O_RDWR, 0600);
+          if (fd >= 0) {
+            void *p = mmap(nullptr, bytes_ ? bytes_ : 1, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+            close(fd);
+            if (p != MAP_FAILED) {
+              bases_[size_t(r)] = p;
+              shmMapped_[size_t(r)] = true;
+            }
+          }
+        }
         continue;
       }
       if (h.hostId != mine.hostId) THROW_RUNTIME("SymmetricHeap: rank " << r << " is on another host");
@@ -86,14 +136,19 @@ SymmetricHeap::SymmetricHeap(std::shared_ptr<Communicator> comm, size_t bytes, M
     }
   }
   comm_->barrier();
+  // every peer has mapped the segment: the name can go, the memory lives until the last unmap
+  if (localShm_) shm_unlink(shmName_);
 }
 
 SymmetricHeap::~SymmetricHeap() {
   const int me = rank_;
-  for (size_t r = 0; r < bases_.size(); ++r)
+  for (size_t r = 0; r < bases_.size(); ++r) {
     if (ipcOpened_[r] && bases_[r]) cudaIpcCloseMemHandle(bases_[r]);
+    if (shmMapped_[r] && bases_[r]) munmap(bases_[r], bytes_ ? bytes_ : 1);
+  }
   if (memory_ == Memory::Host) {
-    std::free(bases_[size_t(me)]);
+    if (localShm_) munmap(bases_[size_t(me)], bytes_ ? bytes_ : 1);
+    else std::free(bases_[size_t(me)]);
   } else if (bases_[size_t(me)]) {
     cudaFree(bases_[size_t(me)]);
   }

@@ -37,6 +37,10 @@ def main(argv=None):
     ap.add_argument("--style", default="choice")
     ap.add_argument("--no-expand-rollout", action="store_true")
     ap.add_argument("--null", action="store_true", help="no GPU: enumerate/search on ids only")
+    ap.add_argument("--host-exec", action="store_true",
+                    help="no GPU, but execute the ops for real on the CPU (host memory)")
+    ap.add_argument("--host-streams", action="store_true",
+                    help="with --host-exec: one worker thread per stream, CUDA event semantics")
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--resume", default=None, metavar="CSV",
                     help="results CSV of an interrupted run of the same command: with the same "
@@ -51,7 +55,7 @@ def main(argv=None):
     comm = make_comm()
     if rank == 0:
         print(_C.reproduce_header([sys.argv[0]] + (argv if argv is not None else sys.argv[1:])))
-    host = args.null or not torch.cuda.is_available()
+    host = args.null or args.host_exec or args.host_streams or not torch.cuda.is_available()
     if args.workload == "spmv":
         wl = DistributedSpMV(comm=comm, n=args.matrix_m, bw=args.matrix_m if args.random else None,
                              dtype=torch.float32 if args.fp32 else torch.float64, host=host,
@@ -59,6 +63,10 @@ def main(argv=None):
     else:
         wl = HaloExchange(comm=comm, nX=args.n, nQ=args.nq, nGhost=args.ghost,
                           neighbors=args.neighbors, host=host, n_streams=args.streams)
+    if args.host_streams:
+        wl.platform.enable_host_streams()
+    elif args.host_exec:
+        wl.platform.set_host_execution(True)
     bench = common.bench_opts(n_iters=args.benchmark_iters)
     benchmarker = _C.EmpiricalBenchmarker() if host else _C.DeviceBenchmarker()
     if host:

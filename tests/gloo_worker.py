@@ -1,5 +1,7 @@
-"""2-rank CPU worker (gloo): DFS + MCTS in lock step over torch.distributed, halo/SpMV set-up
-in host-memory mode is NOT possible across processes, so only the control plane is used here."""
+"""2-rank CPU worker (gloo), launched like bench.py is (one process per rank): DFS + MCTS in
+lock step over torch.distributed, then both workloads EXECUTED on the CPU - host-memory
+symmetric heap mapped across the two processes through POSIX shared memory, host execution of
+every op, the cross-process flag protocol - and checked against the oracles."""
 import os
 import sys
 
@@ -35,6 +37,32 @@ keys = [r.path.canonical_key() for r in res.sim_results]
 gathered = [None, None]
 dist.all_gather_object(gathered, keys)
 assert gathered[0] == gathered[1] and len(keys) > 0
+dist.barrier()
+
+# the workloads for real, one process per rank
+from tenzing_b200.models import DistributedSpMV, HaloExchange, common  # noqa: E402
+from tenzing_b200.models import halo as halo_mod, spmv as spmv_mod  # noqa: E402
+
+_C.set_host_wait_timeout(20.0)
+halo = HaloExchange(comm=comm, nX=6, nY=5, nZ=4, nQ=2, nGhost=2, host=True)
+halo.platform.enable_host_streams()
+spmv = DistributedSpMV(comm=comm, n=301, nnz_per_row=7, seed=3, host=True)
+spmv.platform.set_host_execution(True)
+for wl, styles in ((halo, halo_mod.STYLES), (spmv, spmv_mod.STYLES)):
+    for style in styles:
+        seq = common.fixed_schedule(wl.graph(style), wl.platform)
+        wl.fill()
+        comm.barrier()
+        wl.run(seq, 3)
+        wl.platform.synchronize()
+        comm.barrier()
+        assert wl.check(), (style, rank)
+        comm.barrier()
+# and a search whose every candidate is executed by both processes
+res = halo.search("mcts", style="fused_mixed", iters=5, benchmarker=_C.EmpiricalBenchmarker(),
+                  bench=common.bench_opts(n_iters=2, target_secs=1e-5, max_retries=0,
+                                          check_randomness=False))
+assert len(res.sim_results) == 5
 dist.barrier()
 if rank == 0:
     print("GLOO_WORKER_OK", flush=True)

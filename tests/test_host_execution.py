@@ -155,6 +155,53 @@ def test_the_searched_choice_graph_executes_and_a_real_search_runs_on_the_cpu():
 
 
 @pytest.mark.timeout(120)
+def test_searching_the_spmv_choice_graph_resolves_same_named_ops_of_different_styles():
+    """Every SpMV style has ops called "yl" / "yr" / "PackPut", and they are different ops (other
+    flag sets, other outputs).  A broadcast sequence names ops only by name, so the receiving
+    ranks must pick the alternative the SET of names identifies - otherwise ranks execute
+    different kernels and wait for flags nobody publishes.  (Found by host execution: the
+    multi-rank search over the choice graph timed out in a flag wait.)"""
+    def body(rank, comm):
+        s = DistributedSpMV(comm=comm, n=301, nnz_per_row=7, seed=3, host=True)
+        s.platform.set_host_execution(True)
+        s.fill()
+        bench = common.bench_opts(n_iters=2, target_secs=1e-5, max_retries=0, check_randomness=False)
+        res = s.search("mcts", style="choice", iters=24, benchmarker=_C.EmpiricalBenchmarker(),
+                       bench=bench, seed=4)
+        styles_seen = set()
+        for r in res.sim_results:
+            names = set(r.path.names())
+            styles_seen.add("fused_all" if "SpMVAll" in names else "reference" if "PostSend" in names
+                            else "fused_separate" if "y" in names else "fused")
+        assert len(styles_seen) >= 3, styles_seen       # the search did try several styles
+        seq, _ = common.best_of(res)
+        s.fill()
+        comm.barrier()
+        s.run(seq, 2)
+        comm.barrier()
+        assert s.check()
+        comm.barrier()
+
+    _run_world(3, body)
+
+
+def test_sequence_json_round_trip_picks_the_right_alternative():
+    s = DistributedSpMV(n=120, nnz_per_row=5, host=True)
+    g = s.graph("choice")
+    plat = s.platform
+    for style in spmv_mod.STYLES:
+        want = common.fixed_schedule(s.graph(style), plat)
+        back = _C.sequence_from_json(want.to_json(s.graph(style)), g)    # resolved in the choice graph
+        assert back.names() == want.names()
+        # the resolved ops are the chosen alternative's own ops: executing them gives the answer
+        plat.set_host_execution(True)
+        s.fill()
+        s.run(back, 2)
+        assert s.check(), style
+        plat.set_host_execution(False)
+
+
+@pytest.mark.timeout(120)
 def test_a_wait_nobody_satisfies_raises_instead_of_hanging():
     """dead-lock detection: a rank that waits for a flag its partner never publishes gets an
     exception after the time-out, and the partner is released from its barrier with one too"""

@@ -314,3 +314,27 @@ def test_cached_search_stays_in_lock_step_across_ranks():
     assert out[0] == out[1]                      # same hits, same misses, same rows, same numbers
     hits, misses, rows, _ = out[0]
     assert misses == len({tuple(r) for r in rows}) <= 6 and hits + misses == len(rows)
+
+
+@pytest.mark.timeout(300)
+def test_native_drivers_execute_on_the_cpu_with_one_process_per_rank():
+    """tzrun + SocketComm + host execution: the native search drivers really run both workloads
+    (host heap shared between the processes through POSIX shared memory), including the search
+    over the ChoiceOp of all implementation styles."""
+    tzrun = _tzrun()
+    bindir = os.path.dirname(tzrun)
+    env = dict(os.environ, TENZING_ACK_NOTICE="1", TENZING_HOST_WAIT_SECS="10")
+    port = 30100 + os.getpid() % 300
+    runs = [
+        (2, ["spmv-min-time", "-i", "10", "-b", "2", "-m", "2000", "--host-exec"], 10),
+        # DFS: up to 12 sequences, fewer after equivalent ones are dropped
+        (3, ["spmv", "--max-seqs", "12", "-b", "2", "-m", "2000", "--host-exec", "--style", "fused"], None),
+        (2, ["halo-mcts-min-time", "-i", "6", "-b", "2", "-n", "8", "--host-streams"], 6),
+    ]
+    for k, (n, cmd, rows) in enumerate(runs):
+        p = subprocess.run([tzrun, "-n", str(n), "--grace", "3", "--port", str(port + k),
+                            os.path.join(bindir, cmd[0])] + cmd[1:],
+                           capture_output=True, text=True, timeout=200, env=env)
+        assert p.returncode == 0, (cmd, p.stderr[-2000:])
+        data = [l for l in p.stdout.splitlines() if l[:1].isdigit()]
+        assert (len(data) == rows) if rows else (0 < len(data) <= 12), (cmd, p.stdout[-1000:])
