@@ -155,6 +155,12 @@ int tzb_boxcopy_static(const TzbBox *boxes, int nBoxes, int elemSize, uint64_t e
 /* message of the last failed tzb_boxcopy_static call on this thread ("" if none) */
 const char *tzb_last_error(void);
 
+/* Host interpreter of a plan image (the bytes tzb_boxcopy_plan wrote): executes the work items
+ * one by one with memcpy on HOST pointers; flags are ignored.  A checking tool for the planner -
+ * the result must equal the plain loop nest over the boxes.  Returns the number of items
+ * executed, -1 for a malformed image. */
+long long tzb_boxcopy_host_execute(const void *hostImage, size_t imageBytes);
+
 /* ----------------------------------------------------------------- flags ---- */
 /* publish epoch to up to 32 (possibly peer) flags; wait for n contiguous local flags. */
 typedef struct {

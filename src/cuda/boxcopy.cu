@@ -215,7 +215,9 @@ box_copy_sync_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restri
     }
     if (b.wait) {
       // the data of this box is only there once the producer published this epoch
-      if (threadIdx.x == 0 && !((readyMask >> (w.box & 31)) & 1u)) {
+      // the mask remembers the first 32 boxes only; later ones are polled every time (a
+      // satisfied flag costs one load)
+      if (threadIdx.x == 0 && !(w.box < 32 && ((readyMask >> w.box) & 1u))) {
         wait_flag_geq(b.wait, epoch);
         if (w.box < 32) readyMask |= 1u << w.box;
       }
@@ -448,6 +450,38 @@ int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t
                                                                 info->nBoxes, anySignal, epoch, ctr);
   }
   return cudaGetLastError();
+}
+
+// Host interpreter of a plan image: performs the copies item by item with memcpy.  A checking
+// tool for the planner (every element of every box must be covered by exactly one work item);
+// flags are neither waited for nor published.  Returns the number of items executed, -1 on a
+// malformed image.
+long long tzb_boxcopy_host_execute(const void *hostImage, size_t imageBytes) {
+  if (!hostImage || imageBytes < sizeof(PlanHeader)) return -1;
+  PlanHeader h;
+  std::memcpy(&h, hostImage, sizeof(h));
+  if (h.nBoxes < 0 || h.nItems < 0 || (h.elemSize != 4 && h.elemSize != 8)) return -1;
+  const size_t need = sizeof(PlanHeader) + sizeof(BoxDesc) * size_t(h.nBoxes) + sizeof(WorkItem) * size_t(h.nItems);
+  if (imageBytes < need) return -1;
+  const char *p = static_cast<const char *>(hostImage) + sizeof(PlanHeader);
+  const BoxDesc *boxes = reinterpret_cast<const BoxDesc *>(p);
+  const WorkItem *items = reinterpret_cast<const WorkItem *>(p + sizeof(BoxDesc) * size_t(h.nBoxes));
+  const int64_t es = h.elemSize;
+  for (int it = 0; it < h.nItems; ++it) {
+    const WorkItem &w = items[it];
+    if (w.box < 0 || w.box >= h.nBoxes) return -1;
+    const BoxDesc &b = boxes[w.box];
+    if (w.i3 < 0 || w.i3 >= std::max(b.n3, 1) || w.i2 < 0 || w.i2 + w.c2 > b.n2 || w.i1 < 0 ||
+        w.i1 + w.c1 > b.n1)
+      return -1;
+    for (int j2 = 0; j2 < w.c2; ++j2)
+      for (int j1 = 0; j1 < w.c1; ++j1) {
+        const int64_t so = int64_t(w.i3) * b.s3 + int64_t(w.i2 + j2) * b.s2 + int64_t(w.i1 + j1) * b.s1;
+        const int64_t dof = int64_t(w.i3) * b.d3 + int64_t(w.i2 + j2) * b.d2 + int64_t(w.i1 + j1) * b.d1;
+        std::memcpy(b.dst + dof * es, b.src + so * es, size_t(b.run) * size_t(es));
+      }
+  }
+  return h.nItems;
 }
 
 int tzb_flags_signal(const TzbFlagList *list, uint64_t epoch, void *stream) {
