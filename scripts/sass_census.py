@@ -1,0 +1,75 @@
+#!/usr/bin/env python
+"""SASS census of the kernel library: per kernel, the memory / synchronisation / tensor / TMA
+instructions in the sm_100a SASS (cuobjdump -sass).  Writes profiles/sass_census.txt.
+
+  python scripts/sass_census.py [path/to/libtenzing_b200_kernels.so]
+"""
+import collections
+import os
+import re
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "tenzing_b200", "libtenzing_b200_kernels.so")
+KEEP = re.compile(r"^(LD|ST|ATOM|RED|MEMBAR|ERRBAR|CCTL|BAR|NANOSLEEP|SHFL|UBLKCP|UTMA|SYNCS|HMMA|IMMA|DMMA|"
+                  r"UTC|FENCE|LDSM|STSM|LDGSTS|UCGABAR)")
+HEADER = """# SASS census of libtenzing_b200_kernels.so (cuobjdump -sass, sm_100a): memory / sync / math
+# instructions per kernel (scripts/sass_census.py).  What to look for: ST*.STRONG.SYS +
+# MEMBAR.*.SYS + ERRBAR = the release side of the cross-GPU flag protocol; LD*.STRONG.SYS +
+# NANOSLEEP = the acquire spin; LDG/ST .128 = 16-byte accesses on aligned sides; UBLKCP.S.G /
+# UBLKCP.G.S + SYNCS.*.TRANS64 = the bulk-copy engine (cp.async.bulk + mbarrier) of the
+# experimental box_bulk_kernel; no HMMA/UTC*MMA anywhere (bandwidth-bound kernels, no tensor-core
+# work).
+"""
+
+
+def demangle(names):
+    try:
+        out = subprocess.run(["cu++filt"] + names, capture_output=True, text=True, check=True).stdout
+        return out.splitlines()
+    except Exception:
+        return names
+
+
+def strip_params(name):
+    """drop the parameter list: cut at the first '(' outside the template argument brackets"""
+    depth = 0
+    for i, c in enumerate(name):
+        if c == "<":
+            depth += 1
+        elif c == ">":
+            depth -= 1
+        elif c == "(" and depth == 0:
+            return name[:i]
+    return name
+
+
+def main():
+    sass = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True, check=True).stdout
+    kernels, cur = collections.OrderedDict(), None
+    for line in sass.splitlines():
+        m = re.search(r"Function : (\S+)", line)
+        if m:
+            cur = m.group(1)
+            kernels[cur] = collections.Counter()
+            continue
+        m = re.match(r"\s+/\*[0-9a-f]+\*/\s+(?:@!?U?P\d+\s+)?([A-Z][A-Z0-9_.]*)", line)
+        if m and cur and KEEP.match(m.group(1)) and not m.group(1).startswith(("LDC", "LDCU")):
+            kernels[cur][m.group(1)] += 1
+    names = demangle(list(kernels))
+    lines = [HEADER]
+    for mangled, name in zip(kernels, names):
+        short = re.sub(r"\(anonymous namespace\)::|<unnamed>::", "", name)
+        short = strip_params(re.sub(r"^void ", "", short))
+        short = short.replace("tzb::", "", 1) if short.startswith("tzb::box") or short.startswith("tzb::spmv") or short.startswith("tzb::gather") else short
+        ops = ", ".join(f"{k} x{v}" for k, v in sorted(kernels[mangled].items()))
+        lines.append(f"{short}\n    {ops}")
+    path = os.path.join(ROOT, "profiles", "sass_census.txt")
+    with open(path, "w") as f:
+        f.write("\n".join(lines) + "\n")
+    print(f"{len(kernels)} kernels -> {path}")
+
+
+if __name__ == "__main__":
+    main()

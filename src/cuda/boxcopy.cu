@@ -235,6 +235,120 @@ box_copy_sync_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restri
   }
 }
 
+// ---------------------------------------------------------------------------------------
+// EXPERIMENTAL (opt-in: TZB_BULK=1): the copy engine of the SM does the moving.
+// For plans whose every row is 16-byte aligned on both sides and at least 512 bytes long (the
+// "thick" regions: 4 KB rows of the y/z faces and edges, i.e. the data that crosses NVLink
+// un-staged), one thread per block drives a ring of shared-memory stages with
+//   cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes   (global -> smem)
+//   cp.async.bulk.global.shared::cta.bulk_group                         (smem -> global/peer)
+// so no registers or LSU slots are spent on the payload and the NVLink side sees one bulk
+// store per row instead of thousands of 16-byte ones.  Blocks are one warp; up to seven fit
+// on an SM next to each other (32 KB of stages each).
+// Status: compiles for sm_100a (SASS: UBLKCP, SYNCS.ARRIVE.TRANS64), NOT yet run on hardware -
+// the round's GPU budget was spent when it was written; it is off unless TZB_BULK=1.
+constexpr int kBulkStages = 4;
+constexpr int kBulkStageBytes = 8192;
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+__global__ void __launch_bounds__(32)
+box_bulk_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restrict__ items, int nItems,
+                int nBoxes, int elemSize, int anySignal, uint64_t epoch, unsigned *counter) {
+  __shared__ alignas(128) unsigned char stage[kBulkStages][kBulkStageBytes];
+  __shared__ alignas(8) uint64_t bar[kBulkStages];
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kBulkStages; ++s)
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar[s])) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  __syncwarp();
+  if (threadIdx.x == 0) {
+    uint32_t g = 0; // segments issued so far by this block: stage = g % kBulkStages, use = g / kBulkStages
+    for (int it = blockIdx.x; it < nItems; it += gridDim.x) {
+      const WorkItem w = items[it];
+      const BoxDesc &b = boxes[w.box];
+      const int64_t rowBytes = int64_t(b.run) * elemSize;
+      const int cpr = int((rowBytes + kBulkStageBytes - 1) / kBulkStageBytes); // chunks per row
+      const int nseg = w.c1 * w.c2 * cpr;
+      const char *src = b.src + int64_t(w.i3) * b.s3 * elemSize;
+      char *dst = b.dst + int64_t(w.i3) * b.d3 * elemSize;
+      auto locate = [&](int k, const char *&sp, char *&dp, uint32_t &bytes) {
+        const int r = k / cpr, c = k - r * cpr;
+        const int j2 = r / w.c1, j1 = r - j2 * w.c1;
+        const int64_t off = int64_t(c) * kBulkStageBytes;
+        sp = src + (int64_t(w.i2 + j2) * b.s2 + int64_t(w.i1 + j1) * b.s1) * elemSize + off;
+        dp = dst + (int64_t(w.i2 + j2) * b.d2 + int64_t(w.i1 + j1) * b.d1) * elemSize + off;
+        const int64_t left = rowBytes - off;
+        bytes = uint32_t(left < kBulkStageBytes ? left : kBulkStageBytes);
+      };
+      auto issue_load = [&](int k) {
+        const char *sp;
+        char *dp;
+        uint32_t bytes;
+        locate(k, sp, dp, bytes);
+        const uint32_t s = (g + uint32_t(k)) % kBulkStages;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%1], %0;" ::"r"(bytes),
+                     "r"(smem_u32(&bar[s]))
+                     : "memory");
+        asm volatile(
+            "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                smem_u32(stage[s])),
+            "l"(sp), "r"(bytes), "r"(smem_u32(&bar[s]))
+            : "memory");
+      };
+      const int pre = nseg < kBulkStages ? nseg : kBulkStages;
+      for (int k = 0; k < pre; ++k) issue_load(k);
+      for (int k = 0; k < nseg; ++k) {
+        const uint32_t n = g + uint32_t(k);
+        const uint32_t s = n % kBulkStages, parity = (n / kBulkStages) & 1u;
+        asm volatile(
+            "{\n\t"
+            ".reg .pred P1;\n\t"
+            "WAIT_%=:\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
+            "@P1 bra DONE_%=;\n\t"
+            "bra WAIT_%=;\n\t"
+            "DONE_%=:\n\t"
+            "}" ::"r"(smem_u32(&bar[s])),
+            "r"(parity)
+            : "memory");
+        const char *sp;
+        char *dp;
+        uint32_t bytes;
+        locate(k, sp, dp, bytes);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dp),
+                     "r"(smem_u32(stage[s])), "r"(bytes)
+                     : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        // refill the stage of the PREVIOUS segment: its store has finished reading shared
+        // memory once at most one bulk group (the one just committed) is still pending
+        if (k >= 1 && k - 1 + kBulkStages < nseg) {
+          asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          issue_load(k - 1 + kBulkStages);
+        }
+      }
+      // all stages free again before the next item's prologue reuses them
+      asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+      g += uint32_t(nseg);
+    }
+    // stores complete (not merely read) before this block reports in
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    asm volatile("fence.proxy.async;" ::: "memory");
+  }
+  __syncwarp();
+  if (anySignal) {
+    if (block_arrive_last(counter, gridDim.x)) {
+      for (int bx = threadIdx.x; bx < nBoxes; bx += 32)
+        if (boxes[bx].signal) st_release_sys(boxes[bx].signal, epoch);
+    }
+  }
+}
+
 __global__ void flags_signal_kernel(TzbFlagList l, uint64_t epoch) {
   if (int(threadIdx.x) < l.n) {
     __threadfence_system();
@@ -362,6 +476,20 @@ static int boxcopy_plan_impl(const TzbBox *boxes, int nBoxes, int elemSize, TzbB
     };
     if (aligned(in.src, in.s1, in.s2, in.s3) || aligned(in.dst, in.d1, in.d2, in.d3)) info->reserved |= 8;
   }
+  // bit 4: every row of every box can go through the bulk-copy engine (16-byte aligned on both
+  // sides, a multiple of 16 bytes and at least 512 bytes long); see box_bulk_kernel
+  bool bulk = nBoxes > 0;
+  for (int b = 0; b < nBoxes && bulk; ++b) {
+    const TzbBox &in = boxes[b];
+    const int64_t rowBytes = int64_t(in.run) * elemSize;
+    auto ok = [&](const void *p, int64_t s1, int64_t s2, int64_t s3) {
+      return (reinterpret_cast<uintptr_t>(p) & 15) == 0 && (s1 * elemSize) % 16 == 0 &&
+             (s2 * elemSize) % 16 == 0 && (s3 * elemSize) % 16 == 0;
+    };
+    bulk = rowBytes >= 512 && rowBytes % 16 == 0 && ok(in.src, in.s1, in.s2, in.s3) &&
+           ok(in.dst, in.d1, in.d2, in.d3);
+  }
+  if (bulk) info->reserved |= 16;
   info->planBytes = sizeof(PlanHeader) + sizeof(BoxDesc) * size_t(nBoxes) + sizeof(WorkItem) * items.size();
   info->scratchBytes = (sizeof(unsigned) * size_t(nBoxes + 1) + 255) / 256 * 256; // arrival counters
   info->payloadBytes = payload;
@@ -385,6 +513,14 @@ int tzb_boxcopy_plan(const TzbBox *boxes, int nBoxes, int elemSize, TzbBoxPlanIn
 int tzb_boxcopy_plan_ordered(const TzbBox *boxes, int nBoxes, int elemSize, TzbBoxPlanInfo *info,
                              void *hostImage) {
   return boxcopy_plan_impl(boxes, nBoxes, elemSize, info, hostImage, true);
+}
+
+static bool bulk_enabled() {
+  static const bool on = [] {
+    const char *e = std::getenv("TZB_BULK");
+    return e && std::atoi(e) != 0;
+  }();
+  return on;
 }
 
 int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t epoch,
@@ -437,6 +573,11 @@ int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t
     else
       box_copy_sync_kernel<float, kBlocksPerSM><<<blocks, kThreads, 0, s>>>(
           boxes, items, info->nItems, info->nBoxes, anySignal, epoch, ctr);
+  } else if ((info->reserved & 16) && bulk_enabled()) {
+    // experimental bulk-copy path (see box_bulk_kernel); one warp per block, 7 blocks per SM
+    const int blocks = grid(kSMs * 7);
+    box_bulk_kernel<<<blocks, 32, 0, s>>>(boxes, items, info->nItems, info->nBoxes, info->elemSize,
+                                          anySignal, epoch, ctr);
   } else {
     const int blocks = grid(kSMs * kBlocksPerSM);
     if (info->elemSize == 8 && vec)

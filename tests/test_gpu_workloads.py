@@ -1,5 +1,7 @@
 """Single-GPU end-to-end checks of both workloads: every implementation style must
 produce exactly the oracle result, for both epoch parities (double buffers)."""
+import os
+
 import pytest
 import torch
 
@@ -155,3 +157,28 @@ def test_host_posted_p2p_ops_in_a_searched_graph():
         torch.cuda.synchronize()
         exp = (torch.arange(n, dtype=torch.float64, device="cuda") + float(plat.epoch())) * 2
         assert torch.equal(out, exp)
+
+
+@pytest.mark.skipif(os.environ.get("TENZING_TEST_EXPERIMENTAL") != "1",
+                    reason="experimental bulk-copy path (TZB_BULK=1): not yet validated on hardware; "
+                           "set TENZING_TEST_EXPERIMENTAL=1 to run it")
+def test_experimental_bulk_copy_path_matches_the_oracle():
+    """box_bulk_kernel (cp.async.bulk + mbarrier) on the thick regions of the halo exchange.
+    Runs in a subprocess under a hard time limit: a pipeline bug would hang the kernel."""
+    import subprocess
+    import sys
+    code = (
+        "import os, torch\n"
+        "os.environ['TENZING_ACK_NOTICE'] = '1'\n"
+        "from tenzing_b200.models import HaloExchange, common\n"
+        "from tenzing_b200 import ops\n"
+        "for nx, dtype in ((64, torch.float64), (128, torch.float32), (512, torch.float64)):\n"
+        "    h = HaloExchange(nX=nx, nQ=2, nGhost=3, dtype=dtype)\n"
+        "    for style in ('fused_mixed', 'fused_all', 'direct'):\n"
+        "        seq = common.fixed_schedule(h.graph(style), h.platform)\n"
+        "        h.fill(); h.run(seq, 3); assert h.check(), (nx, style)\n"
+        "print('BULK_OK')\n")
+    env = dict(os.environ, TZB_BULK="1")
+    p = subprocess.run(["timeout", "120", sys.executable, "-c", code], capture_output=True, text=True,
+                       env=env, cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    assert p.returncode == 0 and "BULK_OK" in p.stdout, (p.stdout + p.stderr)[-3000:]
