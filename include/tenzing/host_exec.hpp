@@ -53,6 +53,12 @@ void gather_put(const TzbGatherPutArgs &args, const int *idx, const T *src, uint
 template <typename T>
 void spmv_csr_wait(int rows, const int *rowPtr, const int *colInd, const T *val, const T *x, T *y,
                    bool accumulate, const uint64_t *flags, int nFlags, uint64_t epoch);
+// pull form: wait for the ready flags, product with x read through xPtr, then the acks
+// (tzb_spmv_csr_pull_*)
+template <typename T>
+void spmv_csr_pull(int rows, const int *rowPtr, const int *colInd, const T *val,
+                   const T *const *xPtr, T *y, bool accumulate, const uint64_t *ready, int nReady,
+                   const TzbFlagList &acks, uint64_t epoch);
 // the whole distributed product (tzb_spmv_fused_all_*)
 template <typename T>
 void spmv_fused_all(const TzbGatherPutArgs &put, const int *sendIdx, int rows, const int *lRowPtr,

@@ -42,7 +42,10 @@ public:
     int count = 0;
     int dstDispl = 0; // send only: offset in the peer's rx
   };
-  enum class Style { Reference, Fused, FusedSeparate, FusedAll };
+  // FusedPull is experimental (its kernel has not run on hardware yet): it is built on request
+  // only and is not among the alternatives of make_spmv_choice unless asked for
+  enum class Style { Reference, Fused, FusedSeparate, FusedAll, FusedPull };
+  static constexpr int kFlagSets = 6; // one per style + the acknowledgements of FusedPull
 
   // myRows: the rows [get_partition(n, rank, size)) of the global n x n matrix, global column ids
   RowPartSpmv(std::shared_ptr<Communicator> comm, const CsrMat<int, Scalar> &myRows, int64_t n,
@@ -75,6 +78,12 @@ public:
   uint64_t *flag(int rank, Style style, int src) const {
     return heap_->at<uint64_t>(rank, flagOff_) + size_t(int(style)) * size_t(size()) + size_t(src);
   }
+  // second flag set of the pull style: "rank `src` has finished reading rank `rank`'s x"
+  uint64_t *ack_flag(int rank, int src) const {
+    return heap_->at<uint64_t>(rank, flagOff_) + size_t(kFlagSets - 1) * size_t(size()) + size_t(src);
+  }
+  // pull style: address of every remote column in its owner's x (peer pointers), device array
+  const Scalar *const *x_ptrs() const { return static_cast<const Scalar *const *>(xPtrs_.get()); }
   uint32_t *counter() const { return static_cast<uint32_t *>(counter_.get()); }
   // bytes of x this rank receives per product
   size_t recv_bytes() const { return size_t(num_remote_cols()) * sizeof(Scalar); }
@@ -87,7 +96,7 @@ private:
   Range range_;
   SplitMat<int, Scalar> split_;
   DeviceCsr<Scalar> lA_, rA_;
-  std::shared_ptr<void> xSendIdx_, counter_;
+  std::shared_ptr<void> xSendIdx_, counter_, xPtrs_;
   int numSend_ = 0;
   std::vector<Param> sendParams_, recvParams_;
   std::vector<int> peers_;
@@ -102,6 +111,11 @@ private:
 //   Start -> {yl, PackPut}; {yl, PackPut} -> yr (waits on flags, accumulates into y) -> Finish
 // FusedSeparate keeps yl and yr independent and adds them in `y`.  FusedAll is one op: a
 // single kernel that puts, multiplies locally, waits for the peers and accumulates the remote part.
+// FusedPull moves nothing ahead of time: XReady tells every rank "my x is final", yrPull waits
+// for those flags and reads the remote x entries straight from their owners over NVLink while
+// it multiplies (the gather is fused into the off-diagonal product), then acknowledges;
+// XFree waits for the acknowledgements, after which x may be overwritten:
+//   Start -> {yl, XReady}; {yl, XReady} -> yrPull -> XFree -> Finish
 template <typename Scalar> class SpMV : public CompoundOp {
   std::string name_;
   Graph<OpBase> graph_;
@@ -115,9 +129,10 @@ public:
   CLONE_DEF(SpMV)
 };
 
-// ChoiceOp "spmv" over the four styles
+// ChoiceOp "spmv" over the four validated styles (+ the experimental pull style on request)
 template <typename Scalar>
-std::shared_ptr<ChoiceOp> make_spmv_choice(const std::shared_ptr<RowPartSpmv<Scalar>> &spmv);
+std::shared_ptr<ChoiceOp> make_spmv_choice(const std::shared_ptr<RowPartSpmv<Scalar>> &spmv,
+                                           bool withExperimental = false);
 
 // Root-held matrix -> one row block per rank (reference: send_matrix / receive_matrix,
 // row_part_spmv.cuh:18-90, four MPI_Isend + Probe/Recv per peer).  Rank `root` passes the whole

@@ -69,6 +69,21 @@ int tzb_spmv_csr_wait_f32(int rows, const int *rowPtr, const int *colInd, const 
                           const float *x, float *y, int accumulate, const uint64_t *flags,
                           int nFlags, uint64_t epoch, void *stream);
 
+/* Pull form (EXPERIMENTAL, not yet validated on hardware): the gather of the remote x entries
+ * happens inside the product.  xPtr[c] is the address of remote column c in its owner's x (a
+ * peer pointer); every block waits until the nReady local `ready` flags reached the epoch (all
+ * owners declared their x final), then y (+)= A_remote x; the last block publishes the epoch to
+ * the flags in `acks` ("I have finished reading your x").  `counter`: one zeroed uint32. */
+struct TzbFlagList_;
+int tzb_spmv_csr_pull_f64(int rows, const int *rowPtr, const int *colInd, const double *val,
+                          const double *const *xPtr, double *y, int accumulate,
+                          const uint64_t *ready, int nReady, const struct TzbFlagList_ *acks,
+                          uint64_t epoch, uint32_t *counter, void *stream);
+int tzb_spmv_csr_pull_f32(int rows, const int *rowPtr, const int *colInd, const float *val,
+                          const float *const *xPtr, float *y, int accumulate,
+                          const uint64_t *ready, int nReady, const struct TzbFlagList_ *acks,
+                          uint64_t epoch, uint32_t *counter, void *stream);
+
 /* The whole distributed product in one launch (no counterpart in the reference, where it is
  * seven ops): gather-put of my x entries to every peer + flag publish, y = A_local x, wait for
  * the nFlags local flags, y += A_remote rx.  `counter`: one zeroed uint32 of scratch. */
@@ -163,7 +178,7 @@ long long tzb_boxcopy_host_execute(const void *hostImage, size_t imageBytes);
 
 /* ----------------------------------------------------------------- flags ---- */
 /* publish epoch to up to 32 (possibly peer) flags; wait for n contiguous local flags. */
-typedef struct {
+typedef struct TzbFlagList_ {
   int n;
   uint64_t *flag[32];
 } TzbFlagList;

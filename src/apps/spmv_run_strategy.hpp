@@ -60,6 +60,8 @@ Graph<OpBase> make_graph(const std::shared_ptr<RowPartSpmv<Scalar>> &spmv, const
   else if (style == "fused") op = std::make_shared<SpMV<Scalar>>("spmv", spmv, Style::Fused);
   else if (style == "fused_separate") op = std::make_shared<SpMV<Scalar>>("spmv", spmv, Style::FusedSeparate);
   else if (style == "fused_all") op = std::make_shared<SpMV<Scalar>>("spmv", spmv, Style::FusedAll);
+  else if (style == "fused_pull") op = std::make_shared<SpMV<Scalar>>("spmv", spmv, Style::FusedPull);
+  else if (style == "choice+") op = make_spmv_choice<Scalar>(spmv, true); // with experimental styles
   else THROW_RUNTIME("unknown style " << style);
   g.start_then(op);
   g.then_finish(op);

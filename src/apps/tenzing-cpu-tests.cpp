@@ -661,7 +661,8 @@ TEST_CASE("distributed spmv executes on the host: 4 thread ranks, every style, i
       for (int64_t i = 0; i < n; ++i) x[size_t(i)] = double(i + 1);
       const CsrMat<int, double> mine = random_band_rows<int, double>(n, bw, 6, rr.lb, rr.ub, 9);
       const std::vector<double> want = mine.multiply(x);
-      for (R::Style st : {R::Style::Reference, R::Style::Fused, R::Style::FusedSeparate, R::Style::FusedAll}) {
+      for (R::Style st : {R::Style::Reference, R::Style::Fused, R::Style::FusedSeparate, R::Style::FusedAll,
+                          R::Style::FusedPull}) {
         Graph<OpBase> g;
         auto op = std::make_shared<SpMV<double>>("spmv", spmv, st);
         g.start_then(op);

@@ -33,6 +33,7 @@ typename RowPartSpmv<Scalar>::Style spmv_style(const std::string &s) {
   if (s == "fused") return Style::Fused;
   if (s == "fused_separate") return Style::FusedSeparate;
   if (s == "fused_all") return Style::FusedAll;
+  if (s == "fused_pull") return Style::FusedPull;
   throw std::runtime_error("unknown spmv style '" + s + "'");
 }
 
@@ -109,7 +110,11 @@ template <typename Scalar> void bind_one(py::module_ &m, const char *suffix) {
         },
         py::arg("spmv"), py::arg("style") = "fused", py::arg("name") = "spmv");
   const std::string ch = std::string("make_spmv_choice") + suffix;
-  m.def(ch.c_str(), [](const std::shared_ptr<R> &r) { return make_spmv_choice<Scalar>(r); });
+  m.def(ch.c_str(),
+        [](const std::shared_ptr<R> &r, bool withExperimental) {
+          return make_spmv_choice<Scalar>(r, withExperimental);
+        },
+        py::arg("spmv"), py::arg("with_experimental") = false);
 }
 
 } // namespace
@@ -124,4 +129,6 @@ void bind_spmv(py::module_ &m) {
   });
   s.def("get_owner", &get_owner);
   s.def("styles", [] { return std::vector<std::string>{"reference", "fused", "fused_separate", "fused_all"}; });
+  // built and host-executed, but their kernels have not run on hardware yet
+  s.def("experimental_styles", [] { return std::vector<std::string>{"fused_pull"}; });
 }

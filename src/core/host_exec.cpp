@@ -106,6 +106,19 @@ void spmv_csr_wait(int rows, const int *rowPtr, const int *colInd, const T *val,
 }
 
 template <typename T>
+void spmv_csr_pull(int rows, const int *rowPtr, const int *colInd, const T *val,
+                   const T *const *xPtr, T *y, bool accumulate, const uint64_t *ready, int nReady,
+                   const TzbFlagList &acks, uint64_t epoch) {
+  flags_wait(ready, nReady, epoch);
+  for (int r = 0; r < rows; ++r) {
+    T acc = 0;
+    for (int k = rowPtr[r]; k < rowPtr[r + 1]; ++k) acc += val[k] * *xPtr[colInd[k]];
+    y[r] = accumulate ? y[r] + acc : acc;
+  }
+  flags_signal(acks, epoch);
+}
+
+template <typename T>
 void spmv_fused_all(const TzbGatherPutArgs &put, const int *sendIdx, int rows, const int *lRowPtr,
                     const int *lColInd, const T *lVal, const int *rRowPtr, const int *rColInd,
                     const T *rVal, const T *x, const T *rx, T *y, const uint64_t *flags, int nFlags,
@@ -123,6 +136,8 @@ void spmv_fused_all(const TzbGatherPutArgs &put, const int *sendIdx, int rows, c
   template void gather_put<T>(const TzbGatherPutArgs &, const int *, const T *, uint64_t);         \
   template void spmv_csr_wait<T>(int, const int *, const int *, const T *, const T *, T *, bool,   \
                                  const uint64_t *, int, uint64_t);                                 \
+  template void spmv_csr_pull<T>(int, const int *, const int *, const T *, const T *const *, T *,  \
+                                 bool, const uint64_t *, int, const TzbFlagList &, uint64_t);      \
   template void spmv_fused_all<T>(const TzbGatherPutArgs &, const int *, int, const int *,         \
                                   const int *, const T *, const int *, const int *, const T *,     \
                                   const T *, const T *, T *, const uint64_t *, int, uint64_t);

@@ -271,6 +271,87 @@ cudaError_t spmv_fused_all(const TzbGatherPutArgs *a, const int *sendIdx, int ro
                                       rVal, x, rx, y, flags, nFlags, epoch, counter, nnzPerRow, stream);
 }
 
+// Pull form of the remote product ("gather fused with the off-diagonal SpMV"): no staging
+// copy of x at all.  xPtr[c] points at the owner's copy of remote column c (a peer pointer
+// into that rank's x), so the gather happens inside the product, over NVLink.  Every block
+// first waits until all ranks have declared their x ready for this epoch; the last block to
+// finish tells every rank that this rank is done reading (ackFlags), after which the owners
+// may overwrite their x.
+template <typename T, int TPR>
+__global__ void __launch_bounds__(kThreads)
+spmv_csr_pull_kernel(int rows, const int *__restrict__ rowPtr, const int *__restrict__ colInd,
+                     const T *__restrict__ val, const T *const *__restrict__ xPtr,
+                     T *__restrict__ y, int accumulate, const uint64_t *ready, int nReady,
+                     TzbFlagList acks, uint64_t epoch, unsigned *counter) {
+  if (int(threadIdx.x) < nReady) wait_flag_geq(ready + threadIdx.x, epoch);
+  __syncthreads();
+  const int lane = threadIdx.x % TPR;
+  const unsigned groupMask =
+      TPR == 32 ? 0xffffffffu : (((1u << TPR) - 1u) << ((threadIdx.x & 31) / TPR * TPR));
+  const int groupsPerBlock = kThreads / TPR;
+  for (int row = blockIdx.x * groupsPerBlock + threadIdx.x / TPR; row < rows;
+       row += gridDim.x * groupsPerBlock) {
+    const int begin = __ldg(rowPtr + row), end = __ldg(rowPtr + row + 1);
+    T acc = 0;
+    for (int j = begin + lane; j < end; j += TPR) {
+      const T *xp = reinterpret_cast<const T *>(
+          __ldg(reinterpret_cast<const unsigned long long *>(xPtr) + __ldg(colInd + j)));
+      acc += __ldg(val + j) * *xp; // peer load; x does not change while the product runs
+    }
+#pragma unroll
+    for (int off = TPR / 2; off > 0; off /= 2) acc += __shfl_down_sync(groupMask, acc, off, TPR);
+    if (lane == 0) y[row] = accumulate ? y[row] + acc : acc;
+  }
+  if (block_arrive_last(counter, gridDim.x)) {
+    if (int(threadIdx.x) < acks.n && acks.flag[threadIdx.x])
+      st_release_sys(acks.flag[threadIdx.x], epoch);
+  }
+}
+
+template <typename T>
+cudaError_t launch_spmv_pull(int rows, const int *rowPtr, const int *colInd, const T *val,
+                             const T *const *xPtr, T *y, int accumulate, const uint64_t *ready,
+                             int nReady, const TzbFlagList *acks, uint64_t epoch, uint32_t *counter,
+                             int nnzPerRowHint, cudaStream_t stream) {
+  if (!acks || nReady > kThreads || acks->n > 32) return cudaErrorInvalidValue;
+  int tpr = 2;
+  while (tpr < 32 && tpr * 2 <= nnzPerRowHint) tpr *= 2;
+  const int groupsPerBlock = kThreads / tpr;
+  // at least one block even without rows: the handshake must still happen
+  int blocks = (std::max(rows, 1) + groupsPerBlock - 1) / groupsPerBlock;
+  if (blocks > kSMs * 8) blocks = kSMs * 8;
+  ++g_launches;
+#define TZB_CASE(N)                                                                                \
+  case N:                                                                                          \
+    spmv_csr_pull_kernel<T, N><<<blocks, kThreads, 0, stream>>>(                                   \
+        rows, rowPtr, colInd, val, xPtr, y, accumulate, ready, nReady, *acks, epoch, counter);    \
+    break
+  switch (tpr) {
+    TZB_CASE(2);
+    TZB_CASE(4);
+    TZB_CASE(8);
+    TZB_CASE(16);
+    TZB_CASE(32);
+  }
+#undef TZB_CASE
+  return cudaGetLastError();
+}
+
+cudaError_t spmv_csr_pull(int rows, const int *rowPtr, const int *colInd, const double *val,
+                          const double *const *xPtr, double *y, bool accumulate,
+                          const uint64_t *ready, int nReady, const TzbFlagList *acks, uint64_t epoch,
+                          uint32_t *counter, int nnzPerRow, cudaStream_t stream) {
+  return launch_spmv_pull<double>(rows, rowPtr, colInd, val, xPtr, y, accumulate, ready, nReady,
+                                  acks, epoch, counter, nnzPerRow, stream);
+}
+cudaError_t spmv_csr_pull(int rows, const int *rowPtr, const int *colInd, const float *val,
+                          const float *const *xPtr, float *y, bool accumulate,
+                          const uint64_t *ready, int nReady, const TzbFlagList *acks, uint64_t epoch,
+                          uint32_t *counter, int nnzPerRow, cudaStream_t stream) {
+  return launch_spmv_pull<float>(rows, rowPtr, colInd, val, xPtr, y, accumulate, ready, nReady,
+                                 acks, epoch, counter, nnzPerRow, stream);
+}
+
 } // namespace tzb
 
 using namespace tzb;
@@ -298,6 +379,22 @@ int tzb_spmv_csr_wait_f32(int rows, const int *rowPtr, const int *colInd, const 
                           int nFlags, uint64_t epoch, void *stream) {
   return launch_spmv<float, true>(rows, rowPtr, colInd, val, x, y, accumulate, flags, nFlags,
                                   epoch, kDefaultNnzPerRow, static_cast<cudaStream_t>(stream));
+}
+int tzb_spmv_csr_pull_f64(int rows, const int *rowPtr, const int *colInd, const double *val,
+                          const double *const *xPtr, double *y, int accumulate,
+                          const uint64_t *ready, int nReady, const TzbFlagList *acks, uint64_t epoch,
+                          uint32_t *counter, void *stream) {
+  return launch_spmv_pull<double>(rows, rowPtr, colInd, val, xPtr, y, accumulate, ready, nReady,
+                                  acks, epoch, counter, kDefaultNnzPerRow,
+                                  static_cast<cudaStream_t>(stream));
+}
+int tzb_spmv_csr_pull_f32(int rows, const int *rowPtr, const int *colInd, const float *val,
+                          const float *const *xPtr, float *y, int accumulate,
+                          const uint64_t *ready, int nReady, const TzbFlagList *acks, uint64_t epoch,
+                          uint32_t *counter, void *stream) {
+  return launch_spmv_pull<float>(rows, rowPtr, colInd, val, xPtr, y, accumulate, ready, nReady,
+                                 acks, epoch, counter, kDefaultNnzPerRow,
+                                 static_cast<cudaStream_t>(stream));
 }
 
 int tzb_gather_f64(int n, const int *idx, const double *src, double *dst, void *stream) {

@@ -18,6 +18,12 @@ cudaError_t spmv_csr_wait(int, const int *, const int *, const double *, const d
                           bool, int, const uint64_t *, int, uint64_t, cudaStream_t);
 cudaError_t spmv_csr_wait(int, const int *, const int *, const float *, const float *, float *,
                           bool, int, const uint64_t *, int, uint64_t, cudaStream_t);
+cudaError_t spmv_csr_pull(int, const int *, const int *, const double *, const double *const *,
+                          double *, bool, const uint64_t *, int, const TzbFlagList *, uint64_t,
+                          uint32_t *, int, cudaStream_t);
+cudaError_t spmv_csr_pull(int, const int *, const int *, const float *, const float *const *, float *,
+                          bool, const uint64_t *, int, const TzbFlagList *, uint64_t, uint32_t *, int,
+                          cudaStream_t);
 cudaError_t spmv_fused_all(const TzbGatherPutArgs *, const int *, int, const int *, const int *,
                            const double *, const int *, const int *, const double *, const double *,
                            const double *, double *, const uint64_t *, int, uint64_t, uint32_t *, int,
@@ -125,7 +131,7 @@ RowPartSpmv<Scalar>::RowPartSpmv(std::shared_ptr<Communicator> comm,
   comm->allreduce_max(sizes, 3);
   const size_t maxRows = size_t(sizes[0]), maxRemote = size_t(sizes[1]), maxSend = size_t(sizes[2]);
   const size_t es = sizeof(Scalar);
-  const size_t flagBytes = sizeof(uint64_t) * 4 * size_t(np); // one set per style
+  const size_t flagBytes = sizeof(uint64_t) * size_t(kFlagSets) * size_t(np); // one set per style + acks
   const size_t total = 3 * up256(maxRows * es) + 2 * up256(maxRemote * es) + up256(maxSend * es) +
                        up256(flagBytes) + 4096;
   heap_.reset(new SymmetricHeap(comm, total, memory));
@@ -136,6 +142,16 @@ RowPartSpmv<Scalar>::RowPartSpmv(std::shared_ptr<Communicator> comm,
   rxOff_[1] = heap_->alloc(maxRemote * es);
   sendOff_ = heap_->alloc(maxSend * es);
   flagOff_ = heap_->alloc(flagBytes);
+
+  // pull style: where every remote column lives in its owner's x (peer pointers; a rank in
+  // another process whose host heap could not be mapped leaves null entries - dry runs only)
+  std::vector<const Scalar *> ptrs(need.size(), nullptr);
+  for (size_t c = 0; c < need.size(); ++c) {
+    const int owner = get_owner(n, need[c], np);
+    if (!heap_->peer(owner)) continue;
+    ptrs[c] = lx(owner) + (need[c] - get_partition(n, owner, np).lb);
+  }
+  xPtrs_ = to_device(ptrs.data(), ptrs.size() * sizeof(const Scalar *), null);
 }
 
 template <typename Scalar> size_t RowPartSpmv<Scalar>::hbm_bytes() const {
@@ -414,6 +430,79 @@ public:
   }
 };
 
+// ---- pull style (experimental) ----
+cudaError_t k_pull(int rows, const int *rp, const int *ci, const double *v, const double *const *xp,
+                   double *y, bool acc, const uint64_t *ready, int nReady, const TzbFlagList *acks,
+                   uint64_t e, uint32_t *c, int nnz, cudaStream_t st) {
+  return tzb::spmv_csr_pull(rows, rp, ci, v, xp, y, acc, ready, nReady, acks, e, c, nnz, st);
+}
+cudaError_t k_pull(int rows, const int *rp, const int *ci, const float *v, const float *const *xp,
+                   float *y, bool acc, const uint64_t *ready, int nReady, const TzbFlagList *acks,
+                   uint64_t e, uint32_t *c, int nnz, cudaStream_t st) {
+  return tzb::spmv_csr_pull(rows, rp, ci, v, xp, y, acc, ready, nReady, acks, e, c, nnz, st);
+}
+
+// "my x is final for this epoch": one flag on every rank
+template <typename Scalar> class XReady : public GpuOp {
+  SpmvPtr<Scalar> s_;
+
+public:
+  explicit XReady(SpmvPtr<Scalar> s) : s_(std::move(s)) {}
+  std::string name() const override { return "XReady"; }
+  CLONE_DEF(XReady)
+  void run(cudaStream_t) override { THROW_RUNTIME("XReady needs the platform epoch"); }
+  void run(Platform &plat, cudaStream_t st) override {
+    TzbFlagList l;
+    l.n = 0;
+    for (int r = 0; r < s_->size(); ++r) l.flag[l.n++] = s_->flag(r, St<Scalar>::FusedPull, s_->rank());
+    if (s_->null_device() && plat.host_execution()) return host::flags_signal(l, plat.epoch());
+    if (s_->null_device() || plat.is_null()) return;
+    CUDA_RUNTIME(cudaError_t(tzb_flags_signal(&l, plat.epoch(), st)));
+  }
+};
+
+// ly += A_remote * x read from the owners, then "done reading" to every rank
+template <typename Scalar> class PullSpMV : public GpuOp {
+  SpmvPtr<Scalar> s_;
+
+public:
+  explicit PullSpMV(SpmvPtr<Scalar> s) : s_(std::move(s)) {}
+  std::string name() const override { return "yrPull"; }
+  CLONE_DEF(PullSpMV)
+  void run(cudaStream_t) override { THROW_RUNTIME("yrPull needs the platform epoch"); }
+  void run(Platform &plat, cudaStream_t st) override {
+    const bool hostExec = s_->null_device() && plat.host_execution();
+    if (!hostExec && (s_->null_device() || plat.is_null())) return;
+    const auto &A = s_->rA();
+    TzbFlagList acks;
+    acks.n = 0;
+    for (int r = 0; r < s_->size(); ++r) acks.flag[acks.n++] = s_->ack_flag(r, s_->rank());
+    const uint64_t *ready = s_->flag(s_->rank(), St<Scalar>::FusedPull, 0);
+    if (hostExec)
+      return host::spmv_csr_pull(A.rows, A.row_ptr(), A.col_ind(), A.values(), s_->x_ptrs(), s_->ly(),
+                                 true, ready, s_->size(), acks, plat.epoch());
+    CUDA_RUNTIME(k_pull(A.rows, A.row_ptr(), A.col_ind(), A.values(), s_->x_ptrs(), s_->ly(), true,
+                        ready, s_->size(), &acks, plat.epoch(), s_->counter(), A.nnz_per_row(), st));
+  }
+};
+
+// every rank has finished reading my x: it may be overwritten from here on
+template <typename Scalar> class XFree : public GpuOp {
+  SpmvPtr<Scalar> s_;
+
+public:
+  explicit XFree(SpmvPtr<Scalar> s) : s_(std::move(s)) {}
+  std::string name() const override { return "XFree"; }
+  CLONE_DEF(XFree)
+  void run(cudaStream_t) override { THROW_RUNTIME("XFree needs the platform epoch"); }
+  void run(Platform &plat, cudaStream_t st) override {
+    const uint64_t *acks = s_->ack_flag(s_->rank(), 0);
+    if (s_->null_device() && plat.host_execution()) return host::flags_wait(acks, s_->size(), plat.epoch());
+    if (s_->null_device() || plat.is_null()) return;
+    CUDA_RUNTIME(cudaError_t(tzb_flags_wait(acks, s_->size(), plat.epoch(), st)));
+  }
+};
+
 // host-driven transport of the reference structure (copy engine + flags)
 struct SpmvTransport {
   cudaStream_t send = nullptr, recv = nullptr;
@@ -525,6 +614,16 @@ SpMV<Scalar>::SpMV(const std::string &name, const std::shared_ptr<RowPartSpmv<Sc
     OpPtr all = std::make_shared<FusedAllSpMV<Scalar>>(s);
     g.start_then(all);
     g.then_finish(all);
+  } else if (style == Style::FusedPull) {
+    OpPtr ready = std::make_shared<XReady<Scalar>>(s);
+    OpPtr yr = std::make_shared<PullSpMV<Scalar>>(s);
+    OpPtr done = std::make_shared<XFree<Scalar>>(s);
+    g.start_then(yl);
+    g.start_then(ready);
+    g.then(ready, yr);
+    g.then(yl, yr);
+    g.then(yr, done);
+    g.then_finish(done);
   } else if (style == Style::Fused) {
     OpPtr put = std::make_shared<PackPut<Scalar>>(s, style);
     OpPtr yr = std::make_shared<RemoteSpMV<Scalar>>(s, true, true, style);
@@ -547,17 +646,19 @@ SpMV<Scalar>::SpMV(const std::string &name, const std::shared_ptr<RowPartSpmv<Sc
 }
 
 template <typename Scalar>
-std::shared_ptr<ChoiceOp> make_spmv_choice(const std::shared_ptr<RowPartSpmv<Scalar>> &s) {
+std::shared_ptr<ChoiceOp> make_spmv_choice(const std::shared_ptr<RowPartSpmv<Scalar>> &s,
+                                           bool withExperimental) {
   using Style = typename RowPartSpmv<Scalar>::Style;
   std::vector<OpPtr> alts;
   alts.push_back(std::make_shared<SpMV<Scalar>>("spmv_reference", s, Style::Reference));
   alts.push_back(std::make_shared<SpMV<Scalar>>("spmv_fused", s, Style::Fused));
   alts.push_back(std::make_shared<SpMV<Scalar>>("spmv_fused_separate", s, Style::FusedSeparate));
   alts.push_back(std::make_shared<SpMV<Scalar>>("spmv_fused_all", s, Style::FusedAll));
+  if (withExperimental) alts.push_back(std::make_shared<SpMV<Scalar>>("spmv_fused_pull", s, Style::FusedPull));
   return std::make_shared<ListChoiceOp>("spmv", alts);
 }
-template std::shared_ptr<ChoiceOp> make_spmv_choice<double>(const std::shared_ptr<RowPartSpmv<double>> &);
-template std::shared_ptr<ChoiceOp> make_spmv_choice<float>(const std::shared_ptr<RowPartSpmv<float>> &);
+template std::shared_ptr<ChoiceOp> make_spmv_choice<double>(const std::shared_ptr<RowPartSpmv<double>> &, bool);
+template std::shared_ptr<ChoiceOp> make_spmv_choice<float>(const std::shared_ptr<RowPartSpmv<float>> &, bool);
 
 template class RowPartSpmv<double>;
 template class RowPartSpmv<float>;

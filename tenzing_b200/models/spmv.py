@@ -13,6 +13,9 @@ from ..utils.tensor import device_tensor, host_tensor
 from . import common
 
 STYLES = ("reference", "fused", "fused_separate", "fused_all")
+# host-executed and tested on the CPU, kernels not yet run on hardware: offered only on request
+# (style="fused_pull", or style="choice+" for the ChoiceOp over STYLES + EXPERIMENTAL_STYLES)
+EXPERIMENTAL_STYLES = ("fused_pull",)
 
 
 def _csr_from_dict(d, dtype):
@@ -89,11 +92,12 @@ class DistributedSpMV:
             torch.cuda.synchronize()
 
     def graph(self, style="choice"):
-        """Start -> spmv -> Finish; style in STYLES or "choice" """
+        """Start -> spmv -> Finish; style in STYLES + EXPERIMENTAL_STYLES, "choice" (ChoiceOp over
+        STYLES) or "choice+" (experimental styles included)"""
         if style not in self._graphs:
             g = _C.Graph()
-            if style == "choice":
-                op = getattr(_C.spmv, "make_spmv_choice" + self._sfx)(self.spmv)
+            if style in ("choice", "choice+"):
+                op = getattr(_C.spmv, "make_spmv_choice" + self._sfx)(self.spmv, style == "choice+")
             else:
                 op = getattr(_C.spmv, "make_spmv" + self._sfx)(self.spmv, style, "spmv")
             g.start_then(op)

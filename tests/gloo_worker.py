@@ -48,7 +48,7 @@ halo = HaloExchange(comm=comm, nX=6, nY=5, nZ=4, nQ=2, nGhost=2, host=True)
 halo.platform.enable_host_streams()
 spmv = DistributedSpMV(comm=comm, n=301, nnz_per_row=7, seed=3, host=True)
 spmv.platform.set_host_execution(True)
-for wl, styles in ((halo, halo_mod.STYLES), (spmv, spmv_mod.STYLES)):
+for wl, styles in ((halo, halo_mod.STYLES), (spmv, spmv_mod.STYLES + spmv_mod.EXPERIMENTAL_STYLES)):
     for style in styles:
         seq = common.fixed_schedule(wl.graph(style), wl.platform)
         wl.fill()

@@ -182,3 +182,25 @@ def test_experimental_bulk_copy_path_matches_the_oracle():
     p = subprocess.run(["timeout", "120", sys.executable, "-c", code], capture_output=True, text=True,
                        env=env, cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     assert p.returncode == 0 and "BULK_OK" in p.stdout, (p.stdout + p.stderr)[-3000:]
+
+
+@pytest.mark.skipif(os.environ.get("TENZING_TEST_EXPERIMENTAL") != "1",
+                    reason="experimental SpMV pull style: kernel not yet validated on hardware; "
+                           "set TENZING_TEST_EXPERIMENTAL=1 to run it")
+def test_experimental_spmv_pull_style_matches_the_oracle():
+    """spmv_csr_pull_kernel: the remote x entries are read from their owners inside the product.
+    Subprocess under a hard time limit (a protocol bug would spin in a flag wait)."""
+    import subprocess
+    import sys
+    code = (
+        "import os, torch\n"
+        "os.environ['TENZING_ACK_NOTICE'] = '1'\n"
+        "from tenzing_b200.models import DistributedSpMV, common\n"
+        "for n, dtype in ((5000, torch.float64), (200000, torch.float32)):\n"
+        "    s = DistributedSpMV(n=n, nnz_per_row=10, dtype=dtype)\n"
+        "    seq = common.fixed_schedule(s.graph('fused_pull'), s.platform)\n"
+        "    s.fill(); s.run(seq, 3); assert s.check(), n\n"
+        "print('PULL_OK')\n")
+    p = subprocess.run(["timeout", "120", sys.executable, "-c", code], capture_output=True, text=True,
+                       cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    assert p.returncode == 0 and "PULL_OK" in p.stdout, (p.stdout + p.stderr)[-3000:]

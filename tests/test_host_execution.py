@@ -95,7 +95,7 @@ def test_distributed_spmv_executes_on_the_cpu_in_every_style(size):
         for bw in (None, 10 ** 9):     # band (neighbours only) and random columns (all-to-all)
             s = DistributedSpMV(comm=comm, n=403, bw=bw, nnz_per_row=7, seed=3, host=True)
             s.platform.set_host_execution(True)
-            for style in spmv_mod.STYLES:
+            for style in spmv_mod.STYLES + spmv_mod.EXPERIMENTAL_STYLES:
                 for k, seq in enumerate(_schedules(s, style, 3, seed=5)):
                     s.fill()
                     comm.barrier()
@@ -118,7 +118,7 @@ def test_streams_as_threads_run_the_schedules_concurrently_and_correctly(size):
         h.platform.enable_host_streams()
         s = DistributedSpMV(comm=comm, n=301, nnz_per_row=7, seed=3, host=True)
         s.platform.enable_host_streams()
-        for wl, styles in ((h, halo_mod.STYLES), (s, spmv_mod.STYLES)):
+        for wl, styles in ((h, halo_mod.STYLES), (s, spmv_mod.STYLES + spmv_mod.EXPERIMENTAL_STYLES)):
             for style in styles:
                 for k, seq in enumerate(_schedules(wl, style, 3, seed=23)):
                     wl.fill()
