@@ -47,6 +47,9 @@ def main():
     ap.add_argument("--search-iters", type=int, default=30)
     ap.add_argument("--no-search", action="store_true", help="use a fixed fused schedule as is")
     ap.add_argument("--search-budget", type=float, default=40.0, help="wall-clock seconds for the halo search")
+    ap.add_argument("--host-dry-run", action="store_true",
+                    help="no GPU: the same control flow with the workloads executed on the CPU "
+                         "(host memory, gloo); a test of this script, its number is not a result")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)
@@ -58,13 +61,30 @@ def main():
     from tenzing_b200 import _C, ops
     from tenzing_b200.utils.clocks import ClockSampler
 
-    rank, world, local = init_process_group_from_env()
+    host = args.host_dry_run
+    rank, world, local = init_process_group_from_env(backend="gloo" if host else None)
     comm = make_comm()
-    dev = torch.device("cuda", torch.cuda.current_device())
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    dev = torch.device("cpu") if host else torch.device("cuda", torch.cuda.current_device())
+    flush = torch.empty((1 << 20) if host else (256 << 20), dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def device_sync():
+        if not host:
+            torch.cuda.synchronize()
 
     def timed(wl, seq, steps, warmup):
         wl.platform.provision_events(seq)
+        if host:  # wall clock around host-executed steps; same reductions as the device path
+            t = []
+            for _ in range(warmup + steps):
+                comm.barrier()
+                t0 = time.perf_counter()
+                seq.run(wl.platform)
+                wl.platform.synchronize()
+                t.append(time.perf_counter() - t0)
+            t = torch.tensor(t[warmup:], dtype=torch.float64)
+            if world > 1:
+                torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+            return t.tolist(), 0
         _C.device_time_steps(seq, wl.platform, warmup, flush.data_ptr(), flush.numel())
         n0 = ops.launch_count()
         t = _C.device_time_steps(seq, wl.platform, steps, flush.data_ptr(), flush.numel())
@@ -111,7 +131,9 @@ def main():
     # ---------------- flagship: halo exchange ----------------
     t_setup = time.time()
     halo = HaloExchange(comm=comm, nX=args.nx, nQ=args.nq, nGhost=3, storage_order="XYZQ",
-                        neighbors=26)
+                        neighbors=26, host=host)
+    if host:
+        halo.platform.set_host_execution(True)
     halo.fill()
     # the search: MCTS inside every fused implementation style (their decision spaces are small
     # enough to cover well) plus MCTS over the ChoiceOp of ALL styles, reference structure
@@ -129,7 +151,7 @@ def main():
 
     # SM clock / throttle reasons: sampled from before the timed region until after the
     # end-to-end loop (NVML thread + nvidia-smi -lms 20; start() returns once a sample exists)
-    sampler = ClockSampler(torch.cuda.current_device())
+    sampler = ClockSampler(0 if host else torch.cuda.current_device())
     if rank == 0:
         sampler.start()
     comm.barrier()
@@ -140,21 +162,28 @@ def main():
     # exchange, D2H of one ghost row
     a = halo.args
     g = a.nGhost
-    plane = torch.randn(a.nQ, a.nY, a.nX, dtype=torch.float64).pin_memory()
-    row_out = torch.empty(a.nX, dtype=torch.float64).pin_memory()
+    plane = torch.randn(a.nQ, a.nY, a.nX, dtype=torch.float64)
+    row_out = torch.empty(a.nX, dtype=torch.float64)
+    if not host:
+        plane, row_out = plane.pin_memory(), row_out.pin_memory()
+
+    def stream_sync():
+        if not host:
+            torch.cuda.current_stream().synchronize()
+
     cells = halo.cells()
     halo.platform.provision_events(seq_h)
     e2e = []
     for i in range(args.warmup + args.steps):
         flush.fill_(i & 0xff)
-        torch.cuda.synchronize()
+        device_sync()
         comm.barrier()
         t0 = time.perf_counter()
         cells[:, g, g:g + a.nY, g:g + a.nX].copy_(plane, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
+        stream_sync()
         seq_h.run(halo.platform)
         row_out.copy_(cells[0, 0, g, g:g + a.nX], non_blocking=True)
-        torch.cuda.current_stream().synchronize()
+        stream_sync()
         e2e.append(time.perf_counter() - t0)
     e2e = torch.tensor(e2e[args.warmup:], dtype=torch.float64, device=dev)
     if world > 1:
@@ -163,7 +192,9 @@ def main():
     clocks = sampler.stop() if rank == 0 else {}
 
     # ---------------- secondary: distributed SpMV ----------------
-    spmv = DistributedSpMV(comm=comm, n=args.spmv_n, nnz_per_row=10)
+    spmv = DistributedSpMV(comm=comm, n=args.spmv_n, nnz_per_row=10, host=host)
+    if host:
+        spmv.platform.set_host_execution(True)
     spmv.fill()
     seq_s = find_best(spmv, "dfs", ["fused", "fused_all", "fused_separate"], 64, args.search_budget / 2)
     spmv.fill()
@@ -218,7 +249,8 @@ def main():
             "e2e": {"value": round(e2e_us, 3), "unit": "us",
                     "h2d_bytes_per_step": plane.numel() * 8, "d2h_bytes_per_step": row_out.numel() * 8},
             "gpu_launches": int(launches_h), "spmv_gpu_launches": int(launches_s),
-            "clocks": clocks, "search_seconds": round(search_s, 1), "impl": "ours",
+            "clocks": clocks, "search_seconds": round(search_s, 1),
+            "impl": "ours-host-dry-run (not a result)" if host else "ours",
         }
         print(json.dumps(out))
     if world > 1:
