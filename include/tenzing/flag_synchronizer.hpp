@@ -7,6 +7,9 @@
 // that channel: by induction over sequence positions every publish a wait depends on has an
 // earlier position on every rank.  A channel is the byte offset of the flag word inside the
 // symmetric heap (the producer writes word X of the peer, the consumer polls its own word X).
+// Where the word is indexed by the SOURCE rank (SpMV: rank s publishes word s on everybody), an
+// op declares the words of all ranks: what the same op publishes on the other ranks is what
+// arrives here.
 //
 // Ops declare their channels through HasFlags; FlagSynchronizer checks sequences, derives the
 // publish -> wait graph edges, and can filter decisions so a search never offers a wait
@@ -28,6 +31,9 @@ public:
   // heap offsets of the flag words this op publishes on its peers / polls locally
   virtual std::vector<uint64_t> flags_published() const = 0;
   virtual std::vector<uint64_t> flags_awaited() const = 0;
+  // true for single kernels that publish first and wait afterwards (e.g. the one-launch SpMV):
+  // their own publishes count as "earlier" for their own waits
+  virtual bool publishes_before_waiting() const { return false; }
 };
 
 struct FlagSynchronizer {

@@ -18,6 +18,8 @@ std::vector<FlagSynchronizer::Violation> FlagSynchronizer::check(const Sequence<
   for (size_t i = 0; i < seq.size(); ++i) {
     const HasFlags *f = flags_of(*seq[i]);
     if (!f) continue;
+    if (f->publishes_before_waiting())
+      for (uint64_t c : f->flags_published()) published.insert(c);
     for (uint64_t c : f->flags_awaited())
       if (!published.count(c)) out.push_back(Violation{i, seq[i]->name(), c});
     for (uint64_t c : f->flags_published()) published.insert(c);
@@ -32,6 +34,8 @@ bool FlagSynchronizer::is_ready(const BoundOp &op, const Sequence<BoundOp> &path
   for (const auto &p : path)
     if (const HasFlags *pf = flags_of(*p))
       for (uint64_t c : pf->flags_published()) published.insert(c);
+  if (f->publishes_before_waiting())
+    for (uint64_t c : f->flags_published()) published.insert(c);
   for (uint64_t c : f->flags_awaited())
     if (!published.count(c)) return false;
   return true;

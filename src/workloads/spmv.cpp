@@ -1,4 +1,5 @@
 #include "tenzing/spmv/row_part_spmv.hpp"
+#include "tenzing/flag_synchronizer.hpp"
 #include "tenzing/host_exec.hpp"
 
 #include <cstring>
@@ -225,6 +226,19 @@ namespace {
 template <typename Scalar> using SpmvPtr = std::shared_ptr<RowPartSpmv<Scalar>>;
 template <typename Scalar> using St = typename RowPartSpmv<Scalar>::Style;
 
+// Flag channels of one flag set, for the FlagSynchronizer: the heap offsets of the words of ALL
+// source ranks (rank s publishes word s on every rank; the same op on the other ranks is what
+// fills the remaining words here).
+template <typename Scalar> std::vector<uint64_t> set_channels(const RowPartSpmv<Scalar> &s, int set) {
+  std::vector<uint64_t> out;
+  const uint64_t *base = set == RowPartSpmv<Scalar>::kFlagSets - 1
+                             ? s.ack_flag(s.rank(), 0)
+                             : s.flag(s.rank(), St<Scalar>(set), 0);
+  for (int r = 0; r < s.size(); ++r) out.push_back(uint64_t(s.heap().offset_of(base + r)));
+  return out;
+}
+template <typename Scalar> constexpr int ack_set() { return RowPartSpmv<Scalar>::kFlagSets - 1; }
+
 cudaError_t k_gather(int n, const int *idx, const double *s, double *d, cudaStream_t st) {
   return cudaError_t(tzb_gather_f64(n, idx, s, d, st));
 }
@@ -272,12 +286,16 @@ public:
 
 // remote product A_remote * rx.  intoLy: accumulate into ly (yl must precede),
 // else write ry.  wait: fuse the wait for every rank's flag of this epoch.
-template <typename Scalar> class RemoteSpMV : public GpuOp {
+template <typename Scalar> class RemoteSpMV : public GpuOp, public HasFlags {
   SpmvPtr<Scalar> s_;
   bool intoLy_, wait_;
   St<Scalar> style_;
 
 public:
+  std::vector<uint64_t> flags_published() const override { return {}; }
+  std::vector<uint64_t> flags_awaited() const override {
+    return wait_ ? set_channels(*s_, int(style_)) : std::vector<uint64_t>{};
+  }
   RemoteSpMV(SpmvPtr<Scalar> s, bool intoLy, bool wait, St<Scalar> style)
       : s_(std::move(s)), intoLy_(intoLy), wait_(wait), style_(style) {}
   std::string name() const override { return "yr"; }
@@ -353,11 +371,13 @@ template <typename Scalar>
 TzbGatherPutArgs make_put_args(const RowPartSpmv<Scalar> &s, St<Scalar> style, int parity);
 
 // gather fused with the put into every peer's rx, then one flag per rank
-template <typename Scalar> class PackPut : public GpuOp {
+template <typename Scalar> class PackPut : public GpuOp, public HasFlags {
   SpmvPtr<Scalar> s_;
   St<Scalar> style_;
 
 public:
+  std::vector<uint64_t> flags_published() const override { return set_channels(*s_, int(style_)); }
+  std::vector<uint64_t> flags_awaited() const override { return {}; }
   PackPut(SpmvPtr<Scalar> s, St<Scalar> style) : s_(std::move(s)), style_(style) {}
   std::string name() const override { return "PackPut"; }
   CLONE_DEF(PackPut)
@@ -399,10 +419,15 @@ TzbGatherPutArgs make_put_args(const RowPartSpmv<Scalar> &s, St<Scalar> style, i
 }
 
 // the whole product as one kernel launch (put, local product, flag wait, remote product)
-template <typename Scalar> class FusedAllSpMV : public GpuOp {
+template <typename Scalar> class FusedAllSpMV : public GpuOp, public HasFlags {
   SpmvPtr<Scalar> s_;
 
 public:
+  std::vector<uint64_t> flags_published() const override {
+    return set_channels(*s_, int(St<Scalar>::FusedAll));
+  }
+  std::vector<uint64_t> flags_awaited() const override { return flags_published(); }
+  bool publishes_before_waiting() const override { return true; }
   explicit FusedAllSpMV(SpmvPtr<Scalar> s) : s_(std::move(s)) {}
   std::string name() const override { return "SpMVAll"; }
   CLONE_DEF(FusedAllSpMV)
@@ -443,10 +468,14 @@ cudaError_t k_pull(int rows, const int *rp, const int *ci, const float *v, const
 }
 
 // "my x is final for this epoch": one flag on every rank
-template <typename Scalar> class XReady : public GpuOp {
+template <typename Scalar> class XReady : public GpuOp, public HasFlags {
   SpmvPtr<Scalar> s_;
 
 public:
+  std::vector<uint64_t> flags_published() const override {
+    return set_channels(*s_, int(St<Scalar>::FusedPull));
+  }
+  std::vector<uint64_t> flags_awaited() const override { return {}; }
   explicit XReady(SpmvPtr<Scalar> s) : s_(std::move(s)) {}
   std::string name() const override { return "XReady"; }
   CLONE_DEF(XReady)
@@ -462,10 +491,14 @@ public:
 };
 
 // ly += A_remote * x read from the owners, then "done reading" to every rank
-template <typename Scalar> class PullSpMV : public GpuOp {
+template <typename Scalar> class PullSpMV : public GpuOp, public HasFlags {
   SpmvPtr<Scalar> s_;
 
 public:
+  std::vector<uint64_t> flags_published() const override { return set_channels(*s_, ack_set<Scalar>()); }
+  std::vector<uint64_t> flags_awaited() const override {
+    return set_channels(*s_, int(St<Scalar>::FusedPull));
+  }
   explicit PullSpMV(SpmvPtr<Scalar> s) : s_(std::move(s)) {}
   std::string name() const override { return "yrPull"; }
   CLONE_DEF(PullSpMV)
@@ -487,10 +520,12 @@ public:
 };
 
 // every rank has finished reading my x: it may be overwritten from here on
-template <typename Scalar> class XFree : public GpuOp {
+template <typename Scalar> class XFree : public GpuOp, public HasFlags {
   SpmvPtr<Scalar> s_;
 
 public:
+  std::vector<uint64_t> flags_published() const override { return {}; }
+  std::vector<uint64_t> flags_awaited() const override { return set_channels(*s_, ack_set<Scalar>()); }
   explicit XFree(SpmvPtr<Scalar> s) : s_(std::move(s)) {}
   std::string name() const override { return "XFree"; }
   CLONE_DEF(XFree)
@@ -518,11 +553,15 @@ struct SpmvTransport {
   }
 };
 
-template <typename Scalar> class PostSend : public CpuOp {
+template <typename Scalar> class PostSend : public CpuOp, public HasFlags {
   SpmvPtr<Scalar> s_;
   std::shared_ptr<SpmvTransport> tr_;
 
 public:
+  std::vector<uint64_t> flags_published() const override {
+    return set_channels(*s_, int(St<Scalar>::Reference));
+  }
+  std::vector<uint64_t> flags_awaited() const override { return {}; }
   PostSend(SpmvPtr<Scalar> s, std::shared_ptr<SpmvTransport> tr) : s_(std::move(s)), tr_(std::move(tr)) {}
   std::string name() const override { return "PostSend"; }
   CLONE_DEF(PostSend)
@@ -561,11 +600,15 @@ public:
   }
 };
 
-template <typename Scalar> class WaitRecv : public CpuOp {
+template <typename Scalar> class WaitRecv : public CpuOp, public HasFlags {
   SpmvPtr<Scalar> s_;
   std::shared_ptr<SpmvTransport> tr_;
 
 public:
+  std::vector<uint64_t> flags_published() const override { return {}; }
+  std::vector<uint64_t> flags_awaited() const override {
+    return set_channels(*s_, int(St<Scalar>::Reference));
+  }
   WaitRecv(SpmvPtr<Scalar> s, std::shared_ptr<SpmvTransport> tr) : s_(std::move(s)), tr_(std::move(tr)) {}
   std::string name() const override { return "WaitRecv"; }
   CLONE_DEF(WaitRecv)

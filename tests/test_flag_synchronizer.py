@@ -53,3 +53,37 @@ def test_edges_can_be_derived_from_the_flag_channels():
     assert FS.add_edges(g2) == 0
     for s in tz.dfs.get_all_sequences(g2, tz.Platform.make_null(1), 200, True):
         assert FS.is_deadlock_free(s)
+
+
+def test_spmv_ops_declare_their_flag_channels_too():
+    """every SpMV style (validated and experimental): all enumerated schedules pass, the waits
+    really name channels, and a hand-made schedule that waits before the publish is reported"""
+    from tenzing_b200.models import DistributedSpMV
+    from tenzing_b200.models import spmv as spmv_mod
+
+    def body(rank, comm):
+        s = DistributedSpMV(comm=comm, n=120, nnz_per_row=5, host=True)
+        for style in spmv_mod.STYLES + spmv_mod.EXPERIMENTAL_STYLES:
+            seqs = tz.dfs.get_all_sequences(s.graph(style), s.platform, 200, True)
+            assert seqs
+            for q in seqs:
+                assert FS.is_deadlock_free(q), (style, q.desc())
+        inner = s.graph("fused").find_name("spmv").graph()
+        put = _C.BoundGpuOp(inner.find_name("PackPut"), 0)
+        yl = _C.BoundGpuOp(inner.find_name("yl"), 0)
+        yr = _C.BoundGpuOp(inner.find_name("yr"), 0)
+        g = s.graph("fused")
+        assert FS.is_deadlock_free(tz.Sequence([g.start(), put, yl, yr, g.finish()]))
+        v = FS.check(tz.Sequence([g.start(), yl, yr, put, g.finish()]))
+        assert len(v) == comm.size() and all(name == "yr" for _, name, _ in v)   # one channel per source rank
+        # the one-launch product publishes before it waits: fine on its own
+        one = s.graph("fused_all").find_name("spmv").graph().find_name("SpMVAll")
+        assert FS.is_deadlock_free(tz.Sequence([g.start(), _C.BoundGpuOp(one, 1), g.finish()]))
+        # the pull style: ready -> pull -> free is the only legal order of the three
+        pull = s.graph("fused_pull").find_name("spmv").graph()
+        ready, yrp, free = (_C.BoundGpuOp(pull.find_name(n), 0) for n in ("XReady", "yrPull", "XFree"))
+        assert FS.is_deadlock_free(tz.Sequence([g.start(), ready, yrp, free, g.finish()]))
+        assert FS.check(tz.Sequence([g.start(), yrp, ready, free, g.finish()]))
+        assert FS.check(tz.Sequence([g.start(), ready, free, yrp, g.finish()]))
+
+    _C.loopback_run(3, body)
