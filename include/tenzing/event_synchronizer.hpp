@@ -12,6 +12,7 @@
 // wait are placed relative to other ready ops is itself part of the search.
 #pragma once
 
+#include <unordered_map>
 #include <vector>
 
 #include "tenzing/graph.hpp"
@@ -19,10 +20,42 @@
 
 namespace tenzing {
 
+// What the synchronizer asks about a path, answered from tables built in one pass: where an
+// op sits, which events were recorded on which stream and who waited for them afterwards.
+// State::get_decisions builds one per call and shares it between all frontier ops (the plain
+// overloads below build a temporary one); without it every question is a scan of the path and
+// a decision costs O(frontier x predecessors x path^2).
+class PathIndex {
+public:
+  struct Record {
+    int pos = 0;
+    Event event;
+    bool hostSynced = false;     // a CudaEventSync on the event follows
+    std::vector<int> waiters;    // streams with a CudaStreamWaitEvent on the event afterwards
+    std::shared_ptr<CudaEventRecord> op;
+  };
+  explicit PathIndex(const Sequence<BoundOp> &path);
+  int pos_of(const OpBase &op) const;          // by identity; -1 if absent
+  int pos_of_unbound(const OpBase &op) const;  // ignoring the stream binding; -1 if absent
+  const std::vector<Record> &records(const Stream &s) const;
+  // smallest event id no op of the path uses (= Sequence::new_unique_event)
+  Event new_unique_event() const { return Event(nextEvent_); }
+
+private:
+  std::unordered_map<uint32_t, int> byUid_, byUnbound_;
+  std::unordered_map<int, std::vector<Record>> byStream_;
+  int nextEvent_ = 0;
+};
+
 struct EventSynchronizer {
   // true iff every graph predecessor of `bo` found in `path` is synchronised with it
   static bool is_synced(const BoundOpPtr &bo, const Graph<OpBase> &g,
                         const Sequence<BoundOp> &path);
+  static bool is_synced(const BoundOpPtr &bo, const Graph<OpBase> &g,
+                        const Sequence<BoundOp> &path, const PathIndex &idx);
+  static std::vector<BoundOpPtr> make_syncs(const BoundOpPtr &bo, const Graph<OpBase> &g,
+                                            const Sequence<BoundOp> &path, const PathIndex &idx,
+                                            bool quiet = true);
   // next missing synchronisation ops (deduplicated); empty iff is_synced
   static std::vector<BoundOpPtr> make_syncs(const BoundOpPtr &bo, const Graph<OpBase> &g,
                                             const Sequence<BoundOp> &path, bool quiet = true);

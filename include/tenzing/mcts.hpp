@@ -95,11 +95,19 @@ public:
   bool expanded_ = false;
   bool fullyVisited_ = false;
   size_t n_ = 0; // rollouts through this node
-  std::shared_ptr<const Graph<OpBase>> graph_;
+  // For op nodes the graph of the parent; for graph-rewrite nodes (stream assignment,
+  // expansion, choice) the revised graph, built from `rewrite_` the first time it is needed:
+  // a node may have a hundred rewrite children of which a search visits a few, and every
+  // revised graph is a copy of the whole program graph.
+  mutable std::shared_ptr<const Graph<OpBase>> graph_;
+  DecisionPtr rewrite_;
+  const std::shared_ptr<const Graph<OpBase>> &graph() const;
   NodeStats state_;
 
   Node(std::shared_ptr<const Graph<OpBase>> graph, BoundOpPtr op, Node *parent = nullptr)
       : parent_(parent), op_(std::move(op)), graph_(std::move(graph)) {}
+  // graph-rewrite child: the graph is derived from the parent's on demand
+  Node(DecisionPtr rewrite, Node *parent) : parent_(parent), rewrite_(std::move(rewrite)) {}
   // root: sequence = [Start]
   explicit Node(const Graph<OpBase> &graph);
   Node(const Node &) = delete;

@@ -549,9 +549,15 @@ PYBIND11_MODULE(_C, m) {
         [](const SDP::State &a, const SDP::State &b) { return SDP::get_equivalence(a, b); });
 
   py::class_<EventSynchronizer>(m, "EventSynchronizer")
-      .def_static("is_synced", &EventSynchronizer::is_synced)
-      .def_static("make_syncs", &EventSynchronizer::make_syncs, py::arg("op"), py::arg("graph"),
-                  py::arg("path"), py::arg("quiet") = true);
+      .def_static("is_synced",
+                  [](const BoundOpPtr &op, const G &g, const Seq &path) {
+                    return EventSynchronizer::is_synced(op, g, path);
+                  })
+      .def_static("make_syncs",
+                  [](const BoundOpPtr &op, const G &g, const Seq &path, bool quiet) {
+                    return EventSynchronizer::make_syncs(op, g, path, quiet);
+                  },
+                  py::arg("op"), py::arg("graph"), py::arg("path"), py::arg("quiet") = true);
 
   // cross-rank flag dependencies (device-side synchronisation between GPUs)
   py::class_<FlagSynchronizer>(m, "FlagSynchronizer")

@@ -23,9 +23,13 @@ std::vector<BoundOpPtr> State::get_syncs_before_op(const BoundOpPtr &op) const {
 std::vector<DecisionPtr> State::get_decisions(const Platform &plat, bool quiet) const {
   std::vector<DecisionPtr> decisions;
   std::unordered_set<uint32_t> offeredSyncs; // one ExecuteOp per distinct sync op
+  const PathIndex idx(sequence_);            // one pass over the path serves every frontier op
   for (const OpPtr &op : graph_->frontier(sequence_.vector())) {
     if (auto bop = std::dynamic_pointer_cast<BoundOp>(op)) {
-      const std::vector<BoundOpPtr> syncs = get_syncs_before_op(bop);
+      const std::vector<BoundOpPtr> syncs =
+          Synchronizer::is_synced(bop, *graph_, sequence_, idx)
+              ? std::vector<BoundOpPtr>{}
+              : Synchronizer::make_syncs(bop, *graph_, sequence_, idx, true);
       if (syncs.empty()) {
         decisions.push_back(std::make_shared<ExecuteOp>(bop));
       } else {

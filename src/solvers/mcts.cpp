@@ -76,7 +76,16 @@ size_t Node::fully_visited_size() const {
   return n;
 }
 
-bool Node::is_terminal() const { return op_ && op_->uid() == graph_->finish()->uid(); }
+const std::shared_ptr<const Graph<OpBase>> &Node::graph() const {
+  if (!graph_) {
+    if (!rewrite_ || !parent_) THROW_RUNTIME("mcts node without a graph");
+    const SDP::State before(parent_->graph(), parent_->get_sequence());
+    graph_ = before.apply(*rewrite_).graph_ptr();
+  }
+  return graph_;
+}
+
+bool Node::is_terminal() const { return op_ && op_->uid() == graph()->finish()->uid(); }
 
 bool Node::is_leaf() const {
   if (children_.empty()) return true;
@@ -126,15 +135,14 @@ void Node::ensure_children(const Platform &plat) {
   if (expanded_) return;
   expanded_ = true;
   if (is_terminal()) return;
-  const SDP::State state(graph_, get_sequence());
+  const SDP::State state(graph(), get_sequence());
   for (const DecisionPtr &d : state.get_decisions(plat)) {
     if (d->kind() == Decision::Kind::ExecuteOp) {
       const auto &e = static_cast<const ExecuteOp &>(*d);
-      children_.emplace_back(new Node(graph_, e.op, this));
+      children_.emplace_back(new Node(graph(), e.op, this));
     } else {
-      // graph rewrite: the child carries the revised graph and no op
-      SDP::State next = state.apply(*d);
-      children_.emplace_back(new Node(next.graph_ptr(), nullptr, this));
+      // graph rewrite: no op; the revised graph is built when the child is first visited
+      children_.emplace_back(new Node(d, this));
     }
   }
 }
@@ -185,7 +193,7 @@ Node::RolloutResult Node::get_rollout(const Platform &plat, std::mt19937_64 &rng
   } else {
     // play out on states only; nothing below this node is kept
     if (op_) res.sequence.push_back(op_);
-    SDP::State state(graph_, res.sequence);
+    SDP::State state(graph(), res.sequence);
     while (!state.is_terminal()) {
       const auto decisions = state.get_decisions(plat);
       if (decisions.empty()) THROW_RUNTIME("rollout reached a dead end at " << state.sequence().desc());
