@@ -32,7 +32,8 @@ def main():
     ap.add_argument("--out", default="")
     ap.add_argument("--search-iters", type=int, default=0,
                     help="also report the best schedule of an MCTS (FastMin) search per halo style")
-    ap.add_argument("--halo-styles", default=",".join(HALO_STYLES))
+    ap.add_argument("--halo-styles", default=",".join(HALO_STYLES),
+                    help='comma separated; add "dist" for the torch.distributed (NCCL) baseline')
     ap.add_argument("--hand", action="store_true", help="hand-written fused_groups pipelines + put-only times")
     ap.add_argument("--no-spmv", action="store_true")
     ap.add_argument("--mixed-hand", action="store_true", help="hand schedules over the fused_mixed ops")

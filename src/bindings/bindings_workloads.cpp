@@ -215,6 +215,15 @@ void bind_workloads(py::module_ &m) {
       .def("rank_coord", [](const Domain &d) { auto c = d.args().rankToCoord(d.rank()); return std::vector<int>{c.x, c.y, c.z}; })
       .def("rank_grid", [](const Domain &d) { auto c = d.args().rankGrid; return std::vector<int>{c.x, c.y, c.z}; })
       .def("neighbor", [](const Domain &d, int dx, int dy, int dz) { return d.neighbor(Dim3<int>(dx, dy, dz)); })
+      // staging buffers of THIS rank (dense, one slot per direction): what the reference-style
+      // pack ops fill and unpack ops read; used by transports written in Python (torch.distributed)
+      .def("region_elems", [](const Domain &d, int dx, int dy, int dz) { return d.region_elems(Dim3<int>(dx, dy, dz)); })
+      .def("send_staging_ptr", [](const Domain &d, int dx, int dy, int dz) {
+        return reinterpret_cast<uintptr_t>(d.send_staging(d.rank(), Dim3<int>(dx, dy, dz)));
+      })
+      .def("recv_staging_ptr", [](const Domain &d, int parity, int dx, int dy, int dz) {
+        return reinterpret_cast<uintptr_t>(d.recv_staging(d.rank(), parity, Dim3<int>(dx, dy, dz)));
+      })
       .def("dirs", [](const Domain &d) {
         std::vector<std::vector<int>> r;
         for (const auto &x : d.dirs()) r.push_back({x.x, x.y, x.z});

@@ -13,6 +13,9 @@ from ..utils.tensor import device_tensor, host_tensor
 from . import common
 
 STYLES = ("reference", "staged", "direct", "fused_all", "fused_staged", "fused_groups", "fused_mixed", "fused_pipelined", "fused_pull")
+# baselines that are built in Python and are not alternatives of the ChoiceOp:
+#   "dist"  pack -> torch.distributed send/recv (NCCL on GPUs, gloo on the CPU) -> unpack
+BASELINE_STYLES = ("dist",)
 
 
 class HaloExchange:
@@ -120,6 +123,10 @@ class HaloExchange:
                 op = _C.halo.make_choice(self.domain, list(styles))
                 g.start_then(op)
                 g.then_finish(op)
+            elif style == "dist":
+                # second baseline: packed buffers handed to torch.distributed (NCCL / gloo)
+                from ..ops.dist_p2p import add_halo_dist_style
+                g = add_halo_dist_style(self)
             elif style.startswith("flat:"):
                 _C.halo.add_to_graph(g, self.domain, [g.start()], [g.finish()], style[5:])
             else:

@@ -58,6 +58,20 @@ for wl, styles in ((halo, halo_mod.STYLES), (spmv, spmv_mod.STYLES + spmv_mod.EX
         comm.barrier()
         assert wl.check(), (style, rank)
         comm.barrier()
+# the collective library itself as the transport (second baseline: "dist" style) - here gloo,
+# on GPUs NCCL; a searched schedule of it, not just the fixed one
+res = halo.search("mcts", style="dist", iters=4, benchmarker=_C.EmpiricalBenchmarker(),
+                  bench=common.bench_opts(n_iters=2, target_secs=1e-5, max_retries=0,
+                                          check_randomness=False))
+seq, _ = common.best_of(res)
+assert "he_dist_post" in seq.names() and "he_dist_wait" in seq.names()
+halo.fill()
+comm.barrier()
+halo.run(seq, 3)
+halo.platform.synchronize()
+comm.barrier()
+assert halo.check(), ("dist", rank)
+comm.barrier()
 # and a search whose every candidate is executed by both processes
 res = halo.search("mcts", style="fused_mixed", iters=5, benchmarker=_C.EmpiricalBenchmarker(),
                   bench=common.bench_opts(n_iters=2, target_secs=1e-5, max_retries=0,
