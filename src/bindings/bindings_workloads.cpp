@@ -138,6 +138,22 @@ void bind_workloads(py::module_ &m) {
     a.flag = ptr<uint64_t>(flag), a.request = std::move(req);
     return std::static_pointer_cast<BoundOp>(std::make_shared<Irecv>(a, std::move(tr), name));
   }, py::arg("flag"), py::arg("request"), py::arg("transport"), py::arg("name"));
+  // variants that own their request (reference: OwningIsend / OwningIrecv); returns (op, request)
+  m.def("OwningIsend", [](uintptr_t buf, size_t bytes, uintptr_t peerBuf, uintptr_t peerFlag,
+                          std::shared_ptr<P2PTransport> tr, const std::string &name) {
+    Isend::Args a;
+    a.buf = ptr<void>(buf), a.bytes = bytes, a.peerBuf = ptr<void>(peerBuf);
+    a.peerFlag = ptr<uint64_t>(peerFlag);
+    auto op = std::make_shared<OwningIsend>(a, std::move(tr), name);
+    return std::make_pair(std::static_pointer_cast<BoundOp>(op), op->request());
+  }, py::arg("buf"), py::arg("bytes"), py::arg("peer_buf"), py::arg("peer_flag"), py::arg("transport"),
+     py::arg("name"));
+  m.def("OwningIrecv", [](uintptr_t flag, std::shared_ptr<P2PTransport> tr, const std::string &name) {
+    Irecv::Args a;
+    a.flag = ptr<uint64_t>(flag);
+    auto op = std::make_shared<OwningIrecv>(a, std::move(tr), name);
+    return std::make_pair(std::static_pointer_cast<BoundOp>(op), op->request());
+  }, py::arg("flag"), py::arg("transport"), py::arg("name"));
   m.def("Wait", [](RequestPtr req, const std::string &name) {
     return std::static_pointer_cast<BoundOp>(std::make_shared<Wait>(std::move(req), name));
   });

@@ -225,3 +225,72 @@ def test_a_wait_nobody_satisfies_raises_instead_of_hanging():
     _C.set_host_wait_timeout(20.0)
     assert "did not reach epoch" in seen[0]
     assert "another rank failed" in seen.get(1, "another rank failed")
+
+
+@pytest.mark.timeout(120)
+def test_the_host_posted_comm_op_library_moves_data_between_ranks():
+    """Isend / Irecv / OwningIsend / OwningIrecv / Wait / MultiWait / OwningWaitall / Ialltoallv
+    (reference: mpi/ops_mpi.hpp, ops_halo_exchange.hpp:68-92) executed on host memory: three
+    thread ranks, a ring exchange with the plain ops, one with the owning ops, and a personalised
+    all-to-all, scheduled by the solver and repeated over several epochs."""
+    import ctypes
+    import numpy as np
+
+    n_ranks, n = 3, 16
+
+    def body(rank, comm):
+        heap = _C.SymmetricHeap(comm, 1 << 16, True)
+        off_src, off_dst = heap.alloc(n * 8), heap.alloc(n * 8)
+        off_dst2 = heap.alloc(n * 8)
+        off_a2a_src, off_a2a_dst = heap.alloc(n_ranks * 8), heap.alloc(n_ranks * 8)
+        off_flags = heap.alloc(8 * 8)
+
+        def view(r, off, count):
+            buf = (ctypes.c_double * count).from_address(heap.peer_ptr(r) + off)
+            return np.frombuffer(buf, dtype=np.float64)
+
+        right, left = (rank + 1) % n_ranks, (rank - 1) % n_ranks
+        tr = _C.P2PTransport(True)
+        plat = tz.Platform.make_null(1, comm)
+        plat.set_host_execution(True)
+        sreq, rreq = _C.Request(), _C.Request()
+        isend = _C.Isend(heap.local_ptr() + off_src, n * 8, heap.peer_ptr(right) + off_dst,
+                         heap.peer_ptr(right) + off_flags, sreq, tr, "isend")
+        irecv = _C.Irecv(heap.local_ptr() + off_flags, rreq, tr, "irecv")
+        wait = _C.Wait(sreq, "wait_send")
+        multi = _C.MultiWait([rreq], "wait_recv")
+        oisend, osreq = _C.OwningIsend(heap.local_ptr() + off_src, n * 8, heap.peer_ptr(left) + off_dst2,
+                                       heap.peer_ptr(left) + off_flags + 8, tr, "owning_isend")
+        oirecv, orreq = _C.OwningIrecv(heap.local_ptr() + off_flags + 8, tr, "owning_irecv")
+        owait = _C.OwningWaitall([osreq, orreq], "wait_owned")
+        a2areq = _C.Request()
+        a2a = _C.Ialltoallv(heap.local_ptr() + off_a2a_src, [8 * p for p in range(n_ranks)],
+                            [8] * n_ranks, [heap.peer_ptr(p) + off_a2a_dst + 8 * rank for p in range(n_ranks)],
+                            [heap.peer_ptr(p) + off_flags + 16 + 8 * rank for p in range(n_ranks)],
+                            a2areq, tr, "a2a")
+        a2a_recv = [_C.Irecv(heap.local_ptr() + off_flags + 16 + 8 * p, _C.Request(), tr, f"a2a_irecv{p}")
+                    for p in range(n_ranks)]
+        g = tz.Graph()
+        posts = [isend, irecv, oisend, oirecv, a2a] + a2a_recv
+        waits = [wait, multi, owait]
+        for p in posts:
+            g.start_then(p)
+            for w in waits:
+                g.then(p, w)
+        for w in waits:
+            g.then_finish(w)
+        seqs = tz.dfs.get_all_sequences(g, plat, 6, True)
+        assert seqs
+        for k, seq in enumerate(seqs[:3]):
+            for epoch in range(3):
+                view(rank, off_src, n)[:] = 100 * rank + k + epoch + np.arange(n)
+                view(rank, off_a2a_src, n_ranks)[:] = [1000 * rank + p + epoch for p in range(n_ranks)]
+                comm.barrier()
+                seq.run(plat)
+                comm.barrier()          # everybody's sends have landed (waits only cover my own)
+                assert np.array_equal(view(rank, off_dst, n), 100 * left + k + epoch + np.arange(n))
+                assert np.array_equal(view(rank, off_dst2, n), 100 * right + k + epoch + np.arange(n))
+                assert list(view(rank, off_a2a_dst, n_ranks)) == [1000 * p + rank + epoch for p in range(n_ranks)]
+                comm.barrier()
+
+    _run_world(n_ranks, body)
