@@ -54,6 +54,7 @@ template <typename Scalar> void bind_one(py::module_ &m, const char *suffix) {
       .def("ly_ptr", [](const R &r) { return reinterpret_cast<uintptr_t>(r.ly()); })
       .def("ry_ptr", [](const R &r) { return reinterpret_cast<uintptr_t>(r.ry()); })
       .def("rx_ptr", [](const R &r, int parity) { return reinterpret_cast<uintptr_t>(r.rx(r.rank(), parity)); })
+      .def("send_buf_ptr", [](const R &r) { return reinterpret_cast<uintptr_t>(r.x_send_buf()); })
       .def("remote_globals", [](const R &r) { return as_bytes(r.host_split().globals); })
       .def("local_csr", [](const R &r) { return csr_dict(r.host_split().local); })
       .def("remote_csr", [](const R &r) { return csr_dict(r.host_split().remote); })

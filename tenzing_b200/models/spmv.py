@@ -16,6 +16,8 @@ STYLES = ("reference", "fused", "fused_separate", "fused_all")
 # host-executed and tested on the CPU, kernels not yet run on hardware: offered only on request
 # (style="fused_pull", or style="choice+" for the ChoiceOp over STYLES + EXPERIMENTAL_STYLES)
 EXPERIMENTAL_STYLES = ("fused_pull",)
+# built in Python, not an alternative of the ChoiceOp: Pack -> torch.distributed send/recv -> yr, y
+BASELINE_STYLES = ("dist",)
 
 
 def _csr_from_dict(d, dtype):
@@ -96,6 +98,11 @@ class DistributedSpMV:
         STYLES) or "choice+" (experimental styles included)"""
         if style not in self._graphs:
             g = _C.Graph()
+            if style == "dist":
+                # second baseline: x entries through torch.distributed (NCCL / gloo)
+                from ..ops.dist_p2p import add_spmv_dist_style
+                self._graphs[style] = add_spmv_dist_style(self)
+                return self._graphs[style]
             if style in ("choice", "choice+"):
                 op = getattr(_C.spmv, "make_spmv_choice" + self._sfx)(self.spmv, style == "choice+")
             else:

@@ -92,3 +92,55 @@ def add_halo_dist_style(halo):
         g.then(wait, unpack)
         g.then_finish(unpack)
     return g                                 # the two host ops keep `tr` (tensors, requests) alive
+
+
+class SpmvDistTransport:
+    """x entries through torch.distributed: one send per peer that needs some of my x, one receive
+    per peer that owns some of the x I need (the reference's PostSend / PostRecv, ops_spmv.cuh:217-304)"""
+
+    def __init__(self, spmv_model):
+        self.m = spmv_model
+        s = spmv_model.spmv
+        view = host_tensor if spmv_model.host else device_tensor
+        n_send, n_recv = max(s.num_send(), 1), max(s.num_remote_cols(), 1)
+        self.sendbuf = view(s.send_buf_ptr(), (n_send,), spmv_model.dtype, owner=s)
+        self.rx = {p: view(s.rx_ptr(p), (n_recv,), spmv_model.dtype, owner=s) for p in (0, 1)}
+        self.sends = [tuple(p) for p in s.send_params()]     # (peer, displ, count, dstDispl)
+        self.recvs = [tuple(p) for p in s.recv_params()]     # (peer, displ, count)
+        self.pending = []
+
+    def post(self):
+        rx = self.rx[self.m.platform.epoch() & 1]
+        ops = [dist.P2POp(dist.irecv, rx[displ:displ + count], peer) for peer, displ, count in self.recvs]
+        ops += [dist.P2POp(dist.isend, self.sendbuf[displ:displ + count], peer)
+                for peer, displ, count, _ in self.sends]
+        self.pending = dist.batch_isend_irecv(ops) if ops else []
+
+    def wait(self):
+        for req in self.pending:
+            req.wait()
+        self.pending = []
+        if not self.m.host:
+            torch.cuda.current_stream().synchronize()
+
+
+def add_spmv_dist_style(spmv_model):
+    """Start -> {yl, Pack}; Pack -> x_dist_post -> x_dist_wait -> yr -> y; yl -> y -> Finish, with
+    yl / Pack / yr / y taken from the `reference` style (yr reads the receive buffer, y adds)."""
+    if spmv_model.comm.size() > 1 and not dist.is_initialized():
+        raise RuntimeError("the 'dist' SpMV style needs torch.distributed (launch under torchrun)")
+    tr = SpmvDistTransport(spmv_model)
+    inner = spmv_model.graph("reference").find_name("spmv").graph()
+    yl, pack, yr, y = (inner.find_name(n) for n in ("yl", "Pack", "yr", "y"))
+    post = _C.PyCpuOp("x_dist_post", tr.post)
+    wait = _C.PyCpuOp("x_dist_wait", tr.wait)
+    g = _C.Graph()
+    g.start_then(yl)
+    g.start_then(pack)
+    g.then(pack, post)
+    g.then(post, wait)
+    g.then(wait, yr)
+    g.then(yl, y)
+    g.then(yr, y)
+    g.then_finish(y)
+    return g

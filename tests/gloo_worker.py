@@ -72,6 +72,16 @@ halo.platform.synchronize()
 comm.barrier()
 assert halo.check(), ("dist", rank)
 comm.barrier()
+for bw in (None, 10 ** 9):      # neighbours only / all-to-all
+    sp = DistributedSpMV(comm=comm, n=301, bw=bw, nnz_per_row=7, seed=3, host=True)
+    sp.platform.set_host_execution(True)
+    seq = common.fixed_schedule(sp.graph("dist"), sp.platform)
+    sp.fill()
+    comm.barrier()
+    sp.run(seq, 3)
+    comm.barrier()
+    assert sp.check(), ("spmv dist", rank, bw)
+    comm.barrier()
 # and a search whose every candidate is executed by both processes
 res = halo.search("mcts", style="fused_mixed", iters=5, benchmarker=_C.EmpiricalBenchmarker(),
                   bench=common.bench_opts(n_iters=2, target_secs=1e-5, max_retries=0,
