@@ -40,6 +40,16 @@ for kind in $kinds; do
     TENZING_ACK_NOTICE=1 "$out/tests" "-tc=*[tsan-must-report]*" > /dev/null 2> "$out/control.txt" || true
     if grep -q "ThreadSanitizer: data race" "$out/control.txt"; then
       echo "negative control: the racy graph is reported, as it must be"
+      # second control: flags published without release semantics (fault injection) must make
+      # the host-executed halo exchange racy
+      TENZING_FAULT=relaxed_flags TENZING_ACK_NOTICE=1 "$out/tests" "-tc=halo exchange executes on the host*" \
+        > /dev/null 2> "$out/control2.txt" || true
+      if grep -q "ThreadSanitizer: data race" "$out/control2.txt"; then
+        echo "negative control: an exchange whose flags lack release semantics is reported"
+      else
+        echo "negative control FAILED: relaxed flag stores went unnoticed" >&2
+        exit 1
+      fi
     else
       echo "negative control FAILED: ThreadSanitizer did not report the racy graph" >&2
       exit 1

@@ -3,6 +3,7 @@
 #include <chrono>
 #include <cstdlib>
 #include <cstring>
+#include <string>
 #include <thread>
 
 #include "tenzing/macro_at.hpp"
@@ -23,7 +24,23 @@ double &timeout_ref() {
 double wait_timeout_seconds() { return timeout_ref(); }
 void set_wait_timeout_seconds(double s) { timeout_ref() = s; }
 
-void flag_signal(uint64_t *flag, uint64_t epoch) { __atomic_store_n(flag, epoch, __ATOMIC_RELEASE); }
+namespace {
+// Fault injection for the protocol checks (scripts/sanitize.sh): TENZING_FAULT=relaxed_flags
+// publishes flags WITHOUT release semantics, which leaves the payload unordered with respect to
+// the flag - ThreadSanitizer must then report the host-executed exchanges as racy.
+bool relaxed_flags() {
+  static const bool on = [] {
+    const char *e = std::getenv("TENZING_FAULT");
+    return e && std::string(e) == "relaxed_flags";
+  }();
+  return on;
+}
+} // namespace
+
+void flag_signal(uint64_t *flag, uint64_t epoch) {
+  if (relaxed_flags()) return __atomic_store_n(flag, epoch, __ATOMIC_RELAXED);
+  __atomic_store_n(flag, epoch, __ATOMIC_RELEASE);
+}
 
 void flags_signal(const TzbFlagList &list, uint64_t epoch) {
   for (int i = 0; i < list.n; ++i)
