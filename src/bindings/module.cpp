@@ -544,7 +544,9 @@ PYBIND11_MODULE(_C, m) {
       .def("apply", &SDP::State::apply)
       .def("frontier", &SDP::State::frontier, py::arg("plat"), py::arg("quiet") = true)
       .def("is_terminal", &SDP::State::is_terminal)
-      .def("canonical_key", &SDP::State::canonical_key);
+      .def("canonical_key", [](const SDP::State &st) { return py::bytes(st.canonical_key()); },
+           "opaque bytes: equal for states that differ only in the numbering of streams and events "
+           "(comparable within one process only)");
   m.def("state_equivalence",
         [](const SDP::State &a, const SDP::State &b) { return SDP::get_equivalence(a, b); });
 

@@ -93,43 +93,53 @@ bool State::is_terminal() const {
   return !sequence_.empty() && sequence_.back()->uid() == graph_->finish()->uid();
 }
 
-// sequence first, then graph vertices in name order, one renumbering of streams
-// and events across both (so sequence and graph agree on the renaming)
+// Sequence first, then the graph's vertices in a binding-independent order, with ONE
+// renumbering of streams and events (first use) across both, so sequence and graph agree on
+// the renaming.  Ops are named by their interned unbound identity (kind + name, a 32-bit id
+// that every op caches) instead of by their name strings: the key is compared within one
+// process only (DFS de-duplication), and building it is the inner loop of the enumeration.
 std::string State::canonical_key() const {
   if (!keyCache_.empty()) return keyCache_;
-  std::map<int, int> sMap, eMap;
-  auto relabel = [](std::map<int, int> &m, int id) {
-    auto it = m.find(id);
-    if (it != m.end()) return it->second;
+  std::vector<std::pair<int, int>> sMap, eMap; // id -> first-use rank; a handful of entries
+  auto relabel = [](std::vector<std::pair<int, int>> &m, int id) {
+    for (const auto &kv : m)
+      if (kv.first == id) return kv.second;
     const int n = static_cast<int>(m.size());
-    m.emplace(id, n);
+    m.emplace_back(id, n);
     return n;
   };
-  auto emit = [&](const OpBase &op, std::string &key) {
-    const bool sync = dynamic_cast<const SyncOpBase *>(&op) != nullptr;
-    key += sync ? op.kind() : op.name();
-    if (const auto *hs = dynamic_cast<const HasStream *>(&op))
-      for (const Stream &s : hs->get_streams()) key += "/s" + std::to_string(relabel(sMap, s.id()));
-    if (const auto *he = dynamic_cast<const HasEvent *>(&op))
-      for (const Event &e : he->get_events()) key += "/e" + std::to_string(relabel(eMap, e.id()));
-  };
   std::string key;
-  for (const auto &op : sequence_) {
-    emit(*op, key);
-    key += "|";
-  }
-  key += "#";
+  auto put = [&key](char tag, uint32_t v) {
+    key.push_back(tag);
+    key.append(reinterpret_cast<const char *>(&v), sizeof(v));
+  };
+  auto emit = [&](const OpBase &op) {
+    if (const auto *sync = dynamic_cast<const SyncOpBase *>(&op)) {
+      // synchronisation ops are the same op whatever they are called: kind, not name
+      put('k', intern_key(sync->kind()));
+    } else {
+      put('o', op.unbound_uid());
+    }
+    if (const auto *hs = dynamic_cast<const HasStream *>(&op))
+      for (const Stream &st : hs->get_streams()) put('s', uint32_t(relabel(sMap, st.id())));
+    if (const auto *he = dynamic_cast<const HasEvent *>(&op))
+      for (const Event &e : he->get_events()) put('e', uint32_t(relabel(eMap, e.id())));
+  };
+  key.reserve(16 * (sequence_.size() + 4 * graph_->vertex_size()));
+  for (const auto &op : sequence_) emit(*op);
+  key.push_back('#');
   std::vector<OpPtr> verts = graph_->vertices();
   std::sort(verts.begin(), verts.end(),
-            [](const OpPtr &a, const OpPtr &b) { return a->name() < b->name(); });
+            [](const OpPtr &x, const OpPtr &y) { return x->unbound_uid() < y->unbound_uid(); });
+  std::vector<uint32_t> succIds;
   for (const auto &v : verts) {
-    emit(*v, key);
-    key += ">";
-    std::vector<std::string> succNames;
-    for (const auto &s : graph_->succs(v)) succNames.push_back(s->name());
-    std::sort(succNames.begin(), succNames.end());
-    for (const auto &n : succNames) key += n + ",";
-    key += "|";
+    emit(*v);
+    key.push_back('>');
+    succIds.clear();
+    for (const auto &sc : graph_->succs(v)) succIds.push_back(sc->unbound_uid());
+    std::sort(succIds.begin(), succIds.end());
+    for (uint32_t id : succIds) put(',', id);
+    key.push_back('|');
   }
   keyCache_ = key;
   return key;
