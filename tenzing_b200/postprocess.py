@@ -190,6 +190,45 @@ def evaluate_rules(path_or_text, prefixes=(50, 100, 200, 400), prominence_pct=99
     return out
 
 
+def classes_svg(pct10, peaks, width=900, height=360):
+    """The picture the reference draws with matplotlib (sorted times, a vertical line at every
+    class boundary; postprocess.py:254-316), as a dependency-free SVG string: implementations
+    sorted by pct10 on the x axis, time on a log y axis, class boundaries as dashed lines."""
+    arr = np.sort(np.asarray(pct10, dtype=np.float64))
+    n = len(arr)
+    ml, mr, mt, mb = 70, 15, 20, 40
+    w, h = width - ml - mr, height - mt - mb
+    lo, hi = max(arr.min(), 1e-300), max(arr.max(), 1e-300)
+    if hi <= lo:
+        hi = lo * 1.0001
+    llo, lhi = math.log10(lo), math.log10(hi)
+
+    def px(i):
+        return ml + (w * i / max(n - 1, 1))
+
+    def py(t):
+        return mt + h * (1.0 - (math.log10(max(t, 1e-300)) - llo) / (lhi - llo))
+
+    out = [f'<svg xmlns="http://www.w3.org/2000/svg" width="{width}" height="{height}" '
+           f'viewBox="0 0 {width} {height}" font-family="sans-serif" font-size="11">',
+           f'<rect x="{ml}" y="{mt}" width="{w}" height="{h}" fill="white" stroke="#444"/>']
+    for k in range(6):                                       # y ticks, evenly spaced in log space
+        t = 10 ** (llo + (lhi - llo) * k / 5)
+        y = py(t)
+        out.append(f'<line x1="{ml - 4}" y1="{y:.1f}" x2="{ml}" y2="{y:.1f}" stroke="#444"/>')
+        out.append(f'<text x="{ml - 6}" y="{y + 4:.1f}" text-anchor="end">{t * 1e6:.1f} us</text>')
+    for p_ in peaks:                                         # class boundaries
+        x = px(int(p_))
+        out.append(f'<line x1="{x:.1f}" y1="{mt}" x2="{x:.1f}" y2="{mt + h}" stroke="#c33" '
+                   'stroke-dasharray="4 3"/>')
+    pts = " ".join(f"{px(i):.1f},{py(t):.1f}" for i, t in enumerate(arr))
+    out.append(f'<polyline points="{pts}" fill="none" stroke="#1a5fb4" stroke-width="1.5"/>')
+    out.append(f'<text x="{ml + w / 2:.0f}" y="{height - 10}" text-anchor="middle">'
+               f'{n} implementations sorted by pct10; {len(peaks) + 1} performance classes</text>')
+    out.append("</svg>")
+    return "\n".join(out)
+
+
 def export_dot(clf, cols, path):
     from sklearn.tree import export_graphviz
     export_graphviz(clf, out_file=path, feature_names=cols, filled=True, rounded=True)
@@ -209,6 +248,9 @@ def main(argv=None):
         f.write(res["text"] + "\n")
     if res["tree"] is not None:
         export_dot(res["tree"], res["features"], prefix + "tree.dot")
+    times, _ = read_results(argv[0])
+    with open(prefix + "classes.svg", "w") as f:
+        f.write(classes_svg(times[:, 1], res["peaks"]))
     ev = evaluate_rules(argv[0])
     if ev:
         print("rules from the first n iterations -> accuracy on all:", ev)

@@ -45,6 +45,13 @@ def test_rules_recover_the_planted_structure(tmp_path):
     p.write_text(csv)
     assert postprocess.main([str(p), str(tmp_path / "out.")]) == 0
     assert (tmp_path / "out.rules.txt").exists() and (tmp_path / "out.tree.dot").exists()
+    # the picture of the classes (the reference draws it with matplotlib; here a plain SVG)
+    import xml.etree.ElementTree as ET
+    svg = ET.parse(tmp_path / "out.classes.svg").getroot()
+    ns = "{http://www.w3.org/2000/svg}"
+    dashed = [l for l in svg.iter(ns + "line") if l.get("stroke-dasharray")]
+    assert len(dashed) == 3                               # 4 classes -> 3 boundaries
+    assert len(next(svg.iter(ns + "polyline")).get("points").split()) == 400
 
 
 def test_feature_pruning_drops_constant_and_duplicate_columns():
