@@ -7,10 +7,13 @@
 namespace tenzing {
 
 void HostStreams::backoff(unsigned &spins) {
+  // busy for a moment, then progressively lazier: an idle stream thread must not eat a core
   if (++spins < 256) {
     std::this_thread::yield();
-  } else {
+  } else if (spins < 4096) {
     std::this_thread::sleep_for(std::chrono::microseconds(20));
+  } else {
+    std::this_thread::sleep_for(std::chrono::microseconds(500));
   }
 }
 
