@@ -28,8 +28,9 @@ public:
     if (line.find("coordinate") == std::string::npos) THROW_RUNTIME(path_ << ": only coordinate format");
     while (std::getline(is, line) && !line.empty() && line[0] == '%') {
     }
-    long long m = 0, n = 0, nnz = 0;
-    std::istringstream(line) >> m >> n >> nnz;
+    long long m = 0, n = 0, nnz = -1;
+    if (!(std::istringstream(line) >> m >> n >> nnz) || m <= 0 || n <= 0 || nnz < 0)
+      THROW_RUNTIME(path_ << ": bad size line '" << line << "'");
     CooMat<Ordinal, Scalar> coo(m, n);
     for (long long k = 0; k < nnz; ++k) {
       long long i, j;
@@ -37,6 +38,9 @@ public:
       is >> i >> j;
       if (!pattern) is >> v;
       if (!is) THROW_RUNTIME(path_ << ": truncated at entry " << k);
+      if (i < 1 || i > m || j < 1 || j > n)
+        THROW_RUNTIME(path_ << ": entry " << k << " (" << i << ", " << j << ") lies outside the " << m
+                            << " x " << n << " matrix");
       coo.push_back(Ordinal(i - 1), Ordinal(j - 1), Scalar(v));
       if (symmetric && i != j) coo.push_back(Ordinal(j - 1), Ordinal(i - 1), Scalar(v));
     }

@@ -87,9 +87,25 @@ template <typename Scalar> void bind_one(py::module_ &m, const char *suffix) {
         [](std::shared_ptr<Communicator> comm, const std::string &path, bool host) {
           if (!comm) comm = std::make_shared<SelfComm>();
           CsrMat<int, Scalar> whole;
-          if (comm->rank() == 0) whole = MtxReader<int, Scalar>(path).read_csr();
-          int64_t n = whole.num_rows();
+          // rank 0 reads; a bad file must fail on every rank, not hang the others in a collective
+          int64_t n = -1;
+          std::string error;
+          if (comm->rank() == 0) {
+            try {
+              whole = MtxReader<int, Scalar>(path).read_csr();
+              if (whole.num_rows() != whole.num_cols())
+                THROW_RUNTIME(path << ": " << whole.num_rows() << " x " << whole.num_cols()
+                                   << " - the distributed SpMV needs a square matrix");
+              n = whole.num_rows();
+            } catch (const std::exception &e) {
+              error = e.what();
+            }
+          }
           comm->bcast(&n, sizeof(n), 0);
+          if (n < 0) {
+            error = comm->bcast_string(error, 0);
+            throw std::runtime_error(error);
+          }
           CsrMat<int, Scalar> mine = distribute_rows<Scalar>(*comm, comm->rank() == 0 ? &whole : nullptr, 0);
           return std::make_shared<R>(comm, mine, n,
                                      host ? SymmetricHeap::Memory::Host : SymmetricHeap::Memory::Device);

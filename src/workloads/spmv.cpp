@@ -76,6 +76,9 @@ RowPartSpmv<Scalar>::RowPartSpmv(std::shared_ptr<Communicator> comm,
   const int me = comm->rank(), np = comm->size();
   const bool null = memory == SymmetricHeap::Memory::Host;
   range_ = get_partition(n, me, np);
+  if (myRows.num_cols() != n)
+    THROW_RUNTIME("row-partitioned SpMV needs a square matrix: " << n << " rows, "
+                                                                  << myRows.num_cols() << " columns");
   if (myRows.num_rows() != range_.extent())
     THROW_RUNTIME("rank " << me << " holds " << myRows.num_rows() << " rows, expected "
                           << range_.extent());
