@@ -262,7 +262,15 @@ PYBIND11_MODULE(_C, m) {
     py::gil_scoped_release rel;
     LoopbackWorld::run(size, [&](int rank, std::shared_ptr<Communicator> comm) {
       py::gil_scoped_acquire gil;
-      fn(rank, comm);
+      try {
+        fn(rank, comm);
+      } catch (py::error_already_set &e) {
+        // a rank released from a collective because ANOTHER rank failed: keep it recognisable,
+        // so that the failure reported to the caller is the root cause
+        if (std::string(e.what()).find("LoopbackWorld: another rank failed") != std::string::npos)
+          throw LoopbackAborted();
+        throw;
+      }
     });
   });
 

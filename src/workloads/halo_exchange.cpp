@@ -1,6 +1,7 @@
 #include "tenzing/halo/halo_exchange.hpp"
 #include "tenzing/host_exec.hpp"
 
+#include <algorithm>
 #include <cstring>
 
 #include "tenzing/numeric.hpp"
@@ -80,6 +81,15 @@ Domain::Domain(std::shared_ptr<Communicator> comm, const Args &args, SymmetricHe
   if (!comm) comm = std::make_shared<SelfComm>();
   if (!args_.rankToCoord || !args_.coordToRank) args_.set_default_topology(comm->size());
   if (args_.elemSize != 4 && args_.elemSize != 8) THROW_RUNTIME("elemSize must be 4 or 8");
+  if (args_.nX < 1 || args_.nY < 1 || args_.nZ < 1 || args_.nQ < 1)
+    THROW_RUNTIME("halo domain needs at least one cell and one quantity per rank (nX=" << args_.nX
+                  << " nY=" << args_.nY << " nZ=" << args_.nZ << " nQ=" << args_.nQ << ")");
+  // a ghost layer wider than the interior would need cells of the neighbour's neighbour
+  if (args_.nGhost < 0 || args_.nGhost > std::min(args_.nX, std::min(args_.nY, args_.nZ)))
+    THROW_RUNTIME("ghost radius " << args_.nGhost << " must lie in [0, smallest interior extent]");
+  if (args_.rankGrid.flatten() != 0 && args_.rankGrid.flatten() != comm->size()) // 0: custom topology functions
+    THROW_RUNTIME("rank grid " << args_.rankGrid.x << "x" << args_.rankGrid.y << "x" << args_.rankGrid.z
+                               << " does not have " << comm->size() << " ranks");
   dirs_ = directions(args_.neighbors);
   const int g = args_.nGhost;
   ext_ = Dim3<int>(args_.nX + 2 * g, args_.nY + 2 * g, args_.nZ + 2 * g);

@@ -29,6 +29,8 @@ class HaloExchange:
         a.storageOrder = storage_order
         a.elemSize = 8 if dtype == torch.float64 else 4
         if rank_grid is not None:
+            if len(rank_grid) != 3 or rank_grid[0] * rank_grid[1] * rank_grid[2] != self.comm.size():
+                raise ValueError(f"rank_grid {tuple(rank_grid)} does not describe {self.comm.size()} ranks")
             a.rankGrid = list(rank_grid)
         self.args, self.dtype, self.host = a, dtype, host
         self.domain = _C.halo.Domain(self.comm, a, host)

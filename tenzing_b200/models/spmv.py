@@ -72,6 +72,8 @@ class DistributedSpMV:
     def expected(self):
         """y block from a host CSR product in fp64 (the oracle)"""
         lb, ub = self.spmv.row_range()
+        if ub == lb:                        # more ranks than rows: this rank owns nothing
+            return np.zeros(0, dtype=np.float64)
         xl = self.x_value(np.arange(lb, ub, dtype=np.int64))
         globals_ = np.frombuffer(self.spmv.remote_globals(), dtype=np.int32).astype(np.int64)
         xr = self.x_value(globals_)

@@ -19,6 +19,8 @@ def device_tensor(ptr, shape, dtype, owner=None, device=None):
     """torch tensor aliasing `ptr` (device memory owned by `owner`)."""
     if device is None:
         device = torch.device("cuda", torch.cuda.current_device())
+    if int(np.prod(shape)) == 0:           # e.g. a rank that owns no rows
+        return torch.empty(tuple(shape), dtype=dtype, device=device)
     t = torch.as_tensor(_CudaArray(ptr, shape, dtype, owner), device=device)
     t._tz_owner = owner
     return t
@@ -28,6 +30,8 @@ def host_tensor(ptr, shape, dtype, owner=None):
     """torch tensor aliasing host memory at `ptr` (SymmetricHeap host mode, CPU tests)."""
     import ctypes
     n = int(np.prod(shape))
+    if n == 0:                              # e.g. a rank that owns no rows
+        return torch.empty(tuple(shape), dtype=dtype)
     itemsize = torch.empty(0, dtype=dtype).element_size()
     buf = (ctypes.c_char * (n * itemsize)).from_address(int(ptr))
     t = torch.frombuffer(buf, dtype=dtype, count=n).reshape(tuple(shape))

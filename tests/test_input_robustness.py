@@ -86,3 +86,38 @@ def test_a_bad_matrix_file_fails_on_every_rank_instead_of_hanging_the_others(tmp
 
     _C.loopback_run(3, body)
     assert set(seen) == {0, 1, 2} and all("outside the 3 x 3 matrix" in m for m in seen.values())
+
+
+def test_workload_arguments_are_validated():
+    from tenzing_b200.models import HaloExchange
+    for kw in (dict(nX=2, nGhost=3), dict(nX=0), dict(nX=4, nQ=0), dict(nX=4, nGhost=-1),
+               dict(nX=4, nGhost=1, neighbors=7)):
+        with pytest.raises(RuntimeError):
+            HaloExchange(host=True, **{"nQ": 1, "nGhost": 1, **kw})
+    with pytest.raises(ValueError):
+        HaloExchange(nX=4, nQ=1, nGhost=1, host=True, rank_grid=(2, 1, 1))     # one rank here
+    # the ghost layer may be as wide as the interior, and it may be absent
+    assert HaloExchange(nX=3, nQ=1, nGhost=3, host=True).domain.extent() == [9, 9, 9]
+    assert HaloExchange(nX=3, nQ=1, nGhost=0, host=True).bytes_per_exchange() == 0
+
+
+@pytest.mark.timeout(120)
+def test_more_ranks_than_matrix_rows():
+    """ranks that own no rows still take part in the handshake of every style"""
+    from tenzing_b200.models import common
+    from tenzing_b200.models import spmv as spmv_mod
+
+    def body(rank, comm):
+        for n in (2, 5):
+            s = DistributedSpMV(comm=comm, n=n, nnz_per_row=3, host=True)
+            s.platform.set_host_execution(True)
+            for style in spmv_mod.STYLES + spmv_mod.EXPERIMENTAL_STYLES:
+                seq = common.fixed_schedule(s.graph(style), s.platform)
+                s.fill()
+                comm.barrier()
+                s.run(seq, 2)
+                comm.barrier()
+                assert s.check(), (n, style, rank)
+                comm.barrier()
+
+    _C.loopback_run(4, body)
