@@ -116,7 +116,13 @@ BoundOpPtr sync_op_from_json(const Json &j) {
   if (!j.contains("kind") || !j.at("kind").is_string()) return nullptr;
   const std::string &kind = j.at("kind").as_string();
   const std::string name = j.contains("name") ? j.at("name").as_string() : std::string();
-  auto geti = [&](const char *k) { return static_cast<int>(j.at(k).as_int()); };
+  // ids index tables (event pools, path indexes): a damaged file must not ask for a billion entries
+  auto geti = [&](const char *k) {
+    const int64_t v = j.at(k).as_int();
+    if (v < 0 || v >= (int64_t(1) << 20))
+      THROW_RUNTIME("serialized op " << j.dump() << ": " << k << " = " << v << " is out of range");
+    return static_cast<int>(v);
+  };
   if (kind == "CudaEventRecord") {
     return std::make_shared<CudaEventRecord>(Event(geti("event")), Stream(geti("stream")),
                                              name.empty() ? "CER-anon" : name);

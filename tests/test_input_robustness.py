@@ -121,3 +121,12 @@ def test_more_ranks_than_matrix_rows():
                 comm.barrier()
 
     _C.loopback_run(4, body)
+
+
+def test_serialized_ops_with_absurd_ids_are_refused():
+    g = _graph()
+    for op in ('{"event":2000000000,"kind":"CudaEventRecord","name":"x","stream":0}',
+               '{"event":-3,"kind":"CudaEventSync","name":"x"}',
+               '{"event":0,"kind":"CudaStreamWaitEvent","name":"x","stream":-1}'):
+        with pytest.raises(RuntimeError):
+            _C.sequence_from_json('[{"name":"Start"},' + op + ',{"name":"Finish"}]', g)
