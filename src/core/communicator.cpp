@@ -10,6 +10,7 @@
 #include <netinet/in.h>
 #include <netinet/tcp.h>
 #include <sys/socket.h>
+#include <poll.h>
 #include <unistd.h>
 
 #include "tenzing/macro_at.hpp"
@@ -171,7 +172,16 @@ SocketComm::SocketComm(int rank, int size, const std::string &addr, int port, do
       THROW_RUNTIME("SocketComm: cannot bind " << addr << ":" << port);
     ::listen(listenFd_, size_);
     fds_.assign(size_, -1);
+    const auto deadline =
+        std::chrono::steady_clock::now() + std::chrono::duration<double>(timeoutSec);
     for (int i = 1; i < size_; ++i) {
+      // a rank that never starts must not leave rank 0 in accept() for ever
+      const double left =
+          std::chrono::duration<double>(deadline - std::chrono::steady_clock::now()).count();
+      pollfd pfd{listenFd_, POLLIN, 0};
+      if (left <= 0 || ::poll(&pfd, 1, int(left * 1000) + 1) <= 0)
+        THROW_RUNTIME("SocketComm: only " << (i - 1) << " of " << (size_ - 1)
+                                          << " ranks connected within " << timeoutSec << " s");
       int fd = ::accept(listenFd_, nullptr, nullptr);
       if (fd < 0) THROW_RUNTIME("SocketComm: accept failed");
       setsockopt(fd, IPPROTO_TCP, TCP_NODELAY, &one, sizeof(one));

@@ -338,3 +338,15 @@ def test_native_drivers_execute_on_the_cpu_with_one_process_per_rank():
         assert p.returncode == 0, (cmd, p.stderr[-2000:])
         data = [l for l in p.stdout.splitlines() if l[:1].isdigit()]
         assert (len(data) == rows) if rows else (0 < len(data) <= 12), (cmd, p.stdout[-1000:])
+
+
+@pytest.mark.timeout(60)
+def test_socket_rendezvous_times_out_instead_of_waiting_for_ever():
+    """a rank that never starts: rank 0 gives up in accept, the others give up connecting"""
+    import time
+    port = 32200 + os.getpid() % 300
+    for rank in (1, 0):
+        t0 = time.time()
+        with pytest.raises(RuntimeError):
+            _C.SocketComm(rank, 2, "127.0.0.1", port + rank, 0.5)
+        assert time.time() - t0 < 10
