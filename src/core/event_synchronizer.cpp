@@ -1,5 +1,7 @@
 #include "tenzing/event_synchronizer.hpp"
 
+#include <typeinfo>
+
 namespace tenzing {
 
 // ---------------------------------------------------------------- PathIndex
@@ -96,21 +98,26 @@ struct PredInfo {
 
 PredInfo classify(const BoundOpPtr &pred, const BoundOpPtr &bo) {
   PredInfo r;
-  if (std::dynamic_pointer_cast<Start>(pred)) return r;
-  const bool bCpu = bool(std::dynamic_pointer_cast<CpuOp>(bo));
-  const bool bGpu = bool(std::dynamic_pointer_cast<BoundGpuOp>(bo));
-  const bool pCpu = bool(std::dynamic_pointer_cast<CpuOp>(pred));
-  r.pGpu = std::dynamic_pointer_cast<BoundGpuOp>(pred);
-  if (pCpu && (bCpu || bGpu)) return r;
-  if (r.pGpu && bCpu) {
-    r.need = Need::GpuThenCpu;
-    return r;
+  // BoundGpuOp and Start are final classes: an exact type test (one pointer comparison) is
+  // enough and this function runs once per (frontier op, predecessor) pair of every decision
+  const bool pIsGpu = typeid(*pred) == typeid(BoundGpuOp);
+  const bool bIsGpu = typeid(*bo) == typeid(BoundGpuOp);
+  if (!pIsGpu) {
+    if (typeid(*pred) == typeid(Start)) return r;
+    if (dynamic_cast<const CpuOp *>(pred.get()) && (bIsGpu || dynamic_cast<const CpuOp *>(bo.get())))
+      return r; // CPU -> anything: the host issues in order
+    THROW_RUNTIME("unexpected op combination: " << pred->desc() << " -> " << bo->desc());
   }
-  if (r.pGpu && bGpu) {
+  r.pGpu = std::static_pointer_cast<BoundGpuOp>(pred);
+  if (bIsGpu) {
     // a flag-driven consumer only needs its GPU predecessors issued earlier, which the
     // sequence order already guarantees
-    if (std::static_pointer_cast<BoundGpuOp>(bo)->unbound()->issue_order_only()) return r;
+    if (static_cast<const BoundGpuOp &>(*bo).unbound()->issue_order_only()) return r;
     r.need = Need::GpuThenGpu;
+    return r;
+  }
+  if (dynamic_cast<const CpuOp *>(bo.get())) {
+    r.need = Need::GpuThenCpu;
     return r;
   }
   THROW_RUNTIME("unexpected op combination: " << pred->desc() << " -> " << bo->desc());
