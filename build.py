@@ -67,7 +67,8 @@ def generate():
                      glob.glob(f"{ROOT}/src/workloads/*.cpp"))
     lib_cu = sorted(glob.glob(f"{ROOT}/src/cuda/*.cu") + glob.glob(f"{ROOT}/src/workloads/*.cu"))
     bind_cpp = sorted(glob.glob(f"{ROOT}/src/bindings/*.cpp"))
-    apps = sorted(glob.glob(f"{ROOT}/src/apps/*.cpp") + glob.glob(f"{ROOT}/src/apps/*.cu"))
+    apps = sorted(glob.glob(f"{ROOT}/src/apps/*.cpp") + glob.glob(f"{ROOT}/src/apps/*.cu") +
+                  glob.glob(f"{ROOT}/scripts/probes/*.cu"))  # probes: stand-alone measurement programs
 
     out = []
     w = out.append

@@ -184,6 +184,12 @@ typedef struct TzbFlagList_ {
 } TzbFlagList;
 int tzb_flags_signal(const TzbFlagList *list, uint64_t epoch, void *stream);
 int tzb_flags_wait(const uint64_t *flags, int n, uint64_t epoch, void *stream);
+/* Watchdog of every device-side flag wait of this library (the reference's MPI_Wait has none
+ * and hangs with a dead rank): a wait that stays unsatisfied for `ms` milliseconds
+ * ends its kernel with a trap, so the launch fails with cudaErrorLaunchFailed instead of
+ * spinning until the job is killed.  Default 20000 ms; 0 = wait for ever.  Applies to the
+ * current device; call it before launching (it is a synchronous copy to a device symbol). */
+int tzb_set_wait_timeout_ms(unsigned ms);
 
 /* ------------------------------------------------------------ diagnostics -- */
 /* plain device copy used as the local bandwidth yardstick in the benchmarks */

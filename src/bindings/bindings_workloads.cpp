@@ -92,6 +92,7 @@ void bind_workloads(py::module_ &m) {
     check(tzb_flags_signal(&l, epoch, ptr<void>(s)), "flags_signal");
   });
   k.def("launch_count", [] { return tzb_launch_count(); });
+  k.def("set_wait_timeout_ms", [](unsigned ms) { check(tzb_set_wait_timeout_ms(ms), "set_wait_timeout_ms"); });
   // cudaLimitMaxL2FetchGranularity hint: returns the value the device reports afterwards
   k.def("set_l2_fetch_granularity", [](size_t bytes) {
     cudaError_t e = cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, bytes);

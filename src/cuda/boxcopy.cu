@@ -24,12 +24,12 @@
 namespace tzb {
 
 extern std::atomic<uint64_t> g_launches;
+cudaError_t set_wait_timeout_spmv(unsigned long long ns);
 
 namespace {
 
 constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;
-constexpr int kSMs = 148;
 constexpr int kBlocksPerSM = 4;
 // a work item moves about this many bytes: small enough that the largest
 // workload yields several items per resident block, large enough to amortise
@@ -218,10 +218,12 @@ box_copy_hint_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restri
 // Synchronising variant: waits for region flags, and for ordered plans publishes each region's
 // flag as soon as that region is complete - a block counts the items it finished of the current
 // region and hands the count in (one system-scope fence) when it moves on to another region.
-// Ordered plans run at half occupancy (MIN_BLOCKS = 2, grid of 2 blocks per SM) so that the
-// partner kernel they are meant to overlap with always fits beside them.
+// Ordered plans (MIN_BLOCKS = 2) are launched with a grid of 2 blocks per SM.  Registers are
+// bounded as for the full-occupancy variant (4 blocks of 256 threads fit an SM), so half of
+// every SM's register file and block slots stay free for the partner kernel they are meant to
+// overlap with.
 template <typename T, int MIN_BLOCKS>
-__global__ void __launch_bounds__(kThreads, MIN_BLOCKS)
+__global__ void __launch_bounds__(kThreads, kBlocksPerSM)
 box_copy_sync_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restrict__ items,
                      int nItems, int nBoxes, int anySignal, uint64_t epoch, unsigned *counter) {
   constexpr bool kPerBox = MIN_BLOCKS < kBlocksPerSM; // the ordered (half-occupancy) variant
@@ -432,7 +434,7 @@ static int boxcopy_plan_impl(const TzbBox *boxes, int nBoxes, int elemSize, TzbB
   for (int b = 0; b < nBoxes; ++b)
     totalBytes += int64_t(boxes[b].run) * elemSize * boxes[b].n1 * boxes[b].n2 * boxes[b].n3;
   const int64_t itemBytes =
-      std::min<int64_t>(kItemBytes, std::max<int64_t>(4096, totalBytes / (kSMs * kBlocksPerSM * 4)));
+      std::min<int64_t>(kItemBytes, std::max<int64_t>(4096, totalBytes / (int64_t(sm_count()) * kBlocksPerSM * 4)));
   for (int b = 0; b < nBoxes; ++b) {
     const TzbBox &in = boxes[b];
     if (in.n1 < 0 || in.n2 < 0 || in.n3 < 0 || in.run < 0) return cudaErrorInvalidValue;
@@ -606,7 +608,7 @@ int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t
   unsigned *ctr = static_cast<unsigned *>(scratch);
   ++g_launches;
   if (ordered) {
-    const int blocks = grid(kSMs * (kBlocksPerSM / 2));
+    const int blocks = grid(sm_count() * (kBlocksPerSM / 2));
     if (info->elemSize == 8)
       box_copy_sync_kernel<double, kBlocksPerSM / 2><<<blocks, kThreads, 0, s>>>(
           boxes, items, info->nItems, info->nBoxes, anySignal, epoch, ctr);
@@ -615,7 +617,7 @@ int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t
           boxes, items, info->nItems, info->nBoxes, anySignal, epoch, ctr);
   } else if (waits) {
     // strictly ordered after the local producers (graph edge): full occupancy is safe
-    const int blocks = grid(kSMs * kBlocksPerSM);
+    const int blocks = grid(sm_count() * kBlocksPerSM);
     if (info->elemSize == 8)
       box_copy_sync_kernel<double, kBlocksPerSM><<<blocks, kThreads, 0, s>>>(
           boxes, items, info->nItems, info->nBoxes, anySignal, epoch, ctr);
@@ -624,11 +626,11 @@ int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t
           boxes, items, info->nItems, info->nBoxes, anySignal, epoch, ctr);
   } else if ((info->reserved & 16) && bulk_enabled()) {
     // experimental bulk-copy path (see box_bulk_kernel); one warp per block, 7 blocks per SM
-    const int blocks = grid(kSMs * 7);
+    const int blocks = grid(sm_count() * 7);
     box_bulk_kernel<<<blocks, 32, 0, s>>>(boxes, items, info->nItems, info->nBoxes, info->elemSize,
                                           anySignal, epoch, ctr);
   } else if (thin_hint() && info->elemSize == 8) {
-    const int blocks = grid(kSMs * kBlocksPerSM);
+    const int blocks = grid(sm_count() * kBlocksPerSM);
     switch (thin_hint()) {
     case 64:
       box_copy_hint_kernel<double, 64><<<blocks, kThreads, 0, s>>>(boxes, items, info->nItems, info->nBoxes,
@@ -643,7 +645,7 @@ int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t
                                                                    anySignal, epoch, ctr);
     }
   } else {
-    const int blocks = grid(kSMs * kBlocksPerSM);
+    const int blocks = grid(sm_count() * kBlocksPerSM);
     if (info->elemSize == 8 && vec)
       box_copy_kernel<double, true><<<blocks, kThreads, 0, s>>>(boxes, items, info->nItems,
                                                                 info->nBoxes, anySignal, epoch, ctr);
@@ -704,11 +706,18 @@ int tzb_flags_wait(const uint64_t *flags, int n, uint64_t epoch, void *stream) {
   return cudaGetLastError();
 }
 
+int tzb_set_wait_timeout_ms(unsigned ms) {
+  const unsigned long long ns = (unsigned long long)ms * 1000000ull;
+  cudaError_t e = set_wait_timeout_ns_this_tu(ns);
+  if (e == cudaSuccess) e = set_wait_timeout_spmv(ns);
+  return e;
+}
+
 int tzb_copy_bytes(void *dst, const void *src, size_t bytes, void *stream) {
   if (bytes % 16) return cudaErrorInvalidValue;
   if (!bytes) return cudaSuccess;
   ++g_launches;
-  copy_bytes_kernel<<<kSMs * kBlocksPerSM, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+  copy_bytes_kernel<<<sm_count() * kBlocksPerSM, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<uint4 *>(dst), static_cast<const uint4 *>(src), bytes / 16);
   return cudaGetLastError();
 }

@@ -8,7 +8,26 @@
 
 #include <cstdint>
 
+#include <cuda_runtime.h>
+
 namespace tzb {
+
+// A flag wait that is not satisfied within this many nanoseconds ends the kernel with a trap
+// (the launch then reports cudaErrorLaunchFailed and the process fails) instead of spinning
+// for ever behind a schedule that never publishes or a peer that died.  One copy per
+// translation unit; tzb_set_wait_timeout_ms() sets all of them.  0 = wait for ever.
+static __device__ unsigned long long g_wait_timeout_ns = 20ull * 1000ull * 1000ull * 1000ull;
+
+// host side of the above for the including translation unit
+static inline cudaError_t set_wait_timeout_ns_this_tu(unsigned long long ns) {
+  return cudaMemcpyToSymbol(g_wait_timeout_ns, &ns, sizeof(ns));
+}
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 
 __device__ __forceinline__ void st_release_sys(uint64_t *p, uint64_t v) {
   asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
@@ -20,12 +39,24 @@ __device__ __forceinline__ uint64_t ld_acquire_sys(const uint64_t *p) {
   return v;
 }
 
-// spin until *p >= epoch; back off a little so the polling does not flood L2
+// spin until *p >= epoch; back off a little so the polling does not flood L2.  The watchdog
+// reads the clock only once the back-off has reached its ceiling, so a wait that is satisfied
+// within a few microseconds never pays for it.
 __device__ __forceinline__ void wait_flag_geq(const uint64_t *p, uint64_t epoch) {
   unsigned ns = 20;
+  unsigned long long t0 = 0;
   while (ld_acquire_sys(p) < epoch) {
     __nanosleep(ns);
-    if (ns < 320) ns *= 2;
+    if (ns < 320) {
+      ns *= 2;
+    } else {
+      const unsigned long long limit = g_wait_timeout_ns;
+      if (limit) {
+        const unsigned long long now = globaltimer_ns();
+        if (!t0) t0 = now;
+        else if (now - t0 > limit) __trap();
+      }
+    }
   }
 }
 
@@ -47,6 +78,19 @@ __device__ __forceinline__ bool block_arrive_last(unsigned *counter, unsigned ex
   }
   __syncthreads();
   return isLast;
+}
+
+// number of SMs of the current device (cached per device; 148 on B200)
+inline int sm_count() {
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (!cached[dev]) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
 }
 
 } // namespace tzb

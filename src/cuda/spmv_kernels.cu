@@ -19,21 +19,96 @@ namespace tzb {
 
 std::atomic<uint64_t> g_launches{0};
 
+// the flag-wait watchdog of this translation unit's kernels (see device_sync.cuh)
+cudaError_t set_wait_timeout_spmv(unsigned long long ns) { return set_wait_timeout_ns_this_tu(ns); }
+
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kSMs = 148;
 
-// One row per group of TPR lanes.  A warp therefore streams 32/TPR adjacent
-// rows, whose (val, colInd) segments are adjacent in memory, so the loads of a
-// warp fall into a few contiguous 128 B lines.
+// ---------------------------------------------------------------------------------------
+// CSR product, "stream" form.  A block owns a tile of kThreads consecutive rows.  The tile's
+// non-zeros are one contiguous range of (val, colInd), so all threads stream that range with
+// fully coalesced, mutually independent loads (U pairs per thread in flight, then U gathers
+// of x), park the products in shared memory, and every thread then sums the segment of its own
+// row.  Compared with one row per lane group (the round-1 kernel, kept below for dense rows)
+// there is no rowPtr -> colInd -> x dependency chain per row and no idle lanes when rows are
+// shorter than the lane group: measured 25 % of HBM bandwidth before, see profiles/.
+//
+// COHERENT: x is being written by peer GPUs until the flag wait returns (the remote x of the
+// fused styles), so it must not be read through the non-coherent path.
+template <typename T, bool COHERENT> __device__ __forceinline__ T load_x(const T *x, int c) {
+  if (COHERENT) return __ldcg(x + c);
+  return __ldg(x + c);
+}
+
+// products of tile rows [r0, r0 + kThreads) into `acc` of the thread that owns row r0 + tid
+template <typename T, int U, bool COHERENT>
+__device__ __forceinline__ T tile_product(int r0, int rows, const int *__restrict__ rowPtr,
+                                          const int *__restrict__ colInd, const T *__restrict__ val,
+                                          const T *x, T *prod /* kThreads * U */, int *range /* 2 */) {
+  const int t = threadIdx.x;
+  const int row = r0 + t;
+  int b = 0, e = 0;
+  if (row < rows) b = __ldg(rowPtr + row), e = __ldg(rowPtr + row + 1);
+  __syncthreads(); // the previous tile's readers of `range` and `prod` are done
+  if (t == 0) range[0] = b;
+  if (row == min(r0 + kThreads, rows) - 1) range[1] = e;
+  __syncthreads();
+  const int B = range[0], E = range[1];
+  constexpr int CH = kThreads * U;
+  T acc = 0;
+  for (int c0 = B; c0 < E; c0 += CH) {
+    T v[U];
+    int c[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int j = c0 + t + kThreads * u;
+      v[u] = 0, c[u] = -1;
+      if (j < E) v[u] = __ldcs(val + j), c[u] = __ldcs(colInd + j);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (c[u] >= 0) v[u] *= load_x<T, COHERENT>(x, c[u]);
+#pragma unroll
+    for (int u = 0; u < U; ++u) prod[t + kThreads * u] = v[u];
+    __syncthreads();
+    const int lo = max(b, c0) - c0, hi = min(e, c0 + CH) - c0;
+    for (int j = lo; j < hi; ++j) acc += prod[j];
+    if (c0 + CH < E) __syncthreads(); // before the next chunk overwrites the products
+  }
+  return acc;
+}
+
+template <typename T, int U, bool WAIT>
+__global__ void __launch_bounds__(kThreads)
+spmv_csr_stream_kernel(int rows, const int *__restrict__ rowPtr, const int *__restrict__ colInd,
+                       const T *__restrict__ val, const T *x, T *__restrict__ y, int accumulate,
+                       const uint64_t *flags, int nFlags, uint64_t epoch) {
+  __shared__ T prod[kThreads * U];
+  __shared__ int range[2];
+  if (WAIT) {
+    // remote x entries are only valid once every source rank has published this epoch
+    if (int(threadIdx.x) < nFlags) wait_flag_geq(flags + threadIdx.x, epoch);
+    __syncthreads();
+  }
+  const int tiles = (rows + kThreads - 1) / kThreads;
+  for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+    const int r0 = tile * kThreads;
+    const T acc = tile_product<T, U, WAIT>(r0, rows, rowPtr, colInd, val, x, prod, range);
+    const int row = r0 + threadIdx.x;
+    if (row < rows) y[row] = accumulate ? y[row] + acc : acc;
+  }
+}
+
+// One row per group of TPR lanes: the form for long rows (more than ~48 non-zeros per row),
+// where a row fills its lane group for several trips.
 template <typename T, int TPR, bool WAIT>
 __global__ void __launch_bounds__(kThreads)
 spmv_csr_kernel(int rows, const int *__restrict__ rowPtr, const int *__restrict__ colInd,
-                const T *__restrict__ val, const T *__restrict__ x, T *__restrict__ y,
-                int accumulate, const uint64_t *flags, int nFlags, uint64_t epoch) {
+                const T *__restrict__ val, const T *x, T *__restrict__ y, int accumulate,
+                const uint64_t *flags, int nFlags, uint64_t epoch) {
   if (WAIT) {
-    // remote x entries are only valid once every source rank has published this epoch
     if (int(threadIdx.x) < nFlags) wait_flag_geq(flags + threadIdx.x, epoch);
     __syncthreads();
   }
@@ -47,12 +122,27 @@ spmv_csr_kernel(int rows, const int *__restrict__ rowPtr, const int *__restrict_
        row += gridDim.x * groupsPerBlock) {
     const int begin = __ldg(rowPtr + row), end = __ldg(rowPtr + row + 1);
     T acc = 0;
-    for (int j = begin + lane; j < end; j += TPR) acc += __ldg(val + j) * x[__ldg(colInd + j)];
+    for (int j = begin + lane; j < end; j += TPR)
+      acc += __ldg(val + j) * load_x<T, WAIT>(x, __ldg(colInd + j));
 #pragma unroll
     for (int off = TPR / 2; off > 0; off /= 2) acc += __shfl_down_sync(groupMask, acc, off, TPR);
     if (lane == 0) y[row] = accumulate ? y[row] + acc : acc;
   }
 }
+
+// resident blocks per SM of a kernel (occupancy API, cached by the caller)
+template <typename K> int blocks_per_sm(K kernel) {
+  int n = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, kThreads, 0) != cudaSuccess || n < 1) {
+    (void)cudaGetLastError();
+    n = 1;
+  }
+  return n;
+}
+
+// pairs per thread in flight for a given density: the tile's non-zeros should fit one chunk
+inline int stream_unroll(int nnzPerRowHint) { return nnzPerRowHint <= 4 ? 4 : (nnzPerRowHint <= 8 ? 8 : 12); }
+constexpr int kStreamMaxNnzPerRow = 48;
 
 template <typename T, bool WAIT>
 cudaError_t launch_spmv(int rows, const int *rowPtr, const int *colInd, const T *val, const T *x,
@@ -60,24 +150,39 @@ cudaError_t launch_spmv(int rows, const int *rowPtr, const int *colInd, const T 
                         int nnzPerRowHint, cudaStream_t stream) {
   if (rows <= 0) return cudaSuccess;
   if (WAIT && nFlags > kThreads) return cudaErrorInvalidValue;
+  ++g_launches;
+  if (nnzPerRowHint <= kStreamMaxNnzPerRow) {
+    const int tiles = (rows + kThreads - 1) / kThreads;
+#define TZB_CASE(N)                                                                                \
+  case N: {                                                                                        \
+    static const int perSm = blocks_per_sm(spmv_csr_stream_kernel<T, N, WAIT>);                    \
+    const int blocks = std::min(tiles, sm_count() * perSm);                                       \
+    spmv_csr_stream_kernel<T, N, WAIT><<<blocks, kThreads, 0, stream>>>(                           \
+        rows, rowPtr, colInd, val, x, y, accumulate, flags, nFlags, epoch);                       \
+    break;                                                                                         \
+  }
+    switch (stream_unroll(nnzPerRowHint)) {
+      TZB_CASE(4)
+      TZB_CASE(8)
+      TZB_CASE(12)
+    }
+#undef TZB_CASE
+    return cudaGetLastError();
+  }
   // lanes per row: the largest power of two not above nnz per row (2..32), so few lanes idle
   int tpr = 2;
   while (tpr < 32 && tpr * 2 <= nnzPerRowHint) tpr *= 2;
   const int groupsPerBlock = kThreads / tpr;
   int blocks = (rows + groupsPerBlock - 1) / groupsPerBlock;
-  const int maxBlocks = kSMs * 8; // 8 x 256 threads = full occupancy, grid-stride beyond
+  const int maxBlocks = sm_count() * 8; // 8 x 256 threads = full occupancy, grid-stride beyond
   if (blocks > maxBlocks) blocks = maxBlocks;
-  ++g_launches;
 #define TZB_CASE(N)                                                                                \
   case N:                                                                                          \
     spmv_csr_kernel<T, N, WAIT><<<blocks, kThreads, 0, stream>>>(rows, rowPtr, colInd, val, x, y,  \
                                                                  accumulate, flags, nFlags, epoch); \
     break
   switch (tpr) {
-    TZB_CASE(2);
-    TZB_CASE(4);
-    TZB_CASE(8);
-    TZB_CASE(16);
+  default:
     TZB_CASE(32);
   }
 #undef TZB_CASE
@@ -121,15 +226,21 @@ gather_put_kernel(TzbGatherPutArgs a, const int *__restrict__ idx, const T *__re
 // peers' receive buffers and publish the epoch, (2) local product while those stores and the
 // peers' stores are in flight, (3) wait for every peer's flag, (4) accumulate the remote
 // product.  No block waits for another block of the same GPU; the only waiting is on flags
-// written by other GPUs, whose phase (1) does not depend on anything here.
-template <typename T, int TPR>
+// written by other GPUs, whose phase (1) does not depend on anything here.  A rank publishes
+// only after ALL its blocks have passed phase (1) while resident blocks may already spin in
+// phase (3), so the whole grid has to be co-resident: the launcher sizes it from the occupancy
+// API and launches cooperatively, which the driver refuses rather than deadlocks on.
+// Blocks whose rows have no remote non-zeros never look at the flags.
+template <typename T, int U>
 __global__ void __launch_bounds__(kThreads)
 spmv_fused_all_kernel(TzbGatherPutArgs a, const int *__restrict__ sendIdx, int rows,
                       const int *__restrict__ lRowPtr, const int *__restrict__ lColInd,
                       const T *__restrict__ lVal, const int *__restrict__ rRowPtr,
                       const int *__restrict__ rColInd, const T *__restrict__ rVal,
-                      const T *__restrict__ x, const T *__restrict__ rx, T *__restrict__ y,
+                      const T *__restrict__ x, const T *rx, T *__restrict__ y,
                       const uint64_t *flags, int nFlags, uint64_t epoch, unsigned *counter) {
+  __shared__ T prod[kThreads * U];
+  __shared__ int range[2];
   // (1) put
   const int nSend = a.displ[a.nPeers];
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nSend; i += gridDim.x * blockDim.x) {
@@ -142,40 +253,31 @@ spmv_fused_all_kernel(TzbGatherPutArgs a, const int *__restrict__ sendIdx, int r
       if (a.peerFlag[p]) st_release_sys(a.peerFlag[p], epoch);
   }
   // (2) local product
-  const int lane = threadIdx.x % TPR;
-  // the lanes of MY row only: groups of one warp leave the row loop (or skip empty rows)
-  // independently, so a full-warp mask would name lanes that never arrive
-  const unsigned groupMask =
-      TPR == 32 ? 0xffffffffu : (((1u << TPR) - 1u) << ((threadIdx.x & 31) / TPR * TPR));
-  const int groupsPerBlock = kThreads / TPR;
-  const int row0 = blockIdx.x * groupsPerBlock + threadIdx.x / TPR;
-  const int stride = gridDim.x * groupsPerBlock;
-  for (int row = row0; row < rows; row += stride) {
-    const int begin = __ldg(lRowPtr + row), end = __ldg(lRowPtr + row + 1);
-    T acc = 0;
-    for (int j = begin + lane; j < end; j += TPR) acc += __ldg(lVal + j) * x[__ldg(lColInd + j)];
-#pragma unroll
-    for (int off = TPR / 2; off > 0; off /= 2) acc += __shfl_down_sync(groupMask, acc, off, TPR);
-    if (lane == 0) y[row] = acc;
+  const int tiles = (rows + kThreads - 1) / kThreads;
+  for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+    const int r0 = tile * kThreads;
+    const T acc = tile_product<T, U, false>(r0, rows, lRowPtr, lColInd, lVal, x, prod, range);
+    if (r0 + int(threadIdx.x) < rows) y[r0 + threadIdx.x] = acc;
   }
-  // (3) wait for the peers
-  if (int(threadIdx.x) < nFlags) wait_flag_geq(flags + threadIdx.x, epoch);
-  __syncthreads();
-  // (4) remote product; the same lane group wrote y[row] above, so no inter-thread hazard
-  for (int row = row0; row < rows; row += stride) {
-    const int begin = __ldg(rRowPtr + row), end = __ldg(rRowPtr + row + 1);
-    if (begin == end) continue;
-    T acc = 0;
-    for (int j = begin + lane; j < end; j += TPR) acc += __ldg(rVal + j) * rx[__ldg(rColInd + j)];
-#pragma unroll
-    for (int off = TPR / 2; off > 0; off /= 2) acc += __shfl_down_sync(groupMask, acc, off, TPR);
-    if (lane == 0) y[row] += acc;
+  // (3) + (4): wait for the peers (only blocks that need remote entries), remote product;
+  // the same thread wrote y[row] above, so there is no inter-thread hazard
+  bool waited = false;
+  for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+    const int r0 = tile * kThreads, r1 = min(r0 + kThreads, rows);
+    if (__ldg(rRowPtr + r0) == __ldg(rRowPtr + r1)) continue; // block-uniform
+    if (!waited) {
+      if (int(threadIdx.x) < nFlags) wait_flag_geq(flags + threadIdx.x, epoch);
+      __syncthreads();
+      waited = true;
+    }
+    const T acc = tile_product<T, U, true>(r0, rows, rRowPtr, rColInd, rVal, rx, prod, range);
+    if (r0 + int(threadIdx.x) < rows) y[r0 + threadIdx.x] += acc;
   }
 }
 
 int grid_for(int n) {
   int blocks = (n + kThreads - 1) / kThreads;
-  if (blocks > kSMs * 8) blocks = kSMs * 8;
+  if (blocks > sm_count() * 8) blocks = sm_count() * 8;
   return blocks < 1 ? 1 : blocks;
 }
 
@@ -229,27 +331,28 @@ cudaError_t launch_spmv_fused_all(const TzbGatherPutArgs *a, const int *sendIdx,
                                   uint64_t epoch, uint32_t *counter, int nnzPerRow,
                                   cudaStream_t stream) {
   if (!a || a->nPeers < 0 || a->nPeers > 16 || nFlags > kThreads) return cudaErrorInvalidValue;
-  int tpr = 2;
-  while (tpr < 32 && tpr * 2 <= nnzPerRow) tpr *= 2;
-  const int groupsPerBlock = kThreads / tpr;
-  int blocks = (std::max(rows, 1) + groupsPerBlock - 1) / groupsPerBlock;
-  if (blocks > kSMs * 8) blocks = kSMs * 8;
+  const int tiles = std::max(1, (rows + kThreads - 1) / kThreads);
+  const int nSend = a->displ[a->nPeers];
+  TzbGatherPutArgs args = *a;
+  void *params[] = {&args,    &sendIdx, &rows, &lRowPtr, &lColInd, &lVal,  &rRowPtr, &rColInd,
+                    &rVal,    &x,       &rx,   &y,       &flags,   &nFlags, &epoch,   &counter};
   ++g_launches;
 #define TZB_CASE(N)                                                                                \
-  case N:                                                                                          \
-    spmv_fused_all_kernel<T, N><<<blocks, kThreads, 0, stream>>>(                                  \
-        *a, sendIdx, rows, lRowPtr, lColInd, lVal, rRowPtr, rColInd, rVal, x, rx, y, flags,       \
-        nFlags, epoch, counter);                                                                   \
-    break
-  switch (tpr) {
-    TZB_CASE(2);
-    TZB_CASE(4);
-    TZB_CASE(8);
-    TZB_CASE(16);
-    TZB_CASE(32);
+  case N: {                                                                                        \
+    static const int perSm = blocks_per_sm(spmv_fused_all_kernel<T, N>);                           \
+    /* enough blocks for the tiles and for the gather, never more than fit at once */              \
+    const int want = std::max(tiles, (nSend + kThreads - 1) / kThreads);                           \
+    const int blocks = std::max(1, std::min(want, sm_count() * perSm));                            \
+    return cudaLaunchCooperativeKernel(reinterpret_cast<void *>(spmv_fused_all_kernel<T, N>),      \
+                                       dim3(blocks), dim3(kThreads), params, 0, stream);           \
+  }
+  switch (stream_unroll(nnzPerRow)) {
+    TZB_CASE(4)
+    TZB_CASE(8)
+    TZB_CASE(12)
   }
 #undef TZB_CASE
-  return cudaGetLastError();
+  return cudaErrorInvalidValue;
 }
 
 cudaError_t spmv_fused_all(const TzbGatherPutArgs *a, const int *sendIdx, int rows,
@@ -319,7 +422,7 @@ cudaError_t launch_spmv_pull(int rows, const int *rowPtr, const int *colInd, con
   const int groupsPerBlock = kThreads / tpr;
   // at least one block even without rows: the handshake must still happen
   int blocks = (std::max(rows, 1) + groupsPerBlock - 1) / groupsPerBlock;
-  if (blocks > kSMs * 8) blocks = kSMs * 8;
+  if (blocks > sm_count() * 8) blocks = sm_count() * 8;
   ++g_launches;
 #define TZB_CASE(N)                                                                                \
   case N:                                                                                          \
