@@ -112,6 +112,11 @@ typedef struct {
   int32_t n1, n2, n3, run;   /* extents */
   uint64_t *signal;          /* flag to publish after the box is complete (may be peer), or NULL */
   const uint64_t *wait;      /* local flag to wait on before touching the box, or NULL */
+  /* Elements directly before / after every destination run that are padding the copy may
+   * overwrite with anything (0 = none).  With them a thin run (an x-face ghost piece is 24 bytes)
+   * can be stored as one full 32-byte sector, which spares L2 the read-modify-write of a
+   * partial-sector store. */
+  int32_t dstSlackLo, dstSlackHi;
 } TzbBox;
 
 /* A plan is the device image of the boxes plus a table that cuts them into
@@ -192,6 +197,13 @@ int tzb_flags_wait(const uint64_t *flags, int n, uint64_t epoch, void *stream);
 int tzb_set_wait_timeout_ms(unsigned ms);
 
 /* ------------------------------------------------------------ diagnostics -- */
+/* L2 flush between timed steps: writes `bytes` (> L2 size) of `buf` with `value`, then reads
+ * them back, so L2 ends up full of CLEAN lines of the flush buffer and the timed kernel does
+ * not pay for writing the flush's dirty lines back.  The last 16 bytes of buf are scratch. */
+int tzb_l2_flush(void *buf, size_t bytes, unsigned value, void *stream);
+/* occupies the stream for `us` microseconds (one idle thread): a measurement harness enqueues it
+ * first so that everything behind it is already queued when the timed region starts */
+int tzb_delay_us(unsigned us, void *stream);
 /* plain device copy used as the local bandwidth yardstick in the benchmarks */
 int tzb_copy_bytes(void *dst, const void *src, size_t bytes, void *stream);
 /* number of kernels launched through this library since load (for bench.py's launch count) */

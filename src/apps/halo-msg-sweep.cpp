@@ -8,6 +8,7 @@
 #include <vector>
 
 #include "tenzing/argparse.hpp"
+#include "tenzing/cuda/device_barrier.hpp"
 #include "tenzing/cuda/symmetric_heap.hpp"
 #include "tenzing/driver.hpp"
 #include "tenzing_b200.h"
@@ -39,6 +40,9 @@ int main(int argc, char **argv) {
     CUDA_RUNTIME(cudaMalloc(&scratch, 256));
     CUDA_RUNTIME(cudaMemset(scratch, 0, 256));
     uint64_t epoch = 0;
+    // ranks start together on the GPUs (a host barrier alone leaves 15-25 us of skew, which at
+    // 1 KB is the whole measurement), with the step's kernels already queued behind a short delay
+    DeviceBarrier startLine(ctx.comm);
     if (ctx.rank == 0) std::printf("bytes,fused_us,fused_GBs,memcpy_us,memcpy_GBs\n");
     for (size_t bytes = 1024; bytes <= maxBytes; bytes *= 4) {
       // one contiguous region expressed as rows of 4 KB
@@ -62,6 +66,8 @@ int main(int argc, char **argv) {
           ++epoch;
           CUDA_RUNTIME(cudaStreamSynchronize(s));
           ctx.comm->barrier();
+          CUDA_RUNTIME(cudaError_t(tzb_delay_us(40, s)));
+          if (ctx.size > 1) startLine.enqueue(s);
           CUDA_RUNTIME(cudaEventRecord(e0, s));
           if (mode == 0) {
             CUDA_RUNTIME(cudaError_t(tzb_boxcopy_launch(devPlan, &info, epoch, scratch, s)));

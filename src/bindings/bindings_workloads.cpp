@@ -91,6 +91,9 @@ void bind_workloads(py::module_ &m) {
     for (int i = 0; i < l.n; ++i) l.flag[i] = ptr<uint64_t>(flags[size_t(i)]);
     check(tzb_flags_signal(&l, epoch, ptr<void>(s)), "flags_signal");
   });
+  k.def("l2_flush", [](uintptr_t buf, size_t bytes, unsigned value, uintptr_t s) {
+    check(tzb_l2_flush(ptr<void>(buf), bytes, value, ptr<void>(s)), "l2_flush");
+  });
   k.def("launch_count", [] { return tzb_launch_count(); });
   k.def("set_wait_timeout_ms", [](unsigned ms) { check(tzb_set_wait_timeout_ms(ms), "set_wait_timeout_ms"); });
   // cudaLimitMaxL2FetchGranularity hint: returns the value the device reports afterwards

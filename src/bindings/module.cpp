@@ -701,11 +701,22 @@ PYBIND11_MODULE(_C, m) {
         CUDA_RUNTIME(cudaEventCreate(&stop));
         for (auto &e : joins) CUDA_RUNTIME(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         cudaStream_t s0 = plat.cuda_stream(plat.streams_[0]);
+        // Ranks are lined up on the GPUs, not on the hosts: a host barrier leaves tens of
+        // microseconds of skew, which a device-timed exchange would count as waiting time.
+        if (plat.comm().size() > 1 && !plat.device_barrier())
+          plat.set_device_barrier(std::make_shared<DeviceBarrier>(plat.comm_ptr()));
         for (int i = 0; i < steps; ++i) {
-          if (flushPtr && flushBytes)
-            CUDA_RUNTIME(cudaMemsetAsync(reinterpret_cast<void *>(flushPtr), i & 0xff, flushBytes, s0));
           plat.synchronize();
           plat.comm().barrier();
+          // The L2 flush is queued in front of the step and NOT waited for: while it runs the
+          // host enqueues the device barrier, the start event and the step's kernels, so the
+          // timed region begins with its work already queued (as in the reference's
+          // back-to-back protocol, src/benchmarker.cpp:93-97) instead of with an idle GPU
+          // waiting for the first launch to arrive.
+          if (flushPtr && flushBytes)
+            CUDA_RUNTIME(cudaError_t(tzb_l2_flush(reinterpret_cast<void *>(flushPtr), flushBytes, unsigned(i), s0)));
+          else
+            CUDA_RUNTIME(cudaError_t(tzb_delay_us(30, s0)));
           if (plat.device_barrier()) plat.device_barrier()->enqueue(s0);
           CUDA_RUNTIME(cudaEventRecord(start, s0));
           for (int k = 1; k < plat.num_streams(); ++k)

@@ -45,8 +45,14 @@ struct alignas(16) BoxDesc {
   uint64_t *signal;
   const uint64_t *wait;
   int32_t nItems; // work items this box was cut into
-  int32_t pad;
+  // thin rows (run * 8 bytes <= 32): how each side is accessed, see thin_item().
+  // bits 0-1 source mode, 2-3 destination mode (kElem / kDense / kWindow), 4-5 element offset of
+  // the source piece inside its aligned 32-byte window, 6-7 the same for the destination
+  int32_t thin;
 };
+
+enum ThinMode : int { kElem = 0, kDense = 1, kWindow = 2 };
+constexpr int kThinEnabled = 256; // BoxDesc::thin: this box takes the sector path
 
 // rows [i1, i1+c1) x [i2, i2+c2) of plane i3 of box `box`
 struct alignas(8) WorkItem {
@@ -84,6 +90,134 @@ template <int HINT, typename T> __device__ __forceinline__ T load_thin(const T *
     memcpy(&v, &u, sizeof(v));
   }
   return v;
+}
+
+// ---------------------------------------------------------------------------------------
+// Thin rows, one row per thread ("sector path", 8-byte elements, run <= 4).
+//
+// An x-face row piece of the XYZQ grid is 3 doubles inside a 4 KB row.  Measured on B200
+// (scripts/probes/thin_probe.cu, profiles/): DRAM delivers a whole 128-byte line per piece
+// whatever the load width or engine (8-byte LDG, 256-bit LDG, TMA tile with L2 promotion off
+// all read 100.7 MB for 18.9 MB of payload and take the same 22 us), so the lever is not the
+// bytes but the instruction count and, for stores, avoiding read-modify-write: a 24-byte
+// store into a 32-byte sector makes L2 fetch the sector first (2x the time of the loads),
+// a full-sector store does not.  Therefore:
+//   * a strided piece that lies inside one aligned 32-byte window is LOADED with one 256-bit
+//     access (kWindow) instead of `run` scalar ones;
+//   * where the caller says the rest of the destination window is padding it may clobber
+//     (TzbBox::dstSlackLo/Hi), the piece is STORED as one full 256-bit sector;
+//   * the dense side of a pack / unpack goes through shared memory so that global (or peer)
+//     memory sees contiguous 16-byte accesses.
+struct U256 {
+  unsigned long long a, b, c, d;
+};
+__device__ __forceinline__ U256 ld256(const void *p) {
+  U256 v;
+  asm volatile("ld.global.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(v.a), "=l"(v.b), "=l"(v.c), "=l"(v.d) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ void st256(void *p, const U256 &v) {
+  asm volatile("st.global.v4.u64 [%0], {%1,%2,%3,%4};" ::"l"(p), "l"(v.a), "l"(v.b), "l"(v.c), "l"(v.d) : "memory");
+}
+
+constexpr int kThinRows = kThreads;               // rows per chunk: one row per thread in flight
+constexpr int kThinSmemElems = kThinRows * 4;     // dense image of a chunk (run <= 4)
+// One row per thread is enough: 1024 resident threads per SM keep 128 KB of DRAM lines in
+// flight, several times what the measured 24 G rows/s ceiling needs.
+
+// elements [off, off + 4) of a window, off uniform: no dynamic register indexing
+__device__ __forceinline__ void window_extract(const U256 &w, int off, unsigned long long (&e)[4]) {
+  e[0] = off == 0 ? w.a : (off == 1 ? w.b : (off == 2 ? w.c : w.d));
+  e[1] = off == 0 ? w.b : (off == 1 ? w.c : w.d);
+  e[2] = off == 0 ? w.c : w.d;
+  e[3] = w.d;
+}
+__device__ __forceinline__ U256 window_build(const unsigned long long (&e)[4], int off) {
+  U256 w;
+  w.a = e[0];
+  w.b = off == 0 ? e[1] : e[0];
+  w.c = off == 0 ? e[2] : (off == 1 ? e[1] : e[0]);
+  w.d = off == 0 ? e[3] : (off == 1 ? e[2] : (off == 2 ? e[1] : e[0]));
+  return w;
+}
+
+// One work item of a thin box of 8-byte elements; `sm` holds kThinSmemElems elements.
+// srcMode / dstMode: kWindow = strided piece inside one aligned 32-byte window (a single 256-bit
+// access; for a destination the rest of the window is padding), kDense = the item's rows are
+// contiguous there (moved through shared memory with 16-byte accesses).
+template <int srcMode, int dstMode>
+__device__ __forceinline__ void thin_item_t(const BoxDesc &b, const WorkItem &w, unsigned long long *sm) {
+  const int run = b.run;
+  const int srcOff = (b.thin >> 4) & 3, dstOff = (b.thin >> 6) & 3;
+  const int rows = w.c1 * w.c2, c1 = w.c1;
+  const unsigned long long *src = reinterpret_cast<const unsigned long long *>(b.src) + int64_t(w.i3) * b.s3 +
+                                  int64_t(w.i2) * b.s2 + int64_t(w.i1) * b.s1;
+  unsigned long long *dst = reinterpret_cast<unsigned long long *>(b.dst) + int64_t(w.i3) * b.d3 +
+                            int64_t(w.i2) * b.d2 + int64_t(w.i1) * b.d1;
+  const int t = threadIdx.x;
+#pragma unroll 1
+  for (int r0 = 0; r0 < rows; r0 += kThinRows) {
+    const int nr = min(kThinRows, rows - r0);
+    const int n = nr * run; // elements of this chunk on a dense side
+    if (srcMode == kDense) {
+      const unsigned long long *sp = src + int64_t(r0) * run;
+      if (((reinterpret_cast<uintptr_t>(sp) & 15) == 0) && (n & 1) == 0) {
+#pragma unroll 2
+        for (int i = t; i < n / 2; i += kThreads)
+          reinterpret_cast<ulonglong2 *>(sm)[i] = __ldcs(reinterpret_cast<const ulonglong2 *>(sp) + i);
+      } else {
+#pragma unroll 2
+        for (int i = t; i < n; i += kThreads) sm[i] = __ldcs(sp + i);
+      }
+      __syncthreads();
+    }
+    const int r = r0 + t;
+    const bool live = t < nr;
+    int j2 = 0, j1 = r;
+    if (w.c2 > 1) j2 = r / c1, j1 = r - j2 * c1;
+    unsigned long long e[4] = {0, 0, 0, 0};
+    if (live) {
+      if (srcMode == kWindow) {
+        const U256 win = ld256(src + int64_t(j2) * b.s2 + int64_t(j1) * b.s1 - srcOff);
+        window_extract(win, srcOff, e);
+      } else {
+        const unsigned long long *p = sm + t * run;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          if (i < run) e[i] = p[i];
+      }
+    }
+    if (srcMode == kDense && dstMode == kDense) __syncthreads();
+    if (dstMode == kDense) {
+      if (live) {
+        unsigned long long *p = sm + t * run;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          if (i < run) p[i] = e[i];
+      }
+      __syncthreads();
+      unsigned long long *dp = dst + int64_t(r0) * run;
+      if (((reinterpret_cast<uintptr_t>(dp) & 15) == 0) && (n & 1) == 0) {
+#pragma unroll 1
+        for (int i = t; i < n / 2; i += kThreads)
+          reinterpret_cast<ulonglong2 *>(dp)[i] = reinterpret_cast<const ulonglong2 *>(sm)[i];
+      } else {
+#pragma unroll 1
+        for (int i = t; i < n; i += kThreads) dp[i] = sm[i];
+      }
+    } else if (live) {
+      st256(dst + int64_t(j2) * b.d2 + int64_t(j1) * b.d1 - dstOff, window_build(e, dstOff));
+    }
+    __syncthreads(); // shared memory is free for the next chunk
+  }
+}
+
+__device__ __forceinline__ void thin_item(const BoxDesc &b, const WorkItem &w, unsigned long long *sm) {
+  switch (b.thin & 15) { // block-uniform
+  case kWindow | (kDense << 2): thin_item_t<kWindow, kDense>(b, w, sm); break;   // pack
+  case kDense | (kWindow << 2): thin_item_t<kDense, kWindow>(b, w, sm); break;   // unpack
+  default: thin_item_t<kWindow, kWindow>(b, w, sm); break;                       // direct
+  }
 }
 
 template <typename T, bool VEC, int kThick, int kThin, int HINT = 0>
@@ -183,9 +317,12 @@ __global__ void __launch_bounds__(kThreads, kBlocksPerSM)
 box_copy_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restrict__ items, int nItems,
                 int nBoxes, int anySignal, uint64_t epoch, unsigned *counter) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __shared__ alignas(16) unsigned long long thinSm[kThinSmemElems];
   for (int it = blockIdx.x; it < nItems; it += gridDim.x) {
     const WorkItem w = items[it];
-    copy_item<T, VEC, 8, kThin>(boxes[w.box], w, lane, warp);
+    const BoxDesc &b = boxes[w.box];
+    if (sizeof(T) == 8 && (b.thin & kThinEnabled)) thin_item(b, w, thinSm);
+    else copy_item<T, VEC, 8, kThin>(b, w, lane, warp);
   }
   if (anySignal) {
     // one system-scope fence per block; the last block to finish publishes every flag
@@ -229,6 +366,7 @@ box_copy_sync_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restri
   constexpr bool kPerBox = MIN_BLOCKS < kBlocksPerSM; // the ordered (half-occupancy) variant
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   __shared__ unsigned readyMask; // boxes whose wait flag this block has already seen
+  __shared__ alignas(16) unsigned long long thinSm[kThinSmemElems];
   if (threadIdx.x == 0) readyMask = 0;
   __syncthreads();
   int curBox = -1;
@@ -265,7 +403,8 @@ box_copy_sync_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restri
       }
       __syncthreads();
     }
-    copy_item<T, true, 8, kThin>(b, w, lane, warp);
+    if (sizeof(T) == 8 && (b.thin & kThinEnabled)) thin_item(b, w, thinSm);
+    else copy_item<T, true, 8, kThin>(b, w, lane, warp);
   }
   if (kPerBox) {
     if (curBox >= 0) hand_in(curBox, curCount);
@@ -402,6 +541,29 @@ __global__ void flags_wait_kernel(const uint64_t *flags, int n, uint64_t epoch) 
   for (int i = threadIdx.x; i < n; i += blockDim.x) wait_flag_geq(flags + i, epoch);
 }
 
+// L2 flush for the benchmarks: write the buffer (evicts everything else), then read it back so
+// that what stays in L2 is CLEAN - otherwise the next kernel pays for writing back up to 126 MB
+// of the flush buffer's dirty lines inside its own timed region.
+__global__ void __launch_bounds__(kThreads) flush_write_kernel(uint4 *p, size_t n16, unsigned v) {
+  const size_t stride = size_t(gridDim.x) * blockDim.x;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n16; i += stride) p[i] = make_uint4(v, v, v, v);
+}
+__global__ void __launch_bounds__(kThreads) flush_read_kernel(const uint4 *p, size_t n16, unsigned *sink) {
+  const size_t stride = size_t(gridDim.x) * blockDim.x;
+  unsigned acc = 0;
+  for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n16; i += stride) {
+    const uint4 v = __ldcg(p + i);
+    acc ^= v.x ^ v.y ^ v.z ^ v.w;
+  }
+  if (acc == 0x9e3779b9u) *sink = acc; // never true for a buffer of equal words; keeps the loads alive
+}
+
+// keeps a stream busy for `ns` nanoseconds: lets the host queue what follows before it starts
+__global__ void delay_kernel(unsigned long long ns) {
+  const unsigned long long t0 = globaltimer_ns();
+  while (globaltimer_ns() - t0 < ns) __nanosleep(200);
+}
+
 __global__ void __launch_bounds__(kThreads)
 copy_bytes_kernel(uint4 *__restrict__ dst, const uint4 *__restrict__ src, size_t n16) {
   size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -422,6 +584,16 @@ copy_bytes_kernel(uint4 *__restrict__ dst, const uint4 *__restrict__ src, size_t
 using namespace tzb;
 
 extern "C" {
+
+// TZB_THIN_SECTOR=0 plans thin boxes for the element-wise path of round 1 (A/B comparisons)
+static int thin_sector_level() {
+  static const int level = [] {
+    const char *e = std::getenv("TZB_THIN_SECTOR");
+    return e ? std::atoi(e) : 1;
+  }();
+  return level;
+}
+static bool thin_sector_enabled() { return thin_sector_level() > 0; }
 
 static int boxcopy_plan_impl(const TzbBox *boxes, int nBoxes, int elemSize, TzbBoxPlanInfo *info,
                              void *hostImage, bool ordered) {
@@ -446,7 +618,33 @@ static int boxcopy_plan_impl(const TzbBox *boxes, int nBoxes, int elemSize, TzbB
     d.n1 = in.n1, d.n2 = in.n2, d.n3 = in.n3, d.run = in.run;
     d.signal = in.signal;
     d.wait = in.wait;
-    d.pad = 0;
+    d.thin = 0;
+    if (elemSize == 8 && in.run >= 1 && in.run <= 4 && thin_sector_enabled()) {
+      // how can each side of this thin box be accessed? (see thin_item)
+      auto dense = [&](int64_t t1, int64_t t2) { return t1 == in.run && (in.n2 <= 1 || t2 == t1 * in.n1); };
+      auto window = [&](const void *p, int64_t t1, int64_t t2, int64_t t3, int &off) {
+        const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+        off = int((a & 31) / 8);
+        return (a & 7) == 0 && (t1 * 8) % 32 == 0 && (t2 * 8) % 32 == 0 && (t3 * 8) % 32 == 0 &&
+               off + in.run <= 4;
+      };
+      int so = 0, dof = 0;
+      const bool sDense = dense(in.s1, in.s2), dDense = dense(in.d1, in.d2);
+      const bool sWin = !sDense && window(in.src, in.s1, in.s2, in.s3, so);
+      // a full-sector store is only allowed where the rest of the window is the caller's padding
+      const bool dWin = !dDense && window(in.dst, in.d1, in.d2, in.d3, dof) && in.dstSlackLo >= dof &&
+                        in.dstSlackHi >= 4 - dof - in.run;
+      // pack (window -> dense), unpack (dense -> window) and direct (window -> window); every
+      // other combination stays on the element-wise path of copy_item
+      // Measured (profiles/README.md): only the unpack gains - its full-sector stores spare L2
+      // the fetch of a partially written sector; pack and direct copies are bound by DRAM line
+      // fetches either way and the element-wise path keeps more loads in flight per thread.
+      // TZB_THIN_SECTOR=2 routes all three through the sector path (A/B comparisons).
+      if ((sDense && dWin) || (thin_sector_level() >= 2 && ((sWin && dDense) || (sWin && dWin)))) {
+        const int sm = sDense ? kDense : kWindow, dm = dDense ? kDense : kWindow;
+        d.thin = kThinEnabled | sm | (dm << 2) | ((sWin ? so : 0) << 4) | ((dWin ? dof : 0) << 6);
+      }
+    }
     const int64_t rowBytes = int64_t(in.run) * elemSize;
     const int64_t volume = rowBytes * in.n1 * in.n2 * in.n3;
     payload += size_t(volume);
@@ -711,6 +909,22 @@ int tzb_set_wait_timeout_ms(unsigned ms) {
   cudaError_t e = set_wait_timeout_ns_this_tu(ns);
   if (e == cudaSuccess) e = set_wait_timeout_spmv(ns);
   return e;
+}
+
+int tzb_l2_flush(void *buf, size_t bytes, unsigned value, void *stream) {
+  if (!buf || bytes < 32) return cudaErrorInvalidValue;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const size_t n16 = (bytes - 16) / 16; // the last 16 bytes are the read kernel's sink
+  const int blocks = sm_count() * 8;
+  flush_write_kernel<<<blocks, kThreads, 0, s>>>(static_cast<uint4 *>(buf), n16, value);
+  flush_read_kernel<<<blocks, kThreads, 0, s>>>(static_cast<const uint4 *>(buf), n16,
+                                                reinterpret_cast<unsigned *>(static_cast<char *>(buf) + n16 * 16));
+  return cudaGetLastError();
+}
+
+int tzb_delay_us(unsigned us, void *stream) {
+  delay_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>((unsigned long long)us * 1000ull);
+  return cudaGetLastError();
 }
 
 int tzb_copy_bytes(void *dst, const void *src, size_t bytes, void *stream) {

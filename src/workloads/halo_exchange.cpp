@@ -276,6 +276,14 @@ TzbBox make_box(const Domain &dom, const void *src, Side srcSide, const Dim3<int
   };
   b.src = srcSide == Side::Grid ? grid_base(src, srcOff) : static_cast<const char *>(src);
   b.dst = const_cast<char *>(dstSide == Side::Grid ? grid_base(dst, dstOff) : static_cast<const char *>(dst));
+  if (dstSide == Side::Grid) {
+    // what lies next to a destination run inside its row: padding if the run starts at the
+    // first / ends at the last cell of the row (ghost cells of the x faces), live cells otherwise
+    const int64_t cell = a.storageOrder == StorageOrder::XYZQ ? 1 : a.nQ;
+    if (dstOff.x == 0) b.dstSlackLo = int32_t(dom.x_origin());
+    if (dstOff.x + e.x == dom.extent().x)
+      b.dstSlackHi = int32_t(int64_t(dom.row_elems()) - int64_t(dom.x_origin()) - int64_t(dom.extent().x) * cell);
+  }
   if (a.storageOrder == StorageOrder::XYZQ) {
     // run = x, level1 = y, level2 = z, level3 = q
     b.run = e.x, b.n1 = e.y, b.n2 = e.z, b.n3 = a.nQ;

@@ -19,7 +19,8 @@ class TzbBox(ctypes.Structure):
                 ("d1", ctypes.c_int64), ("d2", ctypes.c_int64), ("d3", ctypes.c_int64),
                 ("n1", ctypes.c_int32), ("n2", ctypes.c_int32), ("n3", ctypes.c_int32),
                 ("run", ctypes.c_int32),
-                ("signal", ctypes.c_void_p), ("wait", ctypes.c_void_p)]
+                ("signal", ctypes.c_void_p), ("wait", ctypes.c_void_p),
+                ("dstSlackLo", ctypes.c_int32), ("dstSlackHi", ctypes.c_int32)]
 
 
 class TzbBoxPlanInfo(ctypes.Structure):
