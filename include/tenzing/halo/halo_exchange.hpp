@@ -146,6 +146,10 @@ public:
   // second flag set of the pull style ("I have read your data" acknowledgements)
   uint64_t *ack_flag(int rank, const Dim3<int> &side) const;
   uint64_t *ack_flags_base(int rank) const;
+  // third set, shared by the styles that put straight into ghost cells: word `side` of rank r
+  // is published by r's neighbour on that side when it allows r to overwrite the ghost cells it
+  // holds for r ("I have consumed what you gave me last time")
+  uint64_t *ready_flag(int rank, const Dim3<int> &side) const;
   int dir_index(const Dim3<int> &d) const;
 
   const std::vector<Dim3<int>> &dirs() const { return dirs_; }
@@ -177,6 +181,7 @@ class BoxCopyOp : public GpuOp, public HasFlags {
   bool ordered_ = false;
   bool null_ = false;
   bool issueOrderOnly_ = false;
+  bool publishesFirst_ = false; // some box grants a permission (TzbBox::ready) before any wait
   std::vector<uint64_t> published_, awaited_; // flag channels (heap offsets), see set_heap()
 
 public:
@@ -187,10 +192,13 @@ public:
             bool ordered = false);
   void set_issue_order_only(bool v) { issueOrderOnly_ = v; }
   // translate the boxes' flag pointers into heap offsets so FlagSynchronizer can reason about them
-  void set_flag_channels(std::vector<uint64_t> published, std::vector<uint64_t> awaited) {
+  void set_flag_channels(std::vector<uint64_t> published, std::vector<uint64_t> awaited,
+                         bool publishesFirst = false) {
     published_ = std::move(published);
     awaited_ = std::move(awaited);
+    publishesFirst_ = publishesFirst;
   }
+  bool publishes_before_waiting() const override { return publishesFirst_; }
   std::vector<uint64_t> flags_published() const override { return published_; }
   std::vector<uint64_t> flags_awaited() const override { return awaited_; }
   bool issue_order_only() const override { return issueOrderOnly_; }

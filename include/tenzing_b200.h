@@ -117,6 +117,11 @@ typedef struct {
    * can be stored as one full 32-byte sector, which spares L2 the read-modify-write of a
    * partial-sector store. */
   int32_t dstSlackLo, dstSlackHi;
+  /* "You may overwrite what I gave you last time": a (peer) flag published at the START of the
+   * kernel, before anything is copied, or NULL.  A put that stores straight into memory its
+   * partner also reads (ghost cells) pairs it with `wait`: every rank grants its partners
+   * permission for this epoch first, then waits for theirs before its first store. */
+  uint64_t *ready;
 } TzbBox;
 
 /* A plan is the device image of the boxes plus a table that cuts them into
@@ -164,6 +169,11 @@ int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t
  *    bytes per ~32 KB of payload, so the array covers roughly 300 MB per call.
  *  - The first call on each device looks up the array's device address; make
  *    that call (with that device current) before any stream capture starts.
+ *  - `stream` must be a stream of the CURRENT device: the array that is used is
+ *    the current device's copy.
+ *  - Every call stages its plan (a few KB to 250 KB) from ordinary host memory to
+ *    the array with cudaMemcpyAsync; for pageable memory the runtime copies the
+ *    bytes before the call returns, so the call costs that much host time.
  *  - All calls share the one array, which keeps the previous call's contents;
  *    the counter is cleared on the stream before each launch.  Two calls whose
  *    kernels may overlap on the GPU (different streams, no ordering between

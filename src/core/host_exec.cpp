@@ -69,6 +69,8 @@ void copy_bytes(void *dst, const void *src, size_t bytes) { std::memcpy(dst, src
 
 void boxcopy(const TzbBox *boxes, int nBoxes, int elemSize, uint64_t epoch, bool ordered) {
   const size_t es = size_t(elemSize);
+  for (int b = 0; b < nBoxes; ++b) // permissions first, as the kernel does
+    if (boxes[b].ready) flag_signal(boxes[b].ready, epoch);
   for (int b = 0; b < nBoxes; ++b) {
     const TzbBox &bx = boxes[b];
     if (bx.wait) flags_wait(bx.wait, 1, epoch);

@@ -49,6 +49,7 @@ struct alignas(16) BoxDesc {
   // bits 0-1 source mode, 2-3 destination mode (kElem / kDense / kWindow), 4-5 element offset of
   // the source piece inside its aligned 32-byte window, 6-7 the same for the destination
   int32_t thin;
+  uint64_t *ready; // published at kernel start (permission for the partner to overwrite), or null
 };
 
 enum ThinMode : int { kElem = 0, kDense = 1, kWindow = 2 };
@@ -368,6 +369,11 @@ box_copy_sync_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restri
   __shared__ unsigned readyMask; // boxes whose wait flag this block has already seen
   __shared__ alignas(16) unsigned long long thinSm[kThinSmemElems];
   if (threadIdx.x == 0) readyMask = 0;
+  // permissions first (a few of the earliest blocks repeat the same stores: whichever of them
+  // the hardware starts first gets them out, nothing here may wait before that)
+  if (blockIdx.x < 4)
+    for (int bx = threadIdx.x; bx < nBoxes; bx += kThreads)
+      if (boxes[bx].ready) st_release_sys(boxes[bx].ready, epoch);
   __syncthreads();
   int curBox = -1;
   unsigned curCount = 0;
@@ -618,6 +624,7 @@ static int boxcopy_plan_impl(const TzbBox *boxes, int nBoxes, int elemSize, TzbB
     d.n1 = in.n1, d.n2 = in.n2, d.n3 = in.n3, d.run = in.run;
     d.signal = in.signal;
     d.wait = in.wait;
+    d.ready = in.ready;
     d.thin = 0;
     if (elemSize == 8 && in.run >= 1 && in.run <= 4 && thin_sector_enabled()) {
       // how can each side of this thin box be accessed? (see thin_item)
@@ -651,7 +658,7 @@ static int boxcopy_plan_impl(const TzbBox *boxes, int nBoxes, int elemSize, TzbB
     int count = 0;
     if (volume == 0) {
       // an empty box still has to wait/publish its flags
-      if (in.signal || in.wait) {
+      if (in.signal || in.wait || in.ready) {
         items.push_back(WorkItem{b, 0, 0, 0, 0, 0});
         count = 1;
       }
@@ -705,7 +712,7 @@ static int boxcopy_plan_impl(const TzbBox *boxes, int nBoxes, int elemSize, TzbB
   info->reserved = 0; // bit 0: some box publishes a flag; bit 1: some box waits for one
   for (int b = 0; b < nBoxes; ++b) {
     if (boxes[b].signal) info->reserved |= 1;
-    if (boxes[b].wait) info->reserved |= 2;
+    if (boxes[b].wait || boxes[b].ready) info->reserved |= 2; // the synchronising kernel
   }
   if (ordered) info->reserved |= 4; // publish per box, share the SMs with a partner kernel
   for (int b = 0; b < nBoxes; ++b) { // some thick box has a 16-byte aligned side: use the vector variant
@@ -781,8 +788,11 @@ int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t
   const WorkItem *items =
       reinterpret_cast<const WorkItem *>(p + sizeof(BoxDesc) * size_t(info->nBoxes));
   // ordered plans are meant to run beside a partner kernel (a put beside the unpack that follows
-  // it region by region): they never take more than half of an SM's block slots, so the partner
-  // launched from another stream can always become resident next to them
+  // it region by region): their grid is at most two blocks per SM and their registers are
+  // bounded so that four blocks fit (checked below with the occupancy API), which leaves room
+  // for the partner launched from another stream - room, not a guarantee: a consumer that spins
+  // on flags of THIS GPU's producer must still be ordered behind it by an event (the workloads
+  // do that for self-neighbours)
   const bool waits = (info->reserved & 2) != 0, ordered = (info->reserved & 4) != 0;
   const bool vec = (info->reserved & 8) != 0;
   // Grid size.  Every block works through kItemsPerBlock (4, TZB_ITEMS_PER_BLOCK overrides;
@@ -806,6 +816,17 @@ int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t
   unsigned *ctr = static_cast<unsigned *>(scratch);
   ++g_launches;
   if (ordered) {
+    static const bool roomChecked = [] {
+      int n = 0;
+      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, box_copy_sync_kernel<double, kBlocksPerSM / 2>,
+                                                        kThreads, 0) != cudaSuccess)
+        (void)cudaGetLastError();
+      else if (n < kBlocksPerSM)
+        std::fprintf(stderr, "tzb: ordered box copy fits only %d blocks per SM (expected %d): kernels meant "
+                             "to overlap with it may have to wait\n", n, kBlocksPerSM);
+      return true;
+    }();
+    (void)roomChecked;
     const int blocks = grid(sm_count() * (kBlocksPerSM / 2));
     if (info->elemSize == 8)
       box_copy_sync_kernel<double, kBlocksPerSM / 2><<<blocks, kThreads, 0, s>>>(

@@ -72,7 +72,7 @@ void Args::set_default_topology(int size) {
 
 // ---------------------------------------------------------------- Domain
 namespace {
-constexpr int kNumStyles = 9; // + one extra flag set (acknowledgements of the pull style)
+constexpr int kNumStyles = 9; // + two extra flag sets: acknowledgements of the pull style, permissions of the direct puts
 size_t round_up_sz(size_t v, size_t a) { return (v + a - 1) / a * a; }
 } // namespace
 
@@ -120,7 +120,7 @@ Domain::Domain(std::shared_ptr<Communicator> comm, const Args &args, SymmetricHe
   stagingElems_ = off;
 
   const size_t stagingBytes = stagingElems_ * es;
-  const size_t flagBytes = sizeof(uint64_t) * 27 * (kNumStyles + 1);
+  const size_t flagBytes = sizeof(uint64_t) * 27 * (kNumStyles + 2);
   const size_t total = round_up_sz(grid_bytes(), 256) + 3 * round_up_sz(stagingBytes, 256) +
                        round_up_sz(flagBytes, 256) + 4096;
   heap_.reset(new SymmetricHeap(comm, total, memory));
@@ -206,6 +206,10 @@ uint64_t *Domain::ack_flags_base(int rank) const {
 
 uint64_t *Domain::ack_flag(int rank, const Dim3<int> &side) const {
   return ack_flags_base(rank) + dir_index(side);
+}
+
+uint64_t *Domain::ready_flag(int rank, const Dim3<int> &side) const {
+  return heap_->at<uint64_t>(rank, flagOff_) + size_t(kNumStyles + 1) * 27 + dir_index(side);
 }
 
 // ---------------------------------------------------------------- BoxCopyOp
@@ -479,10 +483,16 @@ struct Builder {
     return make_box(*dom, src, Side::Dense, {}, dom->grid(), Side::Grid, dom->recv_offset(e),
                     dom->region_extent(e));
   }
-  // my send region d -> neighbour's ghost cells on side -d
+  // my send region d -> neighbour's ghost cells on side -d.  Ghost cells are not double
+  // buffered, so the put may only start once the neighbour has said that it is done with what
+  // they held (it says so at the start of ITS exchange of this epoch, in the box that goes the
+  // other way); before waiting for that, this box grants the same permission to the neighbour.
   TzbBox direct_box(const Dim3<int> &d) const {
-    return make_box(*dom, my_grid(), Side::Grid, dom->send_offset(d), dom->grid_of(dom->neighbor(d)),
-                    Side::Grid, dom->recv_offset(-d), dom->region_extent(d));
+    TzbBox b = make_box(*dom, my_grid(), Side::Grid, dom->send_offset(d), dom->grid_of(dom->neighbor(d)),
+                        Side::Grid, dom->recv_offset(-d), dom->region_extent(d));
+    b.ready = dom->ready_flag(dom->neighbor(d), -d);
+    b.wait = dom->ready_flag(dom->rank(), d);
+    return b;
   }
   // pack + put into the neighbour's staging slot (one box per parity)
   TzbBox packput_box(const Dim3<int> &d, int parity, Style style) const {
@@ -500,11 +510,13 @@ struct Builder {
   // flag channels (heap offsets) of a box list, for the FlagSynchronizer
   void annotate(BoxCopyOp &op, const std::vector<TzbBox> &boxes) const {
     std::vector<uint64_t> pub, wait;
+    bool first = false;
     for (const TzbBox &bx : boxes) {
       if (bx.signal) pub.push_back(uint64_t(dom->heap().offset_of(bx.signal)));
+      if (bx.ready) pub.push_back(uint64_t(dom->heap().offset_of(bx.ready))), first = true;
       if (bx.wait) wait.push_back(uint64_t(dom->heap().offset_of(bx.wait)));
     }
-    op.set_flag_channels(pub, wait);
+    op.set_flag_channels(pub, wait, first);
   }
   std::shared_ptr<BoxCopyOp> op(const std::string &name, const std::vector<TzbBox> &even,
                                 const std::vector<TzbBox> &odd, bool ordered = false) const {
@@ -584,11 +596,19 @@ void add_to_graph(Graph<OpBase> &g, const std::shared_ptr<Domain> &dom,
         "he_wait_puts", dom->flags_base(dom->rank(), style), int(dirs.size()), b.null);
     waitOp->set_channels(dom->heap());
     OpPtr wait = waitOp;
+    // one put op per direction: the permissions cannot travel inside the puts (the put of
+    // direction d would wait for the neighbour's put of direction -d, which every rank may have
+    // queued BEHIND it), so a tiny op grants all of them up front
+    std::vector<uint64_t *> ready;
+    for (const auto &d : dirs) ready.push_back(dom->ready_flag(dom->neighbor(d), -d));
+    OpPtr readyOp = std::make_shared<SignalFlagsOp>("he_ready", ready, dom->heap(), b.null);
+    connect(g, preds, readyOp);
     for (const auto &d : dirs) {
       TzbBox box = b.direct_box(d);
+      box.ready = nullptr;
       box.signal = dom->flag(dom->neighbor(d), style, -d);
       OpPtr put = b.op("he_put_" + dir_suffix(d), {box});
-      connect(g, preds, put);
+      g.add_edge(readyOp, put);
       g.add_edge(put, wait);
     }
     connect(g, wait, succs);
@@ -705,7 +725,13 @@ void add_to_graph(Graph<OpBase> &g, const std::shared_ptr<Domain> &dom,
       }
     auto putOp = b.op("he_packput_pipe", put[0], put[1], true);
     auto finOp = b.op("he_waitunpack_pipe", fin[0], fin[1], true);
-    finOp->set_issue_order_only(true);
+    // The unpack may run beside the put only when every flag it spins on is published by
+    // ANOTHER GPU.  Where a neighbour is this rank itself (a rank-grid dimension of 1) the
+    // flags come from this GPU's own put kernel, and nothing guarantees that kernel a place
+    // on the SMs next to a spinning unpack: keep the real event edge there.
+    bool selfNeighbour = false;
+    for (const auto &d : dirs) selfNeighbour = selfNeighbour || dom->neighbor(d) == dom->rank();
+    finOp->set_issue_order_only(!selfNeighbour);
     connect(g, preds, OpPtr(putOp));
     g.add_edge(OpPtr(putOp), OpPtr(finOp)); // issue order only: the kernels may overlap
     connect(g, OpPtr(putOp), succs);

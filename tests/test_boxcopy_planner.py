@@ -20,7 +20,8 @@ class TzbBox(ctypes.Structure):
                 ("n1", ctypes.c_int32), ("n2", ctypes.c_int32), ("n3", ctypes.c_int32),
                 ("run", ctypes.c_int32),
                 ("signal", ctypes.c_void_p), ("wait", ctypes.c_void_p),
-                ("dstSlackLo", ctypes.c_int32), ("dstSlackHi", ctypes.c_int32)]
+                ("dstSlackLo", ctypes.c_int32), ("dstSlackHi", ctypes.c_int32),
+                ("ready", ctypes.c_void_p)]
 
 
 class TzbBoxPlanInfo(ctypes.Structure):

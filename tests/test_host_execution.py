@@ -294,3 +294,38 @@ def test_the_host_posted_comm_op_library_moves_data_between_ranks():
                 comm.barrier()
 
     _run_world(n_ranks, body)
+
+
+@pytest.mark.timeout(300)
+@pytest.mark.parametrize("size", [2, 4, 8])
+def test_consecutive_exchanges_without_any_barrier_between_them(size):
+    """An application alternates exchange and compute with no rank-wide barrier in between, so a
+    fast rank starts exchange e+1 while a slow neighbour is still reading the ghost cells of
+    exchange e.  Interior values change every epoch and every rank checks its ghosts right after
+    each exchange: staged styles rely on their two staging buffers, the styles that put straight
+    into ghost cells on the permission flags (TzbBox::ready) - a put that arrives an epoch early
+    shows up as a wrong ghost value here."""
+    import time
+
+    def body(rank, comm):
+        h = HaloExchange(comm=comm, nX=5, nY=4, nZ=3, nQ=2, nGhost=2, host=True)
+        h.platform.set_host_execution(True)
+        rng = random.Random(1000 + rank)       # different delays on every rank
+        g = h.args.nGhost
+        for style in halo_mod.STYLES:
+            seq = common.fixed_schedule(h.graph(style), h.platform)
+            h.platform.provision_events(seq)
+            h.fill()
+            base = h.expected()
+            comm.barrier()                      # only between styles
+            for epoch in range(1, 7):
+                interior = h.cells()[:, g:-g, g:-g, g:-g]
+                interior += 1.0e6               # "compute": every interior cell changes
+                seq.run(h.platform)
+                # a slow consumer: the neighbours may long be in their next exchange by now
+                time.sleep(rng.choice((0.0, 0.0, 0.006)))
+                # "consume": every cell, ghosts included, must carry this epoch's values
+                assert torch.equal(h.cells(), base + 1.0e6 * epoch), (style, epoch, rank)
+            comm.barrier()
+
+    _run_world(size, body)

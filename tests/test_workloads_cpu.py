@@ -99,7 +99,7 @@ def test_halo_geometry_and_graph_structure():
     edges = 4 * (2 * 2 * 4 + 2 * 6 * 2 + 8 * 2 * 2)
     corners = 8 * 8
     assert d.bytes_per_exchange() == (faces + edges + corners) * 2 * 8
-    for style, nv in (("reference", 2 + 26 * 5 + 1), ("staged", 2 + 52), ("direct", 2 + 27),
+    for style, nv in (("reference", 2 + 26 * 5 + 1), ("staged", 2 + 52), ("direct", 2 + 28),  # 26 puts + he_ready + he_wait_puts
                       ("fused_all", 4), ("fused_staged", 4)):
         g = h.graph("flat:" + style)
         assert g.vertex_size() == nv, style

@@ -31,7 +31,8 @@ class TzbBox(ctypes.Structure):
                 ("n1", ctypes.c_int32), ("n2", ctypes.c_int32), ("n3", ctypes.c_int32),
                 ("run", ctypes.c_int32),
                 ("signal", ctypes.c_void_p), ("wait", ctypes.c_void_p),
-                ("dstSlackLo", ctypes.c_int32), ("dstSlackHi", ctypes.c_int32)]
+                ("dstSlackLo", ctypes.c_int32), ("dstSlackHi", ctypes.c_int32),
+                ("ready", ctypes.c_void_p)]
 
 
 class TzbBoxPlanInfo(ctypes.Structure):
@@ -114,6 +115,11 @@ def test_static_scratch_entry_matches_allocating_entry(lib, dtype):
         torch.cuda.synchronize()
         # a copy is exact: same tolerance the other box-copy tests use (bitwise equality)
         assert torch.equal(got, want)
+        # and both agree with an oracle that shares nothing with the planner: plain slices of src
+        nq, ez, ey, row = src.shape
+        ex = row - 8
+        oracle = torch.cat([src[:, 0:3, 3:ey - 3, 3:ex - 3].reshape(-1), src[:, :, :, 3:6].reshape(-1)])
+        assert torch.equal(got, oracle)
         assert not bool((got == -1).any())
         assert flag_a.item() == epoch and flag_b.item() == epoch
 
