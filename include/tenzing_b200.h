@@ -117,6 +117,10 @@ typedef struct {
    * can be stored as one full 32-byte sector, which spares L2 the read-modify-write of a
    * partial-sector store. */
   int32_t dstSlackLo, dstSlackHi;
+  /* non-zero: dst is memory of ANOTHER GPU.  A plan whose payload mostly crosses NVLink is
+   * bound by the link, not by the SMs: it is launched with a small resident grid (one block
+   * per SM keeps the link full) so that kernels on other streams find free SM slots beside it. */
+  int32_t dstRemote, reserved0;
   /* "You may overwrite what I gave you last time": a (peer) flag published at the START of the
    * kernel, before anything is copied, or NULL.  A put that stores straight into memory its
    * partner also reads (ghost cells) pairs it with `wait`: every rank grants its partners

@@ -37,6 +37,7 @@ def main():
     ap.add_argument("--hand", action="store_true", help="hand-written fused_groups pipelines + put-only times")
     ap.add_argument("--no-spmv", action="store_true")
     ap.add_argument("--mixed-hand", action="store_true", help="hand schedules over the fused_mixed ops")
+    ap.add_argument("--rank-grid", default="", help="e.g. 1,2,1")
     args = ap.parse_args()
     rank, world, _ = init_process_group_from_env()
     comm = make_comm()
@@ -60,7 +61,8 @@ def main():
             torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
         return float(t.median()) * 1e6, ok, len(seq)
 
-    halo = HaloExchange(comm=comm, nX=args.nx, nQ=args.nq, nGhost=3, n_streams=args.streams)
+    rg = [int(v) for v in args.rank_grid.split(",")] if args.rank_grid else None
+    halo = HaloExchange(comm=comm, nX=args.nx, nQ=args.nq, nGhost=3, n_streams=args.streams, rank_grid=rg)
     def measure_seq(wl, seq):
         wl.fill()
         comm.barrier()

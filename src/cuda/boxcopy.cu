@@ -715,6 +715,16 @@ static int boxcopy_plan_impl(const TzbBox *boxes, int nBoxes, int elemSize, TzbB
     if (boxes[b].wait || boxes[b].ready) info->reserved |= 2; // the synchronising kernel
   }
   if (ordered) info->reserved |= 4; // publish per box, share the SMs with a partner kernel
+  {
+    // bit 6: most of the payload goes to another GPU - the link is the bottleneck
+    int64_t remoteBytes = 0;
+    for (int b = 0; b < nBoxes; ++b)
+      if (boxes[b].dstRemote)
+        remoteBytes += int64_t(boxes[b].run) * elemSize * boxes[b].n1 * boxes[b].n2 * boxes[b].n3;
+    bool thinSource = false; // strided thin sources need the full grid's loads in flight
+    for (int b = 0; b < nBoxes; ++b) thinSource = thinSource || (boxes[b].run > 0 && boxes[b].run < 64);
+    if (remoteBytes > 0 && remoteBytes * 2 >= totalBytes && !thinSource) info->reserved |= 64;
+  }
   for (int b = 0; b < nBoxes; ++b) { // some thick box has a 16-byte aligned side: use the vector variant
     const TzbBox &in = boxes[b];
     if (elemSize != 8 || in.run < 64 || (in.run & 1)) continue;
@@ -806,7 +816,17 @@ int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t
     const char *e = std::getenv("TZB_ITEMS_PER_BLOCK");
     return e ? std::max(0, std::atoi(e)) : 4;
   }();
+  // Link-bound plans (thick rows into another GPU): NVLink is saturated by two blocks per SM
+  // (TZB_LINK_BLOCKS_PER_SM overrides), and every further resident block would only hold an SM
+  // slot for the whole transfer that a kernel on another stream - the unpack of what has
+  // already arrived - could use.
+  static const int linkBlocksPerSM = [] {
+    const char *e = std::getenv("TZB_LINK_BLOCKS_PER_SM");
+    return e ? std::max(1, std::atoi(e)) : 2; // measured: 195 / 166 / 155 us with 4 / 1 / 2 (profiles/README.md)
+  }();
+  const bool linkBound = (info->reserved & 64) != 0;
   auto grid = [&](int cap) {
+    if (linkBound && !ordered) return std::min(info->nItems, sm_count() * linkBlocksPerSM);
     if (itemsPerBlock > 0 && !ordered)
       return std::max(1, (info->nItems + itemsPerBlock - 1) / itemsPerBlock);
     return std::min(info->nItems, cap);

@@ -2,6 +2,7 @@
 #include "tenzing/host_exec.hpp"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 #include "tenzing/numeric.hpp"
@@ -490,14 +491,21 @@ struct Builder {
   TzbBox direct_box(const Dim3<int> &d) const {
     TzbBox b = make_box(*dom, my_grid(), Side::Grid, dom->send_offset(d), dom->grid_of(dom->neighbor(d)),
                         Side::Grid, dom->recv_offset(-d), dom->region_extent(d));
-    b.ready = dom->ready_flag(dom->neighbor(d), -d);
-    b.wait = dom->ready_flag(dom->rank(), d);
+    b.dstRemote = dom->neighbor(d) != dom->rank();
+    // TZB_NO_READY=1: measurement knob (what does the handshake cost?) - not for production,
+    // see tests/test_host_execution.py::test_consecutive_exchanges_without_any_barrier_between_them
+    static const bool handshake = !(std::getenv("TZB_NO_READY") && std::atoi(std::getenv("TZB_NO_READY")) != 0);
+    if (handshake) {
+      b.ready = dom->ready_flag(dom->neighbor(d), -d);
+      b.wait = dom->ready_flag(dom->rank(), d);
+    }
     return b;
   }
   // pack + put into the neighbour's staging slot (one box per parity)
   TzbBox packput_box(const Dim3<int> &d, int parity, Style style) const {
     const int peer = dom->neighbor(d);
     TzbBox b = pack_box(d, dom->recv_staging(peer, parity, -d));
+    b.dstRemote = peer != dom->rank();
     b.signal = dom->flag(peer, style, -d);
     return b;
   }
@@ -694,6 +702,18 @@ void add_to_graph(Graph<OpBase> &g, const std::shared_ptr<Domain> &dom,
       std::memset(&w, 0, sizeof(w));
       w.wait = dom->flag(dom->rank(), style, d);
       thickWait.push_back(w);
+    }
+    // The permissions for the direct puts are granted by BOTH put kernels (the same stores
+    // twice): whichever of them the schedule runs first gets them out at the very start of the
+    // exchange, so a thick put that runs second finds them waiting instead of stalling until
+    // every partner has reached its own thick put.
+    for (const TzbBox &t : thick) {
+      if (!t.ready) continue;
+      TzbBox grant;
+      std::memset(&grant, 0, sizeof(grant));
+      grant.ready = t.ready;
+      thinPut[0].push_back(grant);
+      thinPut[1].push_back(grant);
     }
     OpPtr putThin = b.op("he_packput_thin", thinPut[0], thinPut[1]);
     OpPtr finThin = b.op("he_waitunpack_thin", thinFin[0], thinFin[1]);

@@ -29,7 +29,7 @@ int main(void) {
   box.s1 = ROW; box.s2 = 0; box.s3 = (int64_t)E1 * ROW;
   box.d1 = RUN; box.d2 = 0; box.d3 = (int64_t)N1 * RUN;
   box.n1 = N1; box.n2 = 1; box.n3 = N3; box.run = RUN;
-  box.signal = NULL; box.wait = NULL; box.dstSlackLo = 0; box.dstSlackHi = 0; box.ready = NULL;
+  box.signal = NULL; box.wait = NULL; box.dstSlackLo = 0; box.dstSlackHi = 0; box.dstRemote = 0; box.reserved0 = 0; box.ready = NULL;
   if (tzb_boxcopy_plan(&box, 1, 8, &info, NULL) != 0) return 2;
   image = malloc(info.planBytes);
   if (tzb_boxcopy_plan(&box, 1, 8, &info, image) != 0) return 3;

@@ -32,6 +32,7 @@ class TzbBox(ctypes.Structure):
                 ("run", ctypes.c_int32),
                 ("signal", ctypes.c_void_p), ("wait", ctypes.c_void_p),
                 ("dstSlackLo", ctypes.c_int32), ("dstSlackHi", ctypes.c_int32),
+                ("dstRemote", ctypes.c_int32), ("reserved0", ctypes.c_int32),
                 ("ready", ctypes.c_void_p)]
 
 
