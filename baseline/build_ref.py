@@ -10,17 +10,12 @@ sources:
               reference generates its version header from `git describe --tags`
   * arch:     -DCMAKE_CUDA_ARCHITECTURES=100a
 
-  python baseline/build_ref.py [--halo-patched]   ->  baseline/_ref/build/.../spmv-min-time etc.
-
---halo-patched additionally builds baseline/_ref/build_halo from a second copy of the sources with
-the patches of baseline/patches/ applied (the reference's halo driver throws at graph
-construction as shipped); that copy is only ever used for the labelled halo row.
+  python baseline/build_ref.py      ->  baseline/_ref/build/tenzing-dfs/examples/spmv etc.
 """
 import hashlib
 import os
 import shutil
 import subprocess
-import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 REF_SRC = os.environ.get("TENZING_REFERENCE", "/root/reference")
@@ -79,7 +74,7 @@ exec g++ -I"$INC" "$@" -L"$LIB" -Wl,-rpath,"$LIB" -lmpi
     return inc, lib, wrapper
 
 
-def checkout(dst, patches=()):
+def checkout(dst):
     """copy of the reference sources as a tagged git checkout (its CMake derives the version
     header from `git describe --tags`)"""
     if not os.path.isdir(REF_SRC):
@@ -91,12 +86,10 @@ def checkout(dst, patches=()):
         shutil.rmtree(dst)
     shutil.copytree(REF_SRC, dst, symlinks=True, ignore=shutil.ignore_patterns(".git"))
     run(["chmod", "-R", "u+w", dst])
-    for p in patches:
-        run(["patch", "-p1", "-i", p], cwd=dst)
     git = ["git", "-c", "user.name=baseline", "-c", "user.email=baseline@localhost", "-c", "init.defaultBranch=main"]
     run(git + ["init", "-q"], cwd=dst)
     run(git + ["add", "-A"], cwd=dst)
-    run(git + ["commit", "-q", "-m", "reference snapshot" + (" + halo patches" if patches else "")], cwd=dst)
+    run(git + ["commit", "-q", "-m", "reference snapshot"], cwd=dst)
     run(git + ["tag", "v0.1.0"], cwd=dst)
 
 
@@ -116,13 +109,6 @@ def main():
     checkout(src)
     shutil.rmtree(os.path.join(OUT, "build"), ignore_errors=True)  # paths of another machine in its cache
     cmake_build(src, os.path.join(OUT, "build"), wrapper, ["spmv-min-time", "spmv", "halo-mcts-min-time"])
-    if "--halo-patched" in sys.argv:
-        pdir = os.path.join(HERE, "patches")
-        patches = sorted(os.path.join(pdir, f) for f in os.listdir(pdir) if f.endswith(".patch"))
-        hsrc = os.path.join(OUT, "src_halo_patched")
-        checkout(hsrc, patches)
-        shutil.rmtree(os.path.join(OUT, "build_halo"), ignore_errors=True)
-        cmake_build(hsrc, os.path.join(OUT, "build_halo"), wrapper, ["halo-mcts-min-time"])
     with open(os.path.join(OUT, "BUILD_HOST"), "w") as f:
         f.write(host_id() + "\n")
     print("reference built in", OUT)

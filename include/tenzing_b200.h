@@ -84,6 +84,17 @@ int tzb_spmv_csr_pull_f32(int rows, const int *rowPtr, const int *colInd, const 
                           const uint64_t *ready, int nReady, const struct TzbFlagList_ *acks,
                           uint64_t epoch, uint32_t *counter, void *stream);
 
+/* One-to-many put through NVLS multicast (no counterpart in the reference, whose PostSend
+ * loops over MPI_Isend): src[0..n) is stored to the MULTICAST address mcDst, so NVSwitch writes
+ * it to the same offset of every rank's buffer bound to that multicast object; then the epoch is
+ * multicast-stored to mcFlag (the multicast address of this rank's word in every rank's flag
+ * array).  `counter`: one zeroed uint32.  The multicast mapping comes from the caller
+ * (torch.distributed._symmetric_memory in the Python front end, tenzing_b200/ops/nvls.py). */
+int tzb_multicast_put_f64(int n, const double *src, double *mcDst, uint64_t *mcFlag, uint64_t epoch,
+                          uint32_t *counter, void *stream);
+int tzb_multicast_put_f32(int n, const float *src, float *mcDst, uint64_t *mcFlag, uint64_t epoch,
+                          uint32_t *counter, void *stream);
+
 /* The whole distributed product in one launch (no counterpart in the reference, where it is
  * seven ops): gather-put of my x entries to every peer + flag publish, y = A_local x, wait for
  * the nFlags local flags, y += A_remote rx.  `counter`: one zeroed uint32 of scratch. */

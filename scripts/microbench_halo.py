@@ -69,8 +69,12 @@ def main():
                 continue  # a wait op run alone would spin for a flag nobody publishes
             if args.only and not any(k in op.name() for k in args.only.split(",")):
                 continue
+            if op.name() == "he_ready":
+                continue
             bound = _C.BoundGpuOp(op, 0)
-            seq = _C.Sequence([bound])
+            # a direct put waits for the neighbour's permission, which the style's he_ready op grants
+            pre = [_C.BoundGpuOp(g.find_name("he_ready"), 0)] if style == "direct" else []
+            seq = _C.Sequence(pre + [bound])
             ts = _C.device_time_steps(seq, h.platform, args.reps, flush.data_ptr(), flush.numel())
             us = sorted(ts)[len(ts) // 2] * 1e6
             d = [int(x[2:]) for x in op.name().split("_")[-3:]] if "_dx" in op.name() else None

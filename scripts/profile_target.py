@@ -22,7 +22,9 @@ if which == "halo":
             g = h.graph("flat:" + style)
             for n in ops:
                 op = g.find_name(n)
-                seq = _C.Sequence([_C.BoundGpuOp(op, 0)])
+                # a direct put waits for the neighbour's permission, which the style's he_ready op grants
+                pre = [_C.BoundGpuOp(g.find_name("he_ready"), 0)] if style == "direct" else []
+                seq = _C.Sequence(pre + [_C.BoundGpuOp(op, 0)])
                 seq.run(h.platform)
                 torch.cuda.synchronize()
         # a full fused_staged exchange (put + wait/unpack)

@@ -19,7 +19,7 @@ HEADER = """# SASS census of libtenzing_b200_kernels.so (cuobjdump -sass, sm_100
 # MEMBAR.*.SYS + ERRBAR = the release side of the cross-GPU flag protocol; LD*.STRONG.SYS +
 # NANOSLEEP = the acquire spin; LDG/ST .128 = 16-byte accesses on aligned sides; UBLKCP.S.G /
 # UBLKCP.G.S + SYNCS.*.TRANS64 = the bulk-copy engine (cp.async.bulk + mbarrier) of the
-# experimental box_bulk_kernel; no HMMA/UTC*MMA anywhere (bandwidth-bound kernels, no tensor-core
+# opt-in box_bulk_kernel; LDG/STG.E.ENL2.256 = 256-bit accesses of the thin-row unpack; no HMMA/UTC*MMA anywhere (bandwidth-bound kernels, no tensor-core
 # work).
 """
 

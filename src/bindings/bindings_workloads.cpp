@@ -78,6 +78,26 @@ void bind_workloads(py::module_ &m) {
     check(tzb_gather_put_f64(&a, ptr<int>(idx), ptr<double>(src), epoch, ptr<uint32_t>(counter),
                              ptr<void>(s)), "gather_put_f64");
   });
+  k.def("multicast_put", [](int n, uintptr_t src, uintptr_t mcDst, uintptr_t mcFlag, uint64_t epoch,
+                            uintptr_t counter, bool f64, uintptr_t s) {
+    if (f64)
+      check(tzb_multicast_put_f64(n, ptr<double>(src), ptr<double>(mcDst), ptr<uint64_t>(mcFlag), epoch,
+                                  ptr<uint32_t>(counter), ptr<void>(s)), "multicast_put_f64");
+    else
+      check(tzb_multicast_put_f32(n, ptr<float>(src), ptr<float>(mcDst), ptr<uint64_t>(mcFlag), epoch,
+                                  ptr<uint32_t>(counter), ptr<void>(s)), "multicast_put_f32");
+  });
+  k.def("spmv_csr_wait", [](int rows, uintptr_t rp, uintptr_t ci, uintptr_t val, uintptr_t x, uintptr_t y,
+                            bool accumulate, uintptr_t flags, int nFlags, uint64_t epoch, bool f64, uintptr_t s) {
+    if (f64)
+      check(tzb_spmv_csr_wait_f64(rows, ptr<int>(rp), ptr<int>(ci), ptr<double>(val), ptr<double>(x),
+                                  ptr<double>(y), accumulate, ptr<uint64_t>(flags), nFlags, epoch, ptr<void>(s)),
+            "spmv_csr_wait_f64");
+    else
+      check(tzb_spmv_csr_wait_f32(rows, ptr<int>(rp), ptr<int>(ci), ptr<float>(val), ptr<float>(x),
+                                  ptr<float>(y), accumulate, ptr<uint64_t>(flags), nFlags, epoch, ptr<void>(s)),
+            "spmv_csr_wait_f32");
+  });
   k.def("copy_bytes", [](uintptr_t dst, uintptr_t src, size_t bytes, uintptr_t s) {
     check(tzb_copy_bytes(ptr<void>(dst), ptr<void>(src), bytes, ptr<void>(s)), "copy_bytes");
   });

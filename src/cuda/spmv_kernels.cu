@@ -275,6 +275,28 @@ spmv_fused_all_kernel(TzbGatherPutArgs a, const int *__restrict__ sendIdx, int r
   }
 }
 
+// One-to-many put through NVLS: every store goes to a MULTICAST address, NVSwitch replicates it
+// into the same offset of every rank's buffer (the reference sends the same x entries to each
+// peer in a loop of MPI_Isend, include/tenzing/spmv/ops_spmv.cuh:217-240).  The epoch flag is
+// a multicast store too: word `myRank` of every rank's flag array, after a system-scope fence.
+__device__ __forceinline__ void multimem_st(double *p, double v) {
+  asm volatile("multimem.st.relaxed.sys.global.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
+}
+__device__ __forceinline__ void multimem_st(float *p, float v) {
+  asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+multicast_put_kernel(int n, const T *__restrict__ src, T *mcDst, uint64_t *mcFlag, uint64_t epoch,
+                     unsigned *counter) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    multimem_st(mcDst + i, __ldg(src + i));
+  if (block_arrive_last(counter, gridDim.x)) {
+    if (threadIdx.x == 0)
+      asm volatile("multimem.st.release.sys.global.u64 [%0], %1;" ::"l"(mcFlag), "l"(epoch) : "memory");
+  }
+}
+
 int grid_for(int n) {
   int blocks = (n + kThreads - 1) / kThreads;
   if (blocks > sm_count() * 8) blocks = sm_count() * 8;
@@ -550,6 +572,23 @@ int tzb_spmv_fused_all_f32(const TzbGatherPutArgs *put, const int *sendIdx, int 
   return launch_spmv_fused_all<float>(put, sendIdx, rows, lRowPtr, lColInd, lVal, rRowPtr, rColInd,
                                       rVal, x, rx, y, flags, nFlags, epoch, counter,
                                       kDefaultNnzPerRow, static_cast<cudaStream_t>(stream));
+}
+
+int tzb_multicast_put_f64(int n, const double *src, double *mcDst, uint64_t *mcFlag, uint64_t epoch,
+                          uint32_t *counter, void *stream) {
+  if (n < 0 || !mcFlag) return cudaErrorInvalidValue;
+  ++g_launches;
+  multicast_put_kernel<double><<<grid_for(std::max(n, 1)), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+      n, src, mcDst, mcFlag, epoch, counter);
+  return cudaGetLastError();
+}
+int tzb_multicast_put_f32(int n, const float *src, float *mcDst, uint64_t *mcFlag, uint64_t epoch,
+                          uint32_t *counter, void *stream) {
+  if (n < 0 || !mcFlag) return cudaErrorInvalidValue;
+  ++g_launches;
+  multicast_put_kernel<float><<<grid_for(std::max(n, 1)), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+      n, src, mcDst, mcFlag, epoch, counter);
+  return cudaGetLastError();
 }
 
 uint64_t tzb_launch_count(void) { return g_launches.load(); }

@@ -18,6 +18,9 @@ STYLES = ("reference", "fused", "fused_separate", "fused_all")
 EXPERIMENTAL_STYLES = ("fused_pull",)
 # built in Python, not an alternative of the ChoiceOp: Pack -> torch.distributed send/recv -> yr, y
 BASELINE_STYLES = ("dist",)
+# built in Python on torch's symmetric memory: x blocks through NVLS multicast (multimem.st);
+# only where the host exposes multicast (tenzing_b200.ops.nvls.available())
+NVLS_STYLES = ("nvls",)
 
 
 def _csr_from_dict(d, dtype):
@@ -104,6 +107,10 @@ class DistributedSpMV:
                 # second baseline: x entries through torch.distributed (NCCL / gloo)
                 from ..ops.dist_p2p import add_spmv_dist_style
                 self._graphs[style] = add_spmv_dist_style(self)
+                return self._graphs[style]
+            if style == "nvls":
+                from ..ops.nvls import add_spmv_nvls_style
+                self._graphs[style] = add_spmv_nvls_style(self)
                 return self._graphs[style]
             if style in ("choice", "choice+"):
                 op = getattr(_C.spmv, "make_spmv_choice" + self._sfx)(self.spmv, style == "choice+")

@@ -21,8 +21,6 @@ def all_ok(ok):
     return bool(t.item() > 0.5)
 
 
-# styles whose kernels / transports have not run on hardware yet join in on request only
-EXPERIMENTAL = os.environ.get("TENZING_TEST_EXPERIMENTAL") == "1"
 
 
 def main():
@@ -30,9 +28,13 @@ def main():
     comm = make_comm()
     failures = []
     halo_styles = ("reference", "staged", "direct", "fused_all", "fused_staged", "fused_groups",
-                   "fused_mixed", "fused_pipelined", "fused_pull") + (("dist",) if EXPERIMENTAL else ())
-    spmv_styles = ("reference", "fused", "fused_separate", "fused_all") + \
-        (("fused_pull", "dist") if EXPERIMENTAL else ())
+                   "fused_mixed", "fused_pipelined", "fused_pull", "dist")
+    from tenzing_b200.ops import nvls
+    have_nvls = nvls.available()
+    if rank == 0:
+        print("NVLS multicast available:", have_nvls, flush=True)
+    spmv_styles = ("reference", "fused", "fused_separate", "fused_all", "fused_pull", "dist") + \
+        (("nvls",) if have_nvls else ())
     for order in ("XYZQ", "QXYZ"):
         h = HaloExchange(comm=comm, nX=24, nY=10, nZ=12, nQ=2, nGhost=3, storage_order=order)
         for style in halo_styles:
@@ -64,6 +66,46 @@ def main():
                     if not all_ok(s.check()):
                         failures.append(f"spmv {dtype} n={n} {style}")
                         break
+    # Ialltoallv between real GPUs: rank r sends the 16 values 1000 r + p + (0..15) to every peer p
+    from tenzing_b200 import _C
+    from tenzing_b200.utils.tensor import device_tensor
+    heap = _C.SymmetricHeap(comm, 1 << 20)
+    k = 16
+    off_src, off_dst, off_flags = heap.alloc(k * 8 * world), heap.alloc(k * 8 * world), heap.alloc(8 * world)
+    src = device_tensor(heap.local_ptr() + off_src, (world, k), torch.float64, owner=heap)
+    dst = device_tensor(heap.local_ptr() + off_dst, (world, k), torch.float64, owner=heap)
+    tr = _C.P2PTransport()
+    plat = _C.Platform.make_n_streams(1, comm, False)
+    sreq = _C.Request()
+    a2a = _C.Ialltoallv(src.data_ptr(), [k * 8 * p for p in range(world)], [k * 8] * world,
+                        [heap.peer_ptr(p) + off_dst + k * 8 * rank for p in range(world)],
+                        [heap.peer_ptr(p) + off_flags + 8 * rank for p in range(world)], sreq, tr, "a2a")
+    rreqs = [_C.Request() for _ in range(world)]
+    irecvs = [_C.Irecv(heap.local_ptr() + off_flags + 8 * p, rreqs[p], tr, f"a2a_irecv{p}") for p in range(world)]
+    g = _C.Graph()
+    waits = [_C.Wait(sreq, "a2a_wait_send"), _C.MultiWait(rreqs, "a2a_wait_recv")]
+    for p_ in [a2a] + irecvs:
+        g.start_then(p_)
+        for w in waits:
+            g.then(p_, w)
+    for w in waits:
+        g.then_finish(w)
+    seq = _C.dfs.get_all_sequences(g, plat, 2, True)[0]
+    for epoch in range(3):
+        src.copy_((1000.0 * rank + torch.arange(world, device="cuda", dtype=torch.float64)[:, None]
+                   + torch.arange(k, device="cuda", dtype=torch.float64)[None, :]) + 0.5 * epoch)
+        dst.zero_()
+        torch.cuda.synchronize()
+        comm.barrier()
+        seq.run(plat)
+        plat.synchronize()
+        torch.cuda.synchronize()
+        comm.barrier()
+        exp = (1000.0 * torch.arange(world, device="cuda", dtype=torch.float64)[:, None] + rank
+               + torch.arange(k, device="cuda", dtype=torch.float64)[None, :]) + 0.5 * epoch
+        if not all_ok(bool(torch.equal(dst, exp))):
+            failures.append("Ialltoallv on devices")
+            break
     # a short search across ranks: rank 0 drives, all ranks execute in lock step
     h = HaloExchange(comm=comm, nX=32, nQ=1, nGhost=2, neighbors=6)
     res = h.search("mcts", style="choice", iters=8,

@@ -159,11 +159,9 @@ def test_host_posted_p2p_ops_in_a_searched_graph():
         assert torch.equal(out, exp)
 
 
-@pytest.mark.skipif(os.environ.get("TENZING_TEST_EXPERIMENTAL") != "1",
-                    reason="experimental bulk-copy path (TZB_BULK=1): not yet validated on hardware; "
-                           "set TENZING_TEST_EXPERIMENTAL=1 to run it")
-def test_experimental_bulk_copy_path_matches_the_oracle():
-    """box_bulk_kernel (cp.async.bulk + mbarrier) on the thick regions of the halo exchange.
+def test_bulk_copy_path_matches_the_oracle():
+    """box_bulk_kernel (cp.async.bulk + mbarrier, opt-in with TZB_BULK=1: validated on B200s, not
+    faster than the LSU path there) on the thick regions of the halo exchange.
     Runs in a subprocess under a hard time limit: a pipeline bug would hang the kernel."""
     import subprocess
     import sys
@@ -185,10 +183,7 @@ def test_experimental_bulk_copy_path_matches_the_oracle():
         assert p.returncode == 0 and "BULK_OK" in p.stdout, (p.stdout + p.stderr)[-3000:]
 
 
-@pytest.mark.skipif(os.environ.get("TENZING_TEST_EXPERIMENTAL") != "1",
-                    reason="experimental SpMV pull style: kernel not yet validated on hardware; "
-                           "set TENZING_TEST_EXPERIMENTAL=1 to run it")
-def test_experimental_spmv_pull_style_matches_the_oracle():
+def test_spmv_pull_style_matches_the_oracle():
     """spmv_csr_pull_kernel: the remote x entries are read from their owners inside the product.
     Subprocess under a hard time limit (a protocol bug would spin in a flag wait)."""
     import subprocess
@@ -205,3 +200,41 @@ def test_experimental_spmv_pull_style_matches_the_oracle():
     p = subprocess.run(["timeout", "120", sys.executable, "-c", code], capture_output=True, text=True,
                        cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     assert p.returncode == 0 and "PULL_OK" in p.stdout, (p.stdout + p.stderr)[-3000:]
+
+
+def test_ialltoallv_on_the_device():
+    """Ialltoallv (reference: include/tenzing/mpi/ops_mpi.hpp:82-119, src/mpi/ops_mpi.cpp:29-34)
+    executed on a GPU: copy-engine copies into "every peer's" receive slot (a world of one: this
+    rank itself) plus one flag per peer; the receive side completes through Irecv + Wait."""
+    import tenzing_b200 as tz
+    from tenzing_b200 import _C
+    from tenzing_b200.utils.tensor import device_tensor
+    comm = _C.SelfComm()
+    heap = _C.SymmetricHeap(comm, 1 << 20)
+    n = 1000
+    src = device_tensor(heap.local_ptr() + heap.alloc(n * 8), (n,), torch.float64, owner=heap)
+    dst = device_tensor(heap.peer_ptr(0) + heap.alloc(n * 8), (n,), torch.float64, owner=heap)
+    flag_off = heap.alloc(8)
+    tr = _C.P2PTransport()
+    plat = tz.Platform.make_n_streams(1)
+    sreq, rreq = _C.Request(), _C.Request()
+    a2a = _C.Ialltoallv(src.data_ptr(), [0], [n * 8], [dst.data_ptr()], [heap.peer_ptr(0) + flag_off],
+                        sreq, tr, "a2a")
+    irecv = _C.Irecv(heap.local_ptr() + flag_off, rreq, tr, "irecv")
+    g = tz.Graph()
+    wsend, wrecv = _C.Wait(sreq, "wait_send"), _C.Wait(rreq, "wait_recv")
+    for p in (a2a, irecv):
+        g.start_then(p)
+        g.then(p, wsend)
+        g.then(p, wrecv)
+    g.then_finish(wsend)
+    g.then_finish(wrecv)
+    seq = tz.dfs.get_all_sequences(g, plat, 4, True)[0]
+    for epoch in range(3):
+        src.copy_(torch.arange(n, dtype=torch.float64, device="cuda") * (epoch + 1))
+        dst.zero_()
+        torch.cuda.synchronize()
+        seq.run(plat)
+        plat.synchronize()
+        torch.cuda.synchronize()
+        assert torch.equal(dst, src)
