@@ -256,6 +256,58 @@ def main():
         bo = common.bench_opts(n_iters=n_meas, target_secs=0.01, max_retries=0, check_randomness=False)
         return _C.EmpiricalBenchmarker().benchmark(seq, wl.platform, bo).pct10
 
+    def graph_replay_of(wl, seq):
+        """the schedule captured as a CUDA graph (one launch per step, the kernels read the epoch
+        from a device word), or None where it cannot be (host-driven ops), fails to capture on
+        some rank, or does not reproduce the oracle"""
+        if host:
+            return None
+        ok, _why = _C.GraphReplay.supported(seq)
+        replay = None
+        if ok:
+            try:
+                wl.platform.provision_events(seq)
+                replay = _C.GraphReplay(seq, wl.platform)
+            except Exception as e:  # noqa: BLE001 - falls back to stream launches
+                if rank == 0:
+                    print(f"graph capture failed: {e}", file=sys.stderr)
+                replay = None
+        flag = torch.tensor([1.0 if replay is not None else 0.0], device=dev)
+        if world > 1:
+            torch.distributed.all_reduce(flag, op=torch.distributed.ReduceOp.MIN)
+        if flag.item() < 0.5:
+            return None
+        wl.fill()
+        comm.barrier()
+        replay.launch()
+        replay.launch()
+        wl.sync()
+        comm.barrier()
+        good = torch.tensor([1.0 if wl.check() else 0.0], device=dev)
+        if world > 1:
+            torch.distributed.all_reduce(good, op=torch.distributed.ReduceOp.MIN)
+        return replay if good.item() > 0.5 else None
+
+    def timed_graph(wl, replay, steps, warmup):
+        _C.device_time_graph_steps(replay, wl.platform, warmup, flush.data_ptr(), flush.numel())
+        t = _C.device_time_graph_steps(replay, wl.platform, steps, flush.data_ptr(), flush.numel())
+        return max_over_ranks(t), replay.kernel_nodes() * steps
+
+    def measure(wl, seq, steps, warmup):
+        """the schedule timed both ways - ops issued one by one into the streams, and the same
+        schedule replayed as a CUDA graph; the faster one is the number"""
+        t_stream, l_stream = timed(wl, seq, steps, warmup)
+        rec = {"us_stream_launches": round(statistics.mean(t_stream) * 1e6, 3)}
+        times, launches, mode, replay = t_stream, l_stream, "stream launches", None
+        r = graph_replay_of(wl, seq)
+        if r is not None:
+            t_graph, l_graph = timed_graph(wl, r, steps, warmup)
+            rec["us_cuda_graph"] = round(statistics.mean(t_graph) * 1e6, 3)
+            if statistics.mean(t_graph) < statistics.mean(t_stream):
+                times, launches, mode, replay = t_graph, l_graph, "cuda graph replay", r
+        rec["launch"] = mode
+        return times, launches, rec, replay
+
     # implementation styles whose decision space is small enough to enumerate completely
     SMALL = {"fused_all", "fused_staged", "fused_mixed", "fused_pipelined", "fused_pull",
              "fused", "fused_separate"}
@@ -316,7 +368,7 @@ def main():
         comm.barrier()
         return wl.check()
 
-    def spmv_e2e(wl, seq, steps, warmup):
+    def spmv_e2e(wl, seq, steps, warmup, replay=None):
         """through the public API, per step: H2D of this rank's x block from pinned host memory,
         the schedule, D2H of this rank's y block into pinned host memory; host wall clock"""
         rows = wl.x.numel()
@@ -334,7 +386,11 @@ def main():
             t0 = time.perf_counter()
             wl.x.copy_(xh, non_blocking=True)
             stream_sync()
-            seq.run(wl.platform)
+            if replay is not None:
+                replay.launch()
+                wl.platform.synchronize()
+            else:
+                seq.run(wl.platform)
             yh.copy_(wl.y, non_blocking=True)
             stream_sync()
             t.append(time.perf_counter() - t0)
@@ -364,8 +420,8 @@ def main():
     if rank == 0:
         sampler.start()
     comm.barrier()
-    times_s, launches_s = timed(spmv, seq_s, args.steps, args.warmup)
-    e2e_s, h2d_s, d2h_s = spmv_e2e(spmv, seq_s, args.steps, args.warmup)
+    times_s, launches_s, rec_s, replay_s = measure(spmv, seq_s, args.steps, args.warmup)
+    e2e_s, h2d_s, d2h_s = spmv_e2e(spmv, seq_s, args.steps, args.warmup, replay_s)
     b2b_s = back_to_back(spmv, seq_s, 20)
     clocks = sampler.stop() if rank == 0 else {}
     us_s = statistics.mean(times_s) * 1e6
@@ -377,7 +433,7 @@ def main():
     spmv32.fill()
     seq_s32 = find_best(spmv32, "dfs", SPMV_STYLES, 64, args.search_budget / 4)
     ok_all &= run_and_check(spmv32, seq_s32)
-    times_s32, _ = timed(spmv32, seq_s32, args.steps, args.warmup)
+    times_s32, _, rec_s32, _ = measure(spmv32, seq_s32, args.steps, args.warmup)
     b2b_s32 = back_to_back(spmv32, seq_s32, 20)
 
     out = {
@@ -391,20 +447,21 @@ def main():
                    "l2": "256 MB flush buffer written and read back before every timed step",
                    "timing": "CUDA events, one step per measurement, ranks lined up by a device-side barrier, "
                              "max over ranks, mean of the steps",
+                   "launch": rec_s["launch"] + " (the schedule is timed both ways, the faster is the value)",
                    "search": "no search" if args.no_search else
                    "exhaustive DFS inside each fused style, the 5 best re-measured with 20 measurements each"},
         "schedule": seq_s.names(),
-        "spmv": {"us": round(us_s, 3), **stats([t * 1e6 for t in times_s]), "n": args.spmv_n,
+        "spmv": {"us": round(us_s, 3), **rec_s, **stats([t * 1e6 for t in times_s]), "n": args.spmv_n,
                  "roofline_us": round(roof_s * 1e6, 3), "roofline_frac_of_measured": round(roof_s * 1e6 / us_s, 4),
                  "reference_protocol_pct10_us": None if b2b_s is None else round(b2b_s * 1e6, 3),
-                 "fp32": {"us": round(statistics.mean(times_s32) * 1e6, 3), "schedule": seq_s32.names(),
+                 "fp32": {"us": round(statistics.mean(times_s32) * 1e6, 3), **rec_s32, "schedule": seq_s32.names(),
                           "reference_protocol_pct10_us": None if b2b_s32 is None else round(b2b_s32 * 1e6, 3)}},
         "e2e": {"value": round(statistics.median(e2e_s), 3), "unit": "us", **stats(e2e_s),
                 "h2d_bytes_per_step": h2d_s, "d2h_bytes_per_step": d2h_s},
         "gpu_launches": int(launches_s), "clocks": clocks,
         "impl": "ours-host-dry-run (not a result)" if host else "ours",
     }
-    del spmv32
+    del spmv32, replay_s
 
     # ---------------- BASELINE config 3: 3-D halo exchange ----------------
     if "halo" not in skip:
@@ -420,7 +477,7 @@ def main():
         seq_h = find_best(halo, "mcts", fused + ["choice"], args.search_iters, args.search_budget)
         ok_h = run_and_check(halo, seq_h)
         ok_all &= ok_h
-        times_h, launches_h = timed(halo, seq_h, args.steps, args.warmup)
+        times_h, launches_h, rec_h, replay_h = measure(halo, seq_h, args.steps, args.warmup)
         # end to end: H2D of one fresh interior z-plane (all quantities), the exchange, D2H of a ghost row
         a = halo.args
         g = a.nGhost
@@ -439,7 +496,11 @@ def main():
             t0 = time.perf_counter()
             cells[:, g, g:g + a.nY, g:g + a.nX].copy_(plane, non_blocking=True)
             stream_sync()
-            seq_h.run(halo.platform)
+            if replay_h is not None:
+                replay_h.launch()
+                halo.platform.synchronize()
+            else:
+                seq_h.run(halo.platform)
             row_out.copy_(cells[0, 0, g, g:g + a.nX], non_blocking=True)
             stream_sync()
             e2e.append(time.perf_counter() - t0)
@@ -450,7 +511,7 @@ def main():
         # roofline: the slower of (bytes over NVLink / link bw) and (HBM bytes / HBM bw); every halo
         # byte is read once and written once somewhere (locally or on the peer)
         roof_h = max(remote / nvl, (2 * bytes_out - remote) / hbm)
-        out["halo"] = {"us": round(us_h, 3), **stats([t * 1e6 for t in times_h]),
+        out["halo"] = {"us": round(us_h, 3), **rec_h, **stats([t * 1e6 for t in times_h]),
                        "config": f"halo {args.nx}^3 fp64/rank nQ={args.nq} radius 3, 26 neighbours, XYZQ, "
                                  "rank grid " + "x".join(map(str, halo.domain.rank_grid())),
                        "schedule": seq_h.names(), "correct": bool(ok_h),
@@ -460,7 +521,7 @@ def main():
                        "gbs_per_rank": round(bytes_out / (us_h * 1e-6) / 1e9, 1),
                        "gpu_launches": int(launches_h),
                        "e2e_us": stats(e2e_h), "e2e_h2d_bytes": plane.numel() * 8, "e2e_d2h_bytes": row_out.numel() * 8}
-        del halo, cells
+        del replay_h, halo, cells
 
     # ---------------- BASELINE config 2: band SpMV 1M x 1M, fp64, DFS ----------------
     if "spmv_1m" not in skip:
@@ -471,14 +532,14 @@ def main():
         seq_b = find_best(big, "dfs", SPMV_STYLES, 64, args.search_budget / 2)
         ok_b = run_and_check(big, seq_b)
         ok_all &= ok_b
-        times_b, launches_b = timed(big, seq_b, args.steps, args.warmup)
+        times_b, launches_b, rec_b, replay_b = measure(big, seq_b, args.steps, args.warmup)
         us_b = statistics.mean(times_b) * 1e6
         roof_b = max((big.recv_bytes() if world > 1 else 0) / nvl, big.hbm_bytes() / hbm)
-        out["spmv_1m"] = {"us": round(us_b, 3), **stats([t * 1e6 for t in times_b]), "n": args.spmv_big_n,
+        out["spmv_1m"] = {"us": round(us_b, 3), **rec_b, **stats([t * 1e6 for t in times_b]), "n": args.spmv_big_n,
                           "schedule": seq_b.names(), "correct": bool(ok_b), "roofline_us": round(roof_b * 1e6, 3),
                           "roofline_frac_of_measured": round(roof_b * 1e6 / us_b, 4),
                           "gpu_launches": int(launches_b)}
-        del big
+        del replay_b, big
 
     # ---------------- BASELINE config 4: random-sparse SpMV, MCTS, 3 streams ----------------
     if "spmv_random" not in skip and not host:
@@ -493,16 +554,16 @@ def main():
             seq_r, _ = common.best_of(res)
         ok_r = run_and_check(rnd, seq_r)
         ok_all &= ok_r
-        times_r, launches_r = timed(rnd, seq_r, args.steps, args.warmup)
+        times_r, launches_r, rec_r, replay_r = measure(rnd, seq_r, args.steps, args.warmup)
         us_r = statistics.mean(times_r) * 1e6
         roof_r = max((rnd.recv_bytes() if world > 1 else 0) / nvl, rnd.hbm_bytes() / hbm)
-        out["spmv_random"] = {"us": round(us_r, 3), **stats([t * 1e6 for t in times_r]), "n": n_r, "streams": 3,
+        out["spmv_random"] = {"us": round(us_r, 3), **rec_r, **stats([t * 1e6 for t in times_r]), "n": n_r, "streams": 3,
                               "search": f"MCTS FastMin {args.search_iters} iterations over the ChoiceOp of all styles",
                               "schedule": seq_r.names(), "correct": bool(ok_r),
                               "roofline_us": round(roof_r * 1e6, 3),
                               "roofline_frac_of_measured": round(roof_r * 1e6 / us_r, 4),
                               "gpu_launches": int(launches_r)}
-        del rnd
+        del replay_r, rnd
 
     ok = torch.tensor([1.0 if ok_all else 0.0], device=dev)
     if world > 1:

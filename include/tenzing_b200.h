@@ -221,6 +221,18 @@ int tzb_flags_wait(const uint64_t *flags, int n, uint64_t epoch, void *stream);
  * current device; call it before launching (it is a synchronous copy to a device symbol). */
 int tzb_set_wait_timeout_ms(unsigned ms);
 
+/* ---------------------------------------------------- CUDA-graph replay ---- */
+/* Every kernel above takes its epoch by value.  A launch sequence captured into a CUDA graph is
+ * replayed with the same arguments, so for capture the epoch can come from a device word
+ * instead: while an epoch source is set (for the calling thread; set it around the capture only), every
+ * launch of this library hands the word's address to its kernel, which reads the epoch from it
+ * and ignores the by-value argument.  tzb_epoch_advance enqueues `*devWord += 1` - the first node
+ * of such a graph.  (The reference has no counterpart: its benchmark loop re-issues every op
+ * from the host, src/benchmarker.cpp:93-97.) */
+void tzb_set_epoch_source(const uint64_t *devWord); /* per calling thread; NULL = by value again */
+int tzb_epoch_advance(uint64_t *devWord, void *stream);
+int tzb_epoch_set(uint64_t *devWord, uint64_t value, void *stream);
+
 /* ------------------------------------------------------------ diagnostics -- */
 /* L2 flush between timed steps: writes `bytes` (> L2 size) of `buf` with `value`, then reads
  * them back, so L2 ends up full of CLEAN lines of the flush buffer and the timed kernel does

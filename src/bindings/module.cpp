@@ -10,6 +10,7 @@
 #include <pybind11/stl.h>
 
 #include "tenzing/cuda/device_barrier.hpp"
+#include "tenzing/cuda/graph_replay.hpp"
 #include "tenzing/host_exec.hpp"
 #include "tenzing/tenzing.hpp"
 
@@ -738,6 +739,51 @@ PYBIND11_MODULE(_C, m) {
         return out;
       },
       py::arg("seq"), py::arg("plat"), py::arg("steps"), py::arg("flush_ptr") = 0,
+      py::arg("flush_bytes") = 0, py::call_guard<py::gil_scoped_release>());
+
+  // ---- CUDA-graph replay of a sequence ----
+  py::class_<GraphReplay>(m, "GraphReplay")
+      .def(py::init([](Seq &seq, Platform &plat) { return new GraphReplay(seq, plat); }), py::arg("seq"),
+           py::arg("plat"), py::keep_alive<1, 3>())
+      .def_static("supported", [](const Seq &seq) {
+        std::string why;
+        const bool ok = GraphReplay::supported(seq, &why);
+        return std::make_pair(ok, why);
+      })
+      .def("launch", &GraphReplay::launch, py::call_guard<py::gil_scoped_release>())
+      .def("kernel_nodes", &GraphReplay::kernel_nodes);
+  // device time of single replays, measured exactly as device_time_steps measures single steps
+  m.def(
+      "device_time_graph_steps",
+      [](GraphReplay &replay, Platform &plat, int steps, uintptr_t flushPtr, size_t flushBytes) {
+        std::vector<double> out;
+        cudaEvent_t start, stop;
+        CUDA_RUNTIME(cudaEventCreate(&start));
+        CUDA_RUNTIME(cudaEventCreate(&stop));
+        cudaStream_t s0 = replay.stream();
+        if (plat.comm().size() > 1 && !plat.device_barrier())
+          plat.set_device_barrier(std::make_shared<DeviceBarrier>(plat.comm_ptr()));
+        for (int i = 0; i < steps; ++i) {
+          plat.synchronize();
+          plat.comm().barrier();
+          if (flushPtr && flushBytes)
+            CUDA_RUNTIME(cudaError_t(tzb_l2_flush(reinterpret_cast<void *>(flushPtr), flushBytes, unsigned(i), s0)));
+          else
+            CUDA_RUNTIME(cudaError_t(tzb_delay_us(30, s0)));
+          if (plat.device_barrier()) plat.device_barrier()->enqueue(s0);
+          CUDA_RUNTIME(cudaEventRecord(start, s0));
+          replay.launch();
+          CUDA_RUNTIME(cudaEventRecord(stop, s0));
+          CUDA_RUNTIME(cudaEventSynchronize(stop));
+          float ms = 0;
+          CUDA_RUNTIME(cudaEventElapsedTime(&ms, start, stop));
+          out.push_back(double(ms) * 1e-3);
+        }
+        cudaEventDestroy(start);
+        cudaEventDestroy(stop);
+        return out;
+      },
+      py::arg("replay"), py::arg("plat"), py::arg("steps"), py::arg("flush_ptr") = 0,
       py::arg("flush_bytes") = 0, py::call_guard<py::gil_scoped_release>());
 
   // ---- DFS ----

@@ -221,6 +221,9 @@ __device__ __forceinline__ void thin_item(const BoxDesc &b, const WorkItem &w, u
   }
 }
 
+// 256-bit accesses on thick rows (TZB_WIDE256=1): off by default until measured over NVLink
+__device__ int kWide256 = 0;
+
 template <typename T, bool VEC, int kThick, int kThin, int HINT = 0>
 __device__ __forceinline__ void copy_item(const BoxDesc &b, const WorkItem &w, int lane, int warp) {
   const T *src = reinterpret_cast<const T *>(b.src) + int64_t(w.i3) * b.s3;
@@ -232,6 +235,20 @@ __device__ __forceinline__ void copy_item(const BoxDesc &b, const WorkItem &w, i
       const int j2 = r / w.c1, j1 = r - j2 * w.c1;
       const T *s = src + int64_t(w.i2 + j2) * b.s2 + int64_t(w.i1 + j1) * b.s1;
       T *d = dst + int64_t(w.i2 + j2) * b.d2 + int64_t(w.i1 + j1) * b.d1;
+      if (VEC && sizeof(T) == 8 && kWide256 && (run & 3) == 0 &&
+          ((reinterpret_cast<uintptr_t>(s) | reinterpret_cast<uintptr_t>(d)) & 31) == 0) {
+        // both sides 32-byte aligned (grid rows from the first interior cell are): 256-bit
+        // loads and stores, a warp moves 1 KB per instruction
+        const int quads = run >> 2;
+        int p = lane;
+        for (; p + 32 < quads; p += 64) {
+          const U256 a = ld256(s + 4 * p), b = ld256(s + 4 * (p + 32));
+          st256(d + 4 * p, a);
+          st256(d + 4 * (p + 32), b);
+        }
+        for (; p < quads; p += 32) st256(d + 4 * p, ld256(s + 4 * p));
+        continue;
+      }
       if (VEC && sizeof(T) == 8) {
         // 16-byte accesses on whichever side is 16-byte aligned (staging buffers always are;
         // grid rows start at x = nGhost and usually are not): over NVLink a warp then stores
@@ -316,7 +333,8 @@ __device__ __forceinline__ void copy_item(const BoxDesc &b, const WorkItem &w, i
 template <typename T, bool VEC>
 __global__ void __launch_bounds__(kThreads, kBlocksPerSM)
 box_copy_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restrict__ items, int nItems,
-                int nBoxes, int anySignal, uint64_t epoch, unsigned *counter) {
+                int nBoxes, int anySignal, EpochArg epochArg, unsigned *counter) {
+  const uint64_t epoch = epochArg.get();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   __shared__ alignas(16) unsigned long long thinSm[kThinSmemElems];
   for (int it = blockIdx.x; it < nItems; it += gridDim.x) {
@@ -339,7 +357,8 @@ box_copy_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restrict__ 
 template <typename T, int HINT>
 __global__ void __launch_bounds__(kThreads, kBlocksPerSM)
 box_copy_hint_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restrict__ items, int nItems,
-                     int nBoxes, int anySignal, uint64_t epoch, unsigned *counter) {
+                     int nBoxes, int anySignal, EpochArg epochArg, unsigned *counter) {
+  const uint64_t epoch = epochArg.get();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (int it = blockIdx.x; it < nItems; it += gridDim.x) {
     const WorkItem w = items[it];
@@ -363,7 +382,8 @@ box_copy_hint_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restri
 template <typename T, int MIN_BLOCKS>
 __global__ void __launch_bounds__(kThreads, kBlocksPerSM)
 box_copy_sync_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restrict__ items,
-                     int nItems, int nBoxes, int anySignal, uint64_t epoch, unsigned *counter) {
+                     int nItems, int nBoxes, int anySignal, EpochArg epochArg, unsigned *counter) {
+  const uint64_t epoch = epochArg.get();
   constexpr bool kPerBox = MIN_BLOCKS < kBlocksPerSM; // the ordered (half-occupancy) variant
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   __shared__ unsigned readyMask; // boxes whose wait flag this block has already seen
@@ -443,7 +463,8 @@ __device__ __forceinline__ uint32_t smem_u32(const void *p) {
 
 __global__ void __launch_bounds__(32)
 box_bulk_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restrict__ items, int nItems,
-                int nBoxes, int elemSize, int anySignal, uint64_t epoch, unsigned *counter) {
+                int nBoxes, int elemSize, int anySignal, EpochArg epochArg, unsigned *counter) {
+  const uint64_t epoch = epochArg.get();
   __shared__ alignas(128) unsigned char stage[kBulkStages][kBulkStageBytes];
   __shared__ alignas(8) uint64_t bar[kBulkStages];
   if (threadIdx.x == 0) {
@@ -536,14 +557,16 @@ box_bulk_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restrict__ 
   }
 }
 
-__global__ void flags_signal_kernel(TzbFlagList l, uint64_t epoch) {
+__global__ void flags_signal_kernel(TzbFlagList l, EpochArg epochArg) {
+  const uint64_t epoch = epochArg.get();
   if (int(threadIdx.x) < l.n) {
     __threadfence_system();
     st_release_sys(l.flag[threadIdx.x], epoch);
   }
 }
 
-__global__ void flags_wait_kernel(const uint64_t *flags, int n, uint64_t epoch) {
+__global__ void flags_wait_kernel(const uint64_t *flags, int n, EpochArg epochArg) {
+  const uint64_t epoch = epochArg.get();
   for (int i = threadIdx.x; i < n; i += blockDim.x) wait_flag_geq(flags + i, epoch);
 }
 
@@ -792,6 +815,13 @@ static bool bulk_enabled() {
 int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t epoch,
                        void *scratch, void *stream) {
   if (!devPlan || !info) return cudaErrorInvalidValue;
+  static const bool wideSet = [] {
+    const char *e = std::getenv("TZB_WIDE256");
+    const int v = (e && std::atoi(e) != 0) ? 1 : 0;
+    if (v) (void)cudaMemcpyToSymbol(kWide256, &v, sizeof(v));
+    return true;
+  }();
+  (void)wideSet;
   if (info->nItems == 0) return cudaSuccess;
   const char *p = static_cast<const char *>(devPlan) + sizeof(PlanHeader);
   const BoxDesc *boxes = reinterpret_cast<const BoxDesc *>(p);
@@ -850,50 +880,50 @@ int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t
     const int blocks = grid(sm_count() * (kBlocksPerSM / 2));
     if (info->elemSize == 8)
       box_copy_sync_kernel<double, kBlocksPerSM / 2><<<blocks, kThreads, 0, s>>>(
-          boxes, items, info->nItems, info->nBoxes, anySignal, epoch, ctr);
+          boxes, items, info->nItems, info->nBoxes, anySignal, ep(epoch), ctr);
     else
       box_copy_sync_kernel<float, kBlocksPerSM / 2><<<blocks, kThreads, 0, s>>>(
-          boxes, items, info->nItems, info->nBoxes, anySignal, epoch, ctr);
+          boxes, items, info->nItems, info->nBoxes, anySignal, ep(epoch), ctr);
   } else if (waits) {
     // strictly ordered after the local producers (graph edge): full occupancy is safe
     const int blocks = grid(sm_count() * kBlocksPerSM);
     if (info->elemSize == 8)
       box_copy_sync_kernel<double, kBlocksPerSM><<<blocks, kThreads, 0, s>>>(
-          boxes, items, info->nItems, info->nBoxes, anySignal, epoch, ctr);
+          boxes, items, info->nItems, info->nBoxes, anySignal, ep(epoch), ctr);
     else
       box_copy_sync_kernel<float, kBlocksPerSM><<<blocks, kThreads, 0, s>>>(
-          boxes, items, info->nItems, info->nBoxes, anySignal, epoch, ctr);
+          boxes, items, info->nItems, info->nBoxes, anySignal, ep(epoch), ctr);
   } else if ((info->reserved & 16) && bulk_enabled()) {
     // experimental bulk-copy path (see box_bulk_kernel); one warp per block, 7 blocks per SM
     const int blocks = grid(sm_count() * 7);
     box_bulk_kernel<<<blocks, 32, 0, s>>>(boxes, items, info->nItems, info->nBoxes, info->elemSize,
-                                          anySignal, epoch, ctr);
+                                          anySignal, ep(epoch), ctr);
   } else if (thin_hint() && info->elemSize == 8) {
     const int blocks = grid(sm_count() * kBlocksPerSM);
     switch (thin_hint()) {
     case 64:
       box_copy_hint_kernel<double, 64><<<blocks, kThreads, 0, s>>>(boxes, items, info->nItems, info->nBoxes,
-                                                                  anySignal, epoch, ctr);
+                                                                  anySignal, ep(epoch), ctr);
       break;
     case 128:
       box_copy_hint_kernel<double, 128><<<blocks, kThreads, 0, s>>>(boxes, items, info->nItems, info->nBoxes,
-                                                                   anySignal, epoch, ctr);
+                                                                   anySignal, ep(epoch), ctr);
       break;
     default:
       box_copy_hint_kernel<double, 256><<<blocks, kThreads, 0, s>>>(boxes, items, info->nItems, info->nBoxes,
-                                                                   anySignal, epoch, ctr);
+                                                                   anySignal, ep(epoch), ctr);
     }
   } else {
     const int blocks = grid(sm_count() * kBlocksPerSM);
     if (info->elemSize == 8 && vec)
       box_copy_kernel<double, true><<<blocks, kThreads, 0, s>>>(boxes, items, info->nItems,
-                                                                info->nBoxes, anySignal, epoch, ctr);
+                                                                info->nBoxes, anySignal, ep(epoch), ctr);
     else if (info->elemSize == 8)
       box_copy_kernel<double, false><<<blocks, kThreads, 0, s>>>(boxes, items, info->nItems,
-                                                                 info->nBoxes, anySignal, epoch, ctr);
+                                                                 info->nBoxes, anySignal, ep(epoch), ctr);
     else
       box_copy_kernel<float, false><<<blocks, kThreads, 0, s>>>(boxes, items, info->nItems,
-                                                                info->nBoxes, anySignal, epoch, ctr);
+                                                                info->nBoxes, anySignal, ep(epoch), ctr);
   }
   return cudaGetLastError();
 }
@@ -934,14 +964,14 @@ int tzb_flags_signal(const TzbFlagList *list, uint64_t epoch, void *stream) {
   if (!list || list->n < 0 || list->n > 32) return cudaErrorInvalidValue;
   if (list->n == 0) return cudaSuccess;
   ++g_launches;
-  flags_signal_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(*list, epoch);
+  flags_signal_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(*list, ep(epoch));
   return cudaGetLastError();
 }
 
 int tzb_flags_wait(const uint64_t *flags, int n, uint64_t epoch, void *stream) {
   if (n <= 0) return cudaSuccess;
   ++g_launches;
-  flags_wait_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(flags, n, epoch);
+  flags_wait_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(flags, n, ep(epoch));
   return cudaGetLastError();
 }
 

@@ -23,6 +23,18 @@ static inline cudaError_t set_wait_timeout_ns_this_tu(unsigned long long ns) {
   return cudaMemcpyToSymbol(g_wait_timeout_ns, &ns, sizeof(ns));
 }
 
+// How a kernel gets its epoch.  Normally by value.  A sequence captured into a CUDA graph is
+// replayed many times with the same arguments, so there the value comes from a device word that
+// the first node of the graph increments (tzb_set_epoch_source / tzb_epoch_advance).
+struct EpochArg {
+  uint64_t value;
+  const uint64_t *dev;
+  __device__ __forceinline__ uint64_t get() const { return dev ? *dev : value; }
+};
+// defined in spmv_kernels.cu: the device word the launch wrappers of THIS THREAD hand to kernels, or null
+extern thread_local const uint64_t *g_epochSource;
+inline EpochArg ep(uint64_t value) { return EpochArg{value, g_epochSource}; }
+
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));

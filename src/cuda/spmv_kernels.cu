@@ -18,6 +18,7 @@
 namespace tzb {
 
 std::atomic<uint64_t> g_launches{0};
+thread_local const uint64_t *g_epochSource = nullptr;
 
 // the flag-wait watchdog of this translation unit's kernels (see device_sync.cuh)
 cudaError_t set_wait_timeout_spmv(unsigned long long ns) { return set_wait_timeout_ns_this_tu(ns); }
@@ -84,7 +85,8 @@ template <typename T, int U, bool WAIT>
 __global__ void __launch_bounds__(kThreads)
 spmv_csr_stream_kernel(int rows, const int *__restrict__ rowPtr, const int *__restrict__ colInd,
                        const T *__restrict__ val, const T *x, T *__restrict__ y, int accumulate,
-                       const uint64_t *flags, int nFlags, uint64_t epoch) {
+                       const uint64_t *flags, int nFlags, EpochArg epochArg) {
+  const uint64_t epoch = epochArg.get();
   __shared__ T prod[kThreads * U];
   __shared__ int range[2];
   if (WAIT) {
@@ -107,7 +109,8 @@ template <typename T, int TPR, bool WAIT>
 __global__ void __launch_bounds__(kThreads)
 spmv_csr_kernel(int rows, const int *__restrict__ rowPtr, const int *__restrict__ colInd,
                 const T *__restrict__ val, const T *x, T *__restrict__ y, int accumulate,
-                const uint64_t *flags, int nFlags, uint64_t epoch) {
+                const uint64_t *flags, int nFlags, EpochArg epochArg) {
+  const uint64_t epoch = epochArg.get();
   if (WAIT) {
     if (int(threadIdx.x) < nFlags) wait_flag_geq(flags + threadIdx.x, epoch);
     __syncthreads();
@@ -158,7 +161,7 @@ cudaError_t launch_spmv(int rows, const int *rowPtr, const int *colInd, const T 
     static const int perSm = blocks_per_sm(spmv_csr_stream_kernel<T, N, WAIT>);                    \
     const int blocks = std::min(tiles, sm_count() * perSm);                                       \
     spmv_csr_stream_kernel<T, N, WAIT><<<blocks, kThreads, 0, stream>>>(                           \
-        rows, rowPtr, colInd, val, x, y, accumulate, flags, nFlags, epoch);                       \
+        rows, rowPtr, colInd, val, x, y, accumulate, flags, nFlags, ep(epoch));                       \
     break;                                                                                         \
   }
     switch (stream_unroll(nnzPerRowHint)) {
@@ -179,7 +182,7 @@ cudaError_t launch_spmv(int rows, const int *rowPtr, const int *colInd, const T 
 #define TZB_CASE(N)                                                                                \
   case N:                                                                                          \
     spmv_csr_kernel<T, N, WAIT><<<blocks, kThreads, 0, stream>>>(rows, rowPtr, colInd, val, x, y,  \
-                                                                 accumulate, flags, nFlags, epoch); \
+                                                                 accumulate, flags, nFlags, ep(epoch)); \
     break
   switch (tpr) {
   default:
@@ -209,7 +212,8 @@ vector_add_kernel(int n, const T *__restrict__ a, T *__restrict__ y) {
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
 gather_put_kernel(TzbGatherPutArgs a, const int *__restrict__ idx, const T *__restrict__ src,
-                  uint64_t epoch, unsigned *counter) {
+                  EpochArg epochArg, unsigned *counter) {
+  const uint64_t epoch = epochArg.get();
   const int n = a.displ[a.nPeers];
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     int p = 0;
@@ -238,7 +242,8 @@ spmv_fused_all_kernel(TzbGatherPutArgs a, const int *__restrict__ sendIdx, int r
                       const T *__restrict__ lVal, const int *__restrict__ rRowPtr,
                       const int *__restrict__ rColInd, const T *__restrict__ rVal,
                       const T *__restrict__ x, const T *rx, T *__restrict__ y,
-                      const uint64_t *flags, int nFlags, uint64_t epoch, unsigned *counter) {
+                      const uint64_t *flags, int nFlags, EpochArg epochArg, unsigned *counter) {
+  const uint64_t epoch = epochArg.get();
   __shared__ T prod[kThreads * U];
   __shared__ int range[2];
   // (1) put
@@ -287,8 +292,9 @@ __device__ __forceinline__ void multimem_st(float *p, float v) {
 }
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
-multicast_put_kernel(int n, const T *__restrict__ src, T *mcDst, uint64_t *mcFlag, uint64_t epoch,
+multicast_put_kernel(int n, const T *__restrict__ src, T *mcDst, uint64_t *mcFlag, EpochArg epochArg,
                      unsigned *counter) {
+  const uint64_t epoch = epochArg.get();
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
     multimem_st(mcDst + i, __ldg(src + i));
   if (block_arrive_last(counter, gridDim.x)) {
@@ -296,6 +302,9 @@ multicast_put_kernel(int n, const T *__restrict__ src, T *mcDst, uint64_t *mcFla
       asm volatile("multimem.st.release.sys.global.u64 [%0], %1;" ::"l"(mcFlag), "l"(epoch) : "memory");
   }
 }
+
+__global__ void epoch_advance_kernel(uint64_t *word) { *word += 1; }
+__global__ void epoch_set_kernel(uint64_t *word, uint64_t value) { *word = value; }
 
 int grid_for(int n) {
   int blocks = (n + kThreads - 1) / kThreads;
@@ -309,7 +318,7 @@ cudaError_t launch_gather_put(const TzbGatherPutArgs *args, const int *idx, cons
   if (!args || args->nPeers < 0 || args->nPeers > 16) return cudaErrorInvalidValue;
   const int n = args->displ[args->nPeers];
   ++g_launches;
-  gather_put_kernel<T><<<grid_for(n), kThreads, 0, stream>>>(*args, idx, src, epoch, counter);
+  gather_put_kernel<T><<<grid_for(n), kThreads, 0, stream>>>(*args, idx, src, ep(epoch), counter);
   return cudaGetLastError();
 }
 
@@ -356,8 +365,9 @@ cudaError_t launch_spmv_fused_all(const TzbGatherPutArgs *a, const int *sendIdx,
   const int tiles = std::max(1, (rows + kThreads - 1) / kThreads);
   const int nSend = a->displ[a->nPeers];
   TzbGatherPutArgs args = *a;
+  EpochArg epochArg = ep(epoch);
   void *params[] = {&args,    &sendIdx, &rows, &lRowPtr, &lColInd, &lVal,  &rRowPtr, &rColInd,
-                    &rVal,    &x,       &rx,   &y,       &flags,   &nFlags, &epoch,   &counter};
+                    &rVal,    &x,       &rx,   &y,       &flags,   &nFlags, &epochArg, &counter};
   ++g_launches;
 #define TZB_CASE(N)                                                                                \
   case N: {                                                                                        \
@@ -407,7 +417,8 @@ __global__ void __launch_bounds__(kThreads)
 spmv_csr_pull_kernel(int rows, const int *__restrict__ rowPtr, const int *__restrict__ colInd,
                      const T *__restrict__ val, const T *const *__restrict__ xPtr,
                      T *__restrict__ y, int accumulate, const uint64_t *ready, int nReady,
-                     TzbFlagList acks, uint64_t epoch, unsigned *counter) {
+                     TzbFlagList acks, EpochArg epochArg, unsigned *counter) {
+  const uint64_t epoch = epochArg.get();
   if (int(threadIdx.x) < nReady) wait_flag_geq(ready + threadIdx.x, epoch);
   __syncthreads();
   const int lane = threadIdx.x % TPR;
@@ -449,7 +460,7 @@ cudaError_t launch_spmv_pull(int rows, const int *rowPtr, const int *colInd, con
 #define TZB_CASE(N)                                                                                \
   case N:                                                                                          \
     spmv_csr_pull_kernel<T, N><<<blocks, kThreads, 0, stream>>>(                                   \
-        rows, rowPtr, colInd, val, xPtr, y, accumulate, ready, nReady, *acks, epoch, counter);    \
+        rows, rowPtr, colInd, val, xPtr, y, accumulate, ready, nReady, *acks, ep(epoch), counter);    \
     break
   switch (tpr) {
     TZB_CASE(2);
@@ -579,7 +590,7 @@ int tzb_multicast_put_f64(int n, const double *src, double *mcDst, uint64_t *mcF
   if (n < 0 || !mcFlag) return cudaErrorInvalidValue;
   ++g_launches;
   multicast_put_kernel<double><<<grid_for(std::max(n, 1)), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-      n, src, mcDst, mcFlag, epoch, counter);
+      n, src, mcDst, mcFlag, ep(epoch), counter);
   return cudaGetLastError();
 }
 int tzb_multicast_put_f32(int n, const float *src, float *mcDst, uint64_t *mcFlag, uint64_t epoch,
@@ -587,7 +598,21 @@ int tzb_multicast_put_f32(int n, const float *src, float *mcDst, uint64_t *mcFla
   if (n < 0 || !mcFlag) return cudaErrorInvalidValue;
   ++g_launches;
   multicast_put_kernel<float><<<grid_for(std::max(n, 1)), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-      n, src, mcDst, mcFlag, epoch, counter);
+      n, src, mcDst, mcFlag, ep(epoch), counter);
+  return cudaGetLastError();
+}
+
+void tzb_set_epoch_source(const uint64_t *devWord) { g_epochSource = devWord; }
+
+int tzb_epoch_advance(uint64_t *devWord, void *stream) {
+  if (!devWord) return cudaErrorInvalidValue;
+  epoch_advance_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(devWord);
+  return cudaGetLastError();
+}
+
+int tzb_epoch_set(uint64_t *devWord, uint64_t value, void *stream) {
+  if (!devWord) return cudaErrorInvalidValue;
+  epoch_set_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(devWord, value);
   return cudaGetLastError();
 }
 

@@ -66,8 +66,31 @@ def main():
                     if not all_ok(s.check()):
                         failures.append(f"spmv {dtype} n={n} {style}")
                         break
-    # Ialltoallv between real GPUs: rank r sends the 16 values 1000 r + p + (0..15) to every peer p
+    # the fused schedules replayed as CUDA graphs across ranks (device-side epoch)
     from tenzing_b200 import _C
+    for wl, style in ((HaloExchange(comm=comm, nX=24, nY=10, nZ=12, nQ=2, nGhost=3), "fused_mixed"),
+                      (DistributedSpMV(comm=comm, n=40_000, nnz_per_row=10), "fused_all"),
+                      (DistributedSpMV(comm=comm, n=30_011, bw=30_011, nnz_per_row=10), "fused")):
+        seq = common.fixed_schedule(wl.graph(style), wl.platform)
+        wl.platform.provision_events(seq)
+        wl.fill()
+        comm.barrier()
+        wl.run(seq)
+        wl.sync()
+        comm.barrier()
+        replay = _C.GraphReplay(seq, wl.platform)
+        for _ in range(2):
+            wl.fill()
+            comm.barrier()
+            for _ in range(3):
+                replay.launch()
+            wl.sync()
+            comm.barrier()
+            if not all_ok(wl.check()):
+                failures.append(f"graph replay {style}")
+                break
+        del replay
+    # Ialltoallv between real GPUs: rank r sends the 16 values 1000 r + p + (0..15) to every peer p
     from tenzing_b200.utils.tensor import device_tensor
     heap = _C.SymmetricHeap(comm, 1 << 20)
     k = 16
