@@ -23,7 +23,12 @@ namespace tenzing {
 
 // the two private streams that play the MPI progress engine; share one per program
 class P2PTransport {
-  cudaStream_t send_ = nullptr, recv_ = nullptr;
+public:
+  static constexpr int kSendStreams = 4; // as a CUDA-aware MPI pipelines its peer copies
+private:
+  cudaStream_t send_[kSendStreams] = {nullptr, nullptr, nullptr, nullptr};
+  cudaStream_t recv_ = nullptr;
+  int next_ = 0;
   bool null_;
 
 public:
@@ -31,7 +36,13 @@ public:
   ~P2PTransport();
   P2PTransport(const P2PTransport &) = delete;
   P2PTransport &operator=(const P2PTransport &) = delete;
-  cudaStream_t send_stream() const { return send_; }
+  // the stream for the next message (copy and flag publish of one message share a stream,
+  // consecutive messages rotate over kSendStreams copy streams)
+  cudaStream_t next_send_stream() {
+    cudaStream_t s = send_[next_];
+    next_ = (next_ + 1) % kSendStreams;
+    return s;
+  }
   cudaStream_t recv_stream() const { return recv_; }
   bool is_null() const { return null_; }
 };

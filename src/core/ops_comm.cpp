@@ -6,12 +6,13 @@ namespace tenzing {
 
 P2PTransport::P2PTransport(bool nullDevice) : null_(nullDevice) {
   if (null_) return;
-  CUDA_RUNTIME(cudaStreamCreateWithFlags(&send_, cudaStreamNonBlocking));
+  for (auto &s : send_) CUDA_RUNTIME(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
   CUDA_RUNTIME(cudaStreamCreateWithFlags(&recv_, cudaStreamNonBlocking));
 }
 
 P2PTransport::~P2PTransport() {
-  if (send_) cudaStreamDestroy(send_);
+  for (auto s : send_)
+    if (s) cudaStreamDestroy(s);
   if (recv_) cudaStreamDestroy(recv_);
 }
 
@@ -36,12 +37,13 @@ void Request::wait() {
   kind = Kind::None;
 }
 
-static void mark_sent(Request &r, const std::shared_ptr<P2PTransport> &tr, uint64_t epoch) {
+static void mark_sent(Request &r, const std::shared_ptr<P2PTransport> &tr, uint64_t epoch,
+                      cudaStream_t stream) {
   r.kind = Request::Kind::Send;
   r.transport = tr;
   r.epoch = epoch;
   if (!r.sent) CUDA_RUNTIME(cudaEventCreateWithFlags(&r.sent, cudaEventDisableTiming));
-  CUDA_RUNTIME(cudaEventRecord(r.sent, tr->send_stream()));
+  CUDA_RUNTIME(cudaEventRecord(r.sent, stream));
 }
 
 void Isend::run(Platform &plat) {
@@ -56,14 +58,14 @@ void Isend::run(Platform &plat) {
     return;
   }
   if (tr_->is_null() || plat.is_null()) return;
+  cudaStream_t st = tr_->next_send_stream();
   if (args_.bytes)
-    CUDA_RUNTIME(cudaMemcpyAsync(args_.peerBuf, args_.buf, args_.bytes, cudaMemcpyDeviceToDevice,
-                                 tr_->send_stream()));
+    CUDA_RUNTIME(cudaMemcpyAsync(args_.peerBuf, args_.buf, args_.bytes, cudaMemcpyDeviceToDevice, st));
   TzbFlagList l;
   l.n = 1;
   l.flag[0] = args_.peerFlag;
-  CUDA_RUNTIME(cudaError_t(tzb_flags_signal(&l, plat.epoch(), tr_->send_stream())));
-  if (args_.request) mark_sent(*args_.request, tr_, plat.epoch());
+  CUDA_RUNTIME(cudaError_t(tzb_flags_signal(&l, plat.epoch(), st)));
+  if (args_.request) mark_sent(*args_.request, tr_, plat.epoch(), st);
 }
 
 void Irecv::run(Platform &plat) {
@@ -108,20 +110,22 @@ void Ialltoallv::run(Platform &plat) {
     return;
   }
   if (tr_->is_null() || plat.is_null()) return;
+  // one collective = one stream: its single request completes when the last copy and flag are out
+  cudaStream_t st = tr_->next_send_stream();
   for (size_t p = 0; p < n; ++p) {
     if (args_.sendBytes[p])
       CUDA_RUNTIME(cudaMemcpyAsync(args_.peerBufs[p],
                                    static_cast<const char *>(args_.sendbuf) + args_.sendOffsets[p],
-                                   args_.sendBytes[p], cudaMemcpyDeviceToDevice, tr_->send_stream()));
+                                   args_.sendBytes[p], cudaMemcpyDeviceToDevice, st));
   }
   for (size_t p0 = 0; p0 < n; p0 += 32) {
     TzbFlagList l;
     l.n = 0;
     for (size_t p = p0; p < n && p < p0 + 32; ++p)
       if (args_.peerFlags[p]) l.flag[l.n++] = args_.peerFlags[p];
-    CUDA_RUNTIME(cudaError_t(tzb_flags_signal(&l, plat.epoch(), tr_->send_stream())));
+    CUDA_RUNTIME(cudaError_t(tzb_flags_signal(&l, plat.epoch(), st)));
   }
-  if (args_.request) mark_sent(*args_.request, tr_, plat.epoch());
+  if (args_.request) mark_sent(*args_.request, tr_, plat.epoch(), st);
 }
 
 } // namespace tenzing

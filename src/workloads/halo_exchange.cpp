@@ -314,16 +314,25 @@ TzbBox make_box(const Domain &dom, const void *src, Side srcSide, const Dim3<int
 // shared by the host-driven reference-structure ops: the two internal streams
 // that play the role of the MPI progress engine
 struct RefTransport {
-  cudaStream_t send = nullptr, recv = nullptr;
+  static constexpr int kSendStreams = 4; // peer copies are pipelined over several copy streams
+  cudaStream_t send[kSendStreams] = {nullptr, nullptr, nullptr, nullptr};
+  cudaStream_t recv = nullptr;
+  int next = 0;
   bool null = false;
   explicit RefTransport(bool nullDevice) : null(nullDevice) {
     if (null) return;
-    CUDA_RUNTIME(cudaStreamCreateWithFlags(&send, cudaStreamNonBlocking));
+    for (auto &s : send) CUDA_RUNTIME(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
     CUDA_RUNTIME(cudaStreamCreateWithFlags(&recv, cudaStreamNonBlocking));
   }
   ~RefTransport() {
-    if (send) cudaStreamDestroy(send);
+    for (auto s : send)
+      if (s) cudaStreamDestroy(s);
     if (recv) cudaStreamDestroy(recv);
+  }
+  cudaStream_t next_send_stream() {
+    cudaStream_t s = send[next];
+    next = (next + 1) % kSendStreams;
+    return s;
   }
 };
 
@@ -351,13 +360,14 @@ public:
       return;
     }
     if (tr_->null || plat.is_null()) return;
+    cudaStream_t st = tr_->next_send_stream();
     CUDA_RUNTIME(cudaMemcpyAsync(dom_->recv_staging(peer, int(plat.epoch() & 1), side),
                                  dom_->send_staging(dom_->rank(), d_), bytes,
-                                 cudaMemcpyDeviceToDevice, tr_->send));
+                                 cudaMemcpyDeviceToDevice, st));
     TzbFlagList l;
     l.n = 1;
     l.flag[0] = dom_->flag(peer, Style::Reference, side);
-    CUDA_RUNTIME(cudaError_t(tzb_flags_signal(&l, plat.epoch(), tr_->send)));
+    CUDA_RUNTIME(cudaError_t(tzb_flags_signal(&l, plat.epoch(), st)));
   }
 };
 
@@ -396,7 +406,7 @@ public:
   CLONE_DEF(RefWaitSends)
   void run(Platform &plat) override {
     if (tr_->null || plat.is_null()) return;
-    CUDA_RUNTIME(cudaStreamSynchronize(tr_->send));
+    for (auto s : tr_->send) CUDA_RUNTIME(cudaStreamSynchronize(s));
   }
 };
 

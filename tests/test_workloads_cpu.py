@@ -214,3 +214,19 @@ def test_every_workload_graph_and_rewrite_keeps_the_graph_invariants():
                 st = st.apply(rng.choice(ds))
                 assert st.graph().validate() == ""
             assert not st.get_decisions(plat), "walk did not reach a terminal state"
+
+
+def test_which_sequences_can_be_replayed_as_a_cuda_graph():
+    """GraphReplay::supported: device-only schedules (kernels, event records, stream waits, the
+    trailing host sync in front of Finish) yes; anything that runs an op on the host no"""
+    from tenzing_b200 import _C
+    from tenzing_b200.models import DistributedSpMV, HaloExchange, common
+    h = HaloExchange(nX=8, nQ=1, nGhost=2, host=True)
+    for style in ("fused_all", "fused_staged", "fused_mixed", "staged", "direct", "fused_pull"):
+        ok, why = _C.GraphReplay.supported(common.fixed_schedule(h.graph(style), h.platform))
+        assert ok, (style, why)
+    ok, why = _C.GraphReplay.supported(common.fixed_schedule(h.graph("reference"), h.platform))
+    assert not ok and "host" in why
+    s = DistributedSpMV(n=2000, host=True)
+    assert _C.GraphReplay.supported(common.fixed_schedule(s.graph("fused_all"), s.platform))[0]
+    assert not _C.GraphReplay.supported(common.fixed_schedule(s.graph("reference"), s.platform))[0]
