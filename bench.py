@@ -188,7 +188,7 @@ def main():
     ap.add_argument("--search-iters", type=int, default=30)
     ap.add_argument("--no-search", action="store_true", help="use a fixed fused schedule as is")
     ap.add_argument("--search-budget", type=float, default=30.0, help="wall-clock seconds for the halo search")
-    ap.add_argument("--skip", default="", help="comma separated sub-records to skip: halo,spmv_1m,spmv_random,sweep")
+    ap.add_argument("--skip", default="", help="comma separated sub-records to skip: halo,spmv_1m,spmv_random,sweep,oracle")
     ap.add_argument("--ref-seconds", type=float, default=150.0,
                     help="reference arm: wall-clock seconds its DFS driver gets before SIGINT")
     ap.add_argument("--ref-grace", type=float, default=25.0,
@@ -564,6 +564,48 @@ def main():
                               "roofline_frac_of_measured": round(roof_r * 1e6 / us_r, 4),
                               "gpu_launches": int(launches_r)}
         del replay_r, rnd
+
+    # ---------------- BASELINE config 5: message sizes, every rank to every other rank ----------------
+    if "sweep" not in skip and not host and world > 1:
+        from tenzing_b200.utils.sweep import all_pairs_sweep
+        try:
+            plat_sw = common.make_platform(comm, 1)
+            rows = all_pairs_sweep(comm, plat_sw, [64 << 10, 16 << 20, 256 << 20], max(5, args.steps // 4), flush,
+                                   max_over_ranks)
+            out["msg_sweep"] = {"pattern": f"every rank sends to each of its {world - 1} peers at once and "
+                                           "waits for theirs", "rows": rows}
+            ok_all &= all(r["correct"] for r in rows)
+            del plat_sw
+        except Exception as e:  # noqa: BLE001 - a side record must not take the headline down
+            out["msg_sweep"] = {"error": str(e)[:200]}
+
+    # ---------------- every implementation style against the oracles, on these ranks ----------------
+    if "oracle" not in skip and not args.no_search:
+        from tenzing_b200.models.halo import STYLES as HALO_ALL
+        from tenzing_b200.models.spmv import STYLES as SPMV_ALL, EXPERIMENTAL_STYLES
+        passed = {"halo": [], "spmv": []}
+        small_h = HaloExchange(comm=comm, nX=24, nY=12, nZ=16, nQ=2, nGhost=3, host=host)
+        small_s = DistributedSpMV(comm=comm, n=40_000, nnz_per_row=10, host=host)
+        for wl, styles, key in ((small_h, HALO_ALL, "halo"), (small_s, SPMV_ALL + EXPERIMENTAL_STYLES, "spmv")):
+            if host:
+                wl.platform.set_host_execution(True)
+            for style in styles:
+                seq = common.fixed_schedule(wl.graph(style), wl.platform)
+                wl.platform.provision_events(seq)
+                wl.fill()
+                comm.barrier()
+                wl.run(seq, 2)          # both staging parities
+                wl.sync()
+                comm.barrier()
+                good = torch.tensor([1.0 if wl.check() else 0.0], device=dev)
+                if world > 1:
+                    torch.distributed.all_reduce(good, op=torch.distributed.ReduceOp.MIN)
+                if good.item() > 0.5:
+                    passed[key].append(style)
+                else:
+                    ok_all = False
+        out["oracle_pass"] = {**passed, "of": {"halo": len(HALO_ALL), "spmv": len(SPMV_ALL + EXPERIMENTAL_STYLES)}}
+        del small_h, small_s
 
     ok = torch.tensor([1.0 if ok_all else 0.0], device=dev)
     if world > 1:
