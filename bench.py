@@ -372,10 +372,18 @@ def main():
         """through the public API, per step: H2D of this rank's x block from pinned host memory,
         the schedule, D2H of this rank's y block into pinned host memory; host wall clock"""
         rows = wl.x.numel()
-        xh = torch.rand(rows, dtype=wl.dtype)
-        yh = torch.empty(rows, dtype=wl.dtype)
-        if not host:
-            xh, yh = xh.pin_memory(), yh.pin_memory()
+        if host:
+            xh = torch.rand(rows, dtype=wl.dtype)
+            yh = torch.empty(rows, dtype=wl.dtype)
+        else:
+            # staging buffers from the framework's own pinned pool: page-locked host memory on the
+            # NUMA node next to this rank's GPU (reference counterpart: src/numa.cpp, dead code there)
+            from tenzing_b200.utils.tensor import host_tensor
+            nbytes = max(rows, 1) * wl.x.element_size()
+            pool = _C.PinnedPool(torch.cuda.current_device())
+            xh = host_tensor(pool.get(nbytes), (rows,), wl.dtype, owner=pool)
+            yh = host_tensor(pool.get(nbytes), (rows,), wl.dtype, owner=pool)
+            xh.copy_(torch.rand(rows, dtype=wl.dtype))
         wl.platform.provision_events(seq)
         t = []
         for i in range(warmup + steps):

@@ -71,28 +71,6 @@ struct PlanHeader {
 // (thick rows: one warp per row; thin rows: lanes run over (row, element)
 // pairs so the dense side of a pack/unpack stays fully coalesced).
 
-// one work item: rows [i1, i1+c1) x [i2, i2+c2) of plane i3
-// thin-row load with an L2 prefetch-size qualifier (HINT = 64, 128 or 256; 0 = plain load).
-// Experiment knob for the x-faces: ncu shows a whole 128-byte line fetched per 24-byte piece.
-template <int HINT, typename T> __device__ __forceinline__ T load_thin(const T *p) {
-  if (HINT == 0) return *p;
-  T v;
-  if (sizeof(T) == 8) {
-    unsigned long long u;
-    if (HINT == 64) asm volatile("ld.global.L2::64B.u64 %0, [%1];" : "=l"(u) : "l"(p));
-    else if (HINT == 128) asm volatile("ld.global.L2::128B.u64 %0, [%1];" : "=l"(u) : "l"(p));
-    else asm volatile("ld.global.L2::256B.u64 %0, [%1];" : "=l"(u) : "l"(p));
-    memcpy(&v, &u, sizeof(v));
-  } else {
-    unsigned u;
-    if (HINT == 64) asm volatile("ld.global.L2::64B.u32 %0, [%1];" : "=r"(u) : "l"(p));
-    else if (HINT == 128) asm volatile("ld.global.L2::128B.u32 %0, [%1];" : "=r"(u) : "l"(p));
-    else asm volatile("ld.global.L2::256B.u32 %0, [%1];" : "=r"(u) : "l"(p));
-    memcpy(&v, &u, sizeof(v));
-  }
-  return v;
-}
-
 // ---------------------------------------------------------------------------------------
 // Thin rows, one row per thread ("sector path", 8-byte elements, run <= 4).
 //
@@ -224,7 +202,8 @@ __device__ __forceinline__ void thin_item(const BoxDesc &b, const WorkItem &w, u
 // 256-bit accesses on thick rows (TZB_WIDE256=1): off by default until measured over NVLink
 __device__ int kWide256 = 0;
 
-template <typename T, bool VEC, int kThick, int kThin, int HINT = 0>
+// one work item: rows [i1, i1+c1) x [i2, i2+c2) of plane i3
+template <typename T, bool VEC, int kThick, int kThin>
 __device__ __forceinline__ void copy_item(const BoxDesc &b, const WorkItem &w, int lane, int warp) {
   const T *src = reinterpret_cast<const T *>(b.src) + int64_t(w.i3) * b.s3;
   T *dst = reinterpret_cast<T *>(b.dst) + int64_t(w.i3) * b.d3;
@@ -310,7 +289,7 @@ __device__ __forceinline__ void copy_item(const BoxDesc &b, const WorkItem &w, i
       for (int u = 0; u < kThin; ++u) {
         int64_t so;
         offsets(f + kThreads * u, so, dof[u]);
-        v[u] = load_thin<HINT>(src + so);
+        v[u] = src[so];
       }
 #pragma unroll
       for (int u = 0; u < kThin; ++u) dst[dof[u]] = v[u];
@@ -318,7 +297,7 @@ __device__ __forceinline__ void copy_item(const BoxDesc &b, const WorkItem &w, i
     for (; f < total; f += kThreads) {
       int64_t so, dof;
       offsets(f, so, dof);
-      dst[dof] = load_thin<HINT>(src + so);
+      dst[dof] = src[so];
     }
   }
 }
@@ -345,26 +324,6 @@ box_copy_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restrict__ 
   }
   if (anySignal) {
     // one system-scope fence per block; the last block to finish publishes every flag
-    if (block_arrive_last(counter, gridDim.x)) {
-      for (int bx = threadIdx.x; bx < nBoxes; bx += kThreads)
-        if (boxes[bx].signal) st_release_sys(boxes[bx].signal, epoch);
-    }
-  }
-}
-
-// EXPERIMENTAL (opt-in: TZB_THIN_HINT=64|128|256): box_copy_kernel whose thin-row loads carry an
-// L2 prefetch-size qualifier.  Separate instantiations, so the measured kernels are untouched.
-template <typename T, int HINT>
-__global__ void __launch_bounds__(kThreads, kBlocksPerSM)
-box_copy_hint_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restrict__ items, int nItems,
-                     int nBoxes, int anySignal, EpochArg epochArg, unsigned *counter) {
-  const uint64_t epoch = epochArg.get();
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int it = blockIdx.x; it < nItems; it += gridDim.x) {
-    const WorkItem w = items[it];
-    copy_item<T, true, 8, kThin, HINT>(boxes[w.box], w, lane, warp);
-  }
-  if (anySignal) {
     if (block_arrive_last(counter, gridDim.x)) {
       for (int bx = threadIdx.x; bx < nBoxes; bx += kThreads)
         if (boxes[bx].signal) st_release_sys(boxes[bx].signal, epoch);
@@ -795,15 +754,6 @@ int tzb_boxcopy_plan_ordered(const TzbBox *boxes, int nBoxes, int elemSize, TzbB
   return boxcopy_plan_impl(boxes, nBoxes, elemSize, info, hostImage, true);
 }
 
-static int thin_hint() {
-  static const int h = [] {
-    const char *e = std::getenv("TZB_THIN_HINT");
-    const int v = e ? std::atoi(e) : 0;
-    return (v == 64 || v == 128 || v == 256) ? v : 0;
-  }();
-  return h;
-}
-
 static bool bulk_enabled() {
   static const bool on = [] {
     const char *e = std::getenv("TZB_BULK");
@@ -898,21 +848,6 @@ int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t
     const int blocks = grid(sm_count() * 7);
     box_bulk_kernel<<<blocks, 32, 0, s>>>(boxes, items, info->nItems, info->nBoxes, info->elemSize,
                                           anySignal, ep(epoch), ctr);
-  } else if (thin_hint() && info->elemSize == 8) {
-    const int blocks = grid(sm_count() * kBlocksPerSM);
-    switch (thin_hint()) {
-    case 64:
-      box_copy_hint_kernel<double, 64><<<blocks, kThreads, 0, s>>>(boxes, items, info->nItems, info->nBoxes,
-                                                                  anySignal, ep(epoch), ctr);
-      break;
-    case 128:
-      box_copy_hint_kernel<double, 128><<<blocks, kThreads, 0, s>>>(boxes, items, info->nItems, info->nBoxes,
-                                                                   anySignal, ep(epoch), ctr);
-      break;
-    default:
-      box_copy_hint_kernel<double, 256><<<blocks, kThreads, 0, s>>>(boxes, items, info->nItems, info->nBoxes,
-                                                                   anySignal, ep(epoch), ctr);
-    }
   } else {
     const int blocks = grid(sm_count() * kBlocksPerSM);
     if (info->elemSize == 8 && vec)

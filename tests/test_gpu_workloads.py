@@ -176,8 +176,8 @@ def test_bulk_copy_path_matches_the_oracle():
         "        seq = common.fixed_schedule(h.graph(style), h.platform)\n"
         "        h.fill(); h.run(seq, 3); assert h.check(), (nx, style)\n"
         "print('BULK_OK')\n")
-    # same check for the other opt-in variant: thin-row loads with an L2 prefetch-size qualifier
-    for env in (dict(os.environ, TZB_BULK="1"), dict(os.environ, TZB_THIN_HINT="64")):
+    # same check for the other opt-in variants: 256-bit accesses on thick rows, sector path everywhere
+    for env in (dict(os.environ, TZB_BULK="1"), dict(os.environ, TZB_WIDE256="1"), dict(os.environ, TZB_THIN_SECTOR="2")):
         p = subprocess.run(["timeout", "120", sys.executable, "-c", code], capture_output=True, text=True,
                            env=env, cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
         assert p.returncode == 0 and "BULK_OK" in p.stdout, (p.stdout + p.stderr)[-3000:]
