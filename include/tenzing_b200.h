@@ -69,7 +69,7 @@ int tzb_spmv_csr_wait_f32(int rows, const int *rowPtr, const int *colInd, const 
                           const float *x, float *y, int accumulate, const uint64_t *flags,
                           int nFlags, uint64_t epoch, void *stream);
 
-/* Pull form (EXPERIMENTAL, not yet validated on hardware): the gather of the remote x entries
+/* Pull form: the gather of the remote x entries
  * happens inside the product.  xPtr[c] is the address of remote column c in its owner's x (a
  * peer pointer); every block waits until the nReady local `ready` flags reached the epoch (all
  * owners declared their x final), then y (+)= A_remote x; the last block publishes the epoch to

@@ -44,17 +44,18 @@ template <typename T, bool COHERENT> __device__ __forceinline__ T load_x(const T
 }
 
 // products of tile rows [r0, r0 + kThreads) into `acc` of the thread that owns row r0 + tid
+// tileRows (<= kThreads) rows per tile: small problems use small tiles so that every SM has one
 template <typename T, int U, bool COHERENT>
-__device__ __forceinline__ T tile_product(int r0, int rows, const int *__restrict__ rowPtr,
+__device__ __forceinline__ T tile_product(int r0, int rows, int tileRows, const int *__restrict__ rowPtr,
                                           const int *__restrict__ colInd, const T *__restrict__ val,
                                           const T *x, T *prod /* kThreads * U */, int *range /* 2 */) {
   const int t = threadIdx.x;
   const int row = r0 + t;
   int b = 0, e = 0;
-  if (row < rows) b = __ldg(rowPtr + row), e = __ldg(rowPtr + row + 1);
+  if (t < tileRows && row < rows) b = __ldg(rowPtr + row), e = __ldg(rowPtr + row + 1);
   __syncthreads(); // the previous tile's readers of `range` and `prod` are done
   if (t == 0) range[0] = b;
-  if (row == min(r0 + kThreads, rows) - 1) range[1] = e;
+  if (t < tileRows && row == min(r0 + tileRows, rows) - 1) range[1] = e;
   __syncthreads();
   const int B = range[0], E = range[1];
   constexpr int CH = kThreads * U;
@@ -83,7 +84,7 @@ __device__ __forceinline__ T tile_product(int r0, int rows, const int *__restric
 
 template <typename T, int U, bool WAIT>
 __global__ void __launch_bounds__(kThreads)
-spmv_csr_stream_kernel(int rows, const int *__restrict__ rowPtr, const int *__restrict__ colInd,
+spmv_csr_stream_kernel(int rows, int tileRows, const int *__restrict__ rowPtr, const int *__restrict__ colInd,
                        const T *__restrict__ val, const T *x, T *__restrict__ y, int accumulate,
                        const uint64_t *flags, int nFlags, EpochArg epochArg) {
   const uint64_t epoch = epochArg.get();
@@ -94,12 +95,12 @@ spmv_csr_stream_kernel(int rows, const int *__restrict__ rowPtr, const int *__re
     if (int(threadIdx.x) < nFlags) wait_flag_geq(flags + threadIdx.x, epoch);
     __syncthreads();
   }
-  const int tiles = (rows + kThreads - 1) / kThreads;
+  const int tiles = (rows + tileRows - 1) / tileRows;
   for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
-    const int r0 = tile * kThreads;
-    const T acc = tile_product<T, U, WAIT>(r0, rows, rowPtr, colInd, val, x, prod, range);
+    const int r0 = tile * tileRows;
+    const T acc = tile_product<T, U, WAIT>(r0, rows, tileRows, rowPtr, colInd, val, x, prod, range);
     const int row = r0 + threadIdx.x;
-    if (row < rows) y[row] = accumulate ? y[row] + acc : acc;
+    if (int(threadIdx.x) < tileRows && row < rows) y[row] = accumulate ? y[row] + acc : acc;
   }
 }
 
@@ -143,6 +144,14 @@ template <typename K> int blocks_per_sm(K kernel) {
   return n;
 }
 
+// rows per tile: 256 where that still gives every SM two tiles, else 128 or 64 (a tile is one
+// dependent chain rowPtr -> (val, colInd) -> x -> sum, so a small problem wants many small tiles)
+inline int stream_tile_rows(int rows) {
+  const long want = 2L * sm_count();
+  if (rows >= want * kThreads) return kThreads;
+  if (rows >= want * (kThreads / 2)) return kThreads / 2;
+  return kThreads / 4;
+}
 // pairs per thread in flight for a given density: the tile's non-zeros should fit one chunk
 inline int stream_unroll(int nnzPerRowHint) { return nnzPerRowHint <= 4 ? 4 : (nnzPerRowHint <= 8 ? 8 : 12); }
 constexpr int kStreamMaxNnzPerRow = 48;
@@ -155,13 +164,14 @@ cudaError_t launch_spmv(int rows, const int *rowPtr, const int *colInd, const T 
   if (WAIT && nFlags > kThreads) return cudaErrorInvalidValue;
   ++g_launches;
   if (nnzPerRowHint <= kStreamMaxNnzPerRow) {
-    const int tiles = (rows + kThreads - 1) / kThreads;
+    const int tileRows = stream_tile_rows(rows);
+    const int tiles = (rows + tileRows - 1) / tileRows;
 #define TZB_CASE(N)                                                                                \
   case N: {                                                                                        \
     static const int perSm = blocks_per_sm(spmv_csr_stream_kernel<T, N, WAIT>);                    \
     const int blocks = std::min(tiles, sm_count() * perSm);                                       \
     spmv_csr_stream_kernel<T, N, WAIT><<<blocks, kThreads, 0, stream>>>(                           \
-        rows, rowPtr, colInd, val, x, y, accumulate, flags, nFlags, ep(epoch));                       \
+        rows, tileRows, rowPtr, colInd, val, x, y, accumulate, flags, nFlags, ep(epoch));             \
     break;                                                                                         \
   }
     switch (stream_unroll(nnzPerRowHint)) {
@@ -237,7 +247,7 @@ gather_put_kernel(TzbGatherPutArgs a, const int *__restrict__ idx, const T *__re
 // Blocks whose rows have no remote non-zeros never look at the flags.
 template <typename T, int U>
 __global__ void __launch_bounds__(kThreads)
-spmv_fused_all_kernel(TzbGatherPutArgs a, const int *__restrict__ sendIdx, int rows,
+spmv_fused_all_kernel(TzbGatherPutArgs a, const int *__restrict__ sendIdx, int rows, int tileRows,
                       const int *__restrict__ lRowPtr, const int *__restrict__ lColInd,
                       const T *__restrict__ lVal, const int *__restrict__ rRowPtr,
                       const int *__restrict__ rColInd, const T *__restrict__ rVal,
@@ -258,25 +268,25 @@ spmv_fused_all_kernel(TzbGatherPutArgs a, const int *__restrict__ sendIdx, int r
       if (a.peerFlag[p]) st_release_sys(a.peerFlag[p], epoch);
   }
   // (2) local product
-  const int tiles = (rows + kThreads - 1) / kThreads;
+  const int tiles = (rows + tileRows - 1) / tileRows;
   for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
-    const int r0 = tile * kThreads;
-    const T acc = tile_product<T, U, false>(r0, rows, lRowPtr, lColInd, lVal, x, prod, range);
-    if (r0 + int(threadIdx.x) < rows) y[r0 + threadIdx.x] = acc;
+    const int r0 = tile * tileRows;
+    const T acc = tile_product<T, U, false>(r0, rows, tileRows, lRowPtr, lColInd, lVal, x, prod, range);
+    if (int(threadIdx.x) < tileRows && r0 + int(threadIdx.x) < rows) y[r0 + threadIdx.x] = acc;
   }
   // (3) + (4): wait for the peers (only blocks that need remote entries), remote product;
   // the same thread wrote y[row] above, so there is no inter-thread hazard
   bool waited = false;
   for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
-    const int r0 = tile * kThreads, r1 = min(r0 + kThreads, rows);
+    const int r0 = tile * tileRows, r1 = min(r0 + tileRows, rows);
     if (__ldg(rRowPtr + r0) == __ldg(rRowPtr + r1)) continue; // block-uniform
     if (!waited) {
       if (int(threadIdx.x) < nFlags) wait_flag_geq(flags + threadIdx.x, epoch);
       __syncthreads();
       waited = true;
     }
-    const T acc = tile_product<T, U, true>(r0, rows, rRowPtr, rColInd, rVal, rx, prod, range);
-    if (r0 + int(threadIdx.x) < rows) y[r0 + threadIdx.x] += acc;
+    const T acc = tile_product<T, U, true>(r0, rows, tileRows, rRowPtr, rColInd, rVal, rx, prod, range);
+    if (int(threadIdx.x) < tileRows && r0 + int(threadIdx.x) < rows) y[r0 + threadIdx.x] += acc;
   }
 }
 
@@ -362,11 +372,12 @@ cudaError_t launch_spmv_fused_all(const TzbGatherPutArgs *a, const int *sendIdx,
                                   uint64_t epoch, uint32_t *counter, int nnzPerRow,
                                   cudaStream_t stream) {
   if (!a || a->nPeers < 0 || a->nPeers > 16 || nFlags > kThreads) return cudaErrorInvalidValue;
-  const int tiles = std::max(1, (rows + kThreads - 1) / kThreads);
+  int tileRows = stream_tile_rows(rows);
+  const int tiles = std::max(1, (rows + tileRows - 1) / tileRows);
   const int nSend = a->displ[a->nPeers];
   TzbGatherPutArgs args = *a;
   EpochArg epochArg = ep(epoch);
-  void *params[] = {&args,    &sendIdx, &rows, &lRowPtr, &lColInd, &lVal,  &rRowPtr, &rColInd,
+  void *params[] = {&args,    &sendIdx, &rows, &tileRows, &lRowPtr, &lColInd, &lVal,  &rRowPtr, &rColInd,
                     &rVal,    &x,       &rx,   &y,       &flags,   &nFlags, &epochArg, &counter};
   ++g_launches;
 #define TZB_CASE(N)                                                                                \

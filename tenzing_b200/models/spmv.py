@@ -13,8 +13,9 @@ from ..utils.tensor import device_tensor, host_tensor
 from . import common
 
 STYLES = ("reference", "fused", "fused_separate", "fused_all")
-# host-executed and tested on the CPU, kernels not yet run on hardware: offered only on request
-# (style="fused_pull", or style="choice+" for the ChoiceOp over STYLES + EXPERIMENTAL_STYLES)
+# validated on 2 and 8 B200s, but slower than the push styles on both shipped matrices (8-byte
+# peer loads): offered on request (style="fused_pull", or style="choice+" for the ChoiceOp over
+# STYLES + EXPERIMENTAL_STYLES), not in the default ChoiceOp
 EXPERIMENTAL_STYLES = ("fused_pull",)
 # built in Python, not an alternative of the ChoiceOp: Pack -> torch.distributed send/recv -> yr, y
 BASELINE_STYLES = ("dist",)
