@@ -67,6 +67,21 @@ def _ref_ensure_built(local_rank):
     return (exe, None) if ok() else (None, "reference build did not complete")
 
 
+def _ref_result_rows(lines):
+    """[pct01, pct10, pct50, pct90, pct99, stddev] (seconds) of every result row of the reference's
+    CSV: `idx|pct01|pct10|pct50|pct90|pct99|stddev|<op json>|...` (tenzing-dfs/src/dfs.cpp:84-104);
+    the reproduce header and the `{"dfs__Opts":...}` line are skipped"""
+    rows = []
+    for line in lines:
+        f = line.split("|")
+        if len(f) > 7 and f[0].strip().isdigit():
+            try:
+                rows.append([float(v) for v in f[1:7]])
+            except ValueError:
+                pass
+    return rows
+
+
 def reference_arm(args):
     """The reference arm: the UNMODIFIED reference (sandialabs/tenzing), built by its own CMake
     into baseline/_ref/ (baseline/build_ref.py), run through its own stock driver
@@ -135,14 +150,7 @@ def reference_arm(args):
         import shutil
         shutil.rmtree(logdir, ignore_errors=True)
         return 0
-    rows = []
-    for line in open(out_path, errors="replace"):
-        f = line.split("|")
-        if len(f) > 7 and f[0].strip().isdigit():
-            try:
-                rows.append([float(v) for v in f[1:7]])
-            except ValueError:
-                pass
+    rows = _ref_result_rows(open(out_path, errors="replace"))
     with open(err_path, "rb") as fe:
         fe.seek(max(0, os.path.getsize(err_path) - 400))
         tail = fe.read().decode(errors="replace").replace("\n", " ")

@@ -62,3 +62,17 @@ def test_reference_arm_reports_unavailable_and_exits_zero():
     assert p.returncode == 0
     d = json.loads(p.stdout.strip().splitlines()[-1])
     assert d["impl"] == "reference" and d["unavailable"]
+
+
+def test_reference_arm_reads_the_references_csv():
+    sys.path.insert(0, ROOT)
+    import bench
+    text = [
+        '{"args":["spmv"],"hash":"abc","major":0,"minor":1,"patch":0}\n',
+        '{"dfs__Opts":{"maxSeqs":15000}}\n',
+        '0|6.6e-05|6.7e-05|6.8e-05|7e-05|7.1e-05|1e-06|{"name":"Start"}|{"name":"yl","stream":0}|{"name":"Finish"}\n',
+        '1|6.4e-05|6.486e-05|6.5e-05|6.9e-05|7e-05|1e-06|{"name":"Start"}|{"name":"Pack","stream":1}|{"name":"Finish"}\n',
+        'some log line | with | pipes\n',
+    ]
+    rows = bench._ref_result_rows(text)
+    assert len(rows) == 2 and min(r[1] for r in rows) == 6.486e-05
