@@ -1,4 +1,6 @@
 #!/bin/bash
+# One-GPU acceptance run on a B200 box: the GPU test tier, the smoke test, one bench line.
+#   gpurun --timeout 900 -- bash scripts/gpu_check.sh
 mkdir -p gpurun_out
 export TENZING_ACK_NOTICE=1
 echo "== pytest gpu"; timeout 400 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "rc=$?"; tail -6 gpurun_out/pytest_gpu.log | cut -c1-250
