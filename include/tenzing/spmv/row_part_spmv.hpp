@@ -42,7 +42,7 @@ public:
     int count = 0;
     int dstDispl = 0; // send only: offset in the peer's rx
   };
-  // FusedPull (validated on 2 and 8 B200s, slower than the push styles there) is built on request
+  // FusedPull (validated against the oracle on 2 and 8 B200s, not timed there) is built on request
   // only and is not among the alternatives of make_spmv_choice unless asked for
   enum class Style { Reference, Fused, FusedSeparate, FusedAll, FusedPull };
   static constexpr int kFlagSets = 6; // one per style + the acknowledgements of FusedPull

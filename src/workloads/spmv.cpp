@@ -458,7 +458,7 @@ public:
   }
 };
 
-// ---- pull style (on request: slower than the push styles on the shipped matrices) ----
+// ---- pull style (built on request, not a default alternative) ----
 cudaError_t k_pull(int rows, const int *rp, const int *ci, const double *v, const double *const *xp,
                    double *y, bool acc, const uint64_t *ready, int nReady, const TzbFlagList *acks,
                    uint64_t e, uint32_t *c, int nnz, cudaStream_t st) {

@@ -13,8 +13,8 @@ from ..utils.tensor import device_tensor, host_tensor
 from . import common
 
 STYLES = ("reference", "fused", "fused_separate", "fused_all")
-# validated on 2 and 8 B200s, but slower than the push styles on both shipped matrices (8-byte
-# peer loads): offered on request (style="fused_pull", or style="choice+" for the ChoiceOp over
+# validated against the oracle on 2 and 8 B200s but never timed there (8-byte peer loads are not
+# expected to win): offered on request (style="fused_pull", or style="choice+" for the ChoiceOp over
 # STYLES + EXPERIMENTAL_STYLES), not in the default ChoiceOp
 EXPERIMENTAL_STYLES = ("fused_pull",)
 # built in Python, not an alternative of the ChoiceOp: Pack -> torch.distributed send/recv -> yr, y
