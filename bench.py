@@ -170,7 +170,8 @@ def reference_arm(args):
     us = best[1] * 1e6
     print(json.dumps({
         "impl": "reference", "metric": REF_METRIC, "value": round(us, 3), "unit": "us", "n_gpus": world,
-        "steps": 50, "warmup": 0, "ms_per_step": round(us / 1e3, 6),
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(us / 1e3, 6),
+        "reference_measurements_per_schedule": 50,
         "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "fp32",
         "data": "synthetic",
         "config": {"model": "banded SpMV 150000 x 150000, 10 nnz/row, band half-width n/ranks, fp32 "
@@ -178,8 +179,9 @@ def reference_arm(args):
                    "global_batch": "150000 rows", "seq_len": None, "parallelism": f"row-partition {world}",
                    "driver": "baseline/_ref/build/tenzing-dfs/examples/spmv (stock, no arguments), "
                              f"SIGINT after {args.ref_seconds:.0f} s",
-                   "protocol": "reference's EmpiricalBenchmarker: 50 measurements of back-to-back runs >= 10 ms, "
-                               "host wall clock, max over ranks, pct10; best of the schedules reached; no L2 flush",
+                   "protocol": "reference's EmpiricalBenchmarker decides the sample counts itself (--steps/--warmup "
+                               "cannot be passed to its stock driver): 50 measurements of back-to-back runs >= 10 ms "
+                               "each, host wall clock, max over ranks, pct10; best of the schedules reached; no L2 flush",
                    "transport": "baseline/mpi_shim (single-node MPI stand-in: CUDA-IPC rendezvous, "
                                 "copy-engine pulls over NVLink on 4 streams, event completion)"},
         "schedules_benchmarked": len(rows), "pct50_us": round(best[2] * 1e6, 3),
