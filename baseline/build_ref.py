@@ -74,6 +74,14 @@ exec g++ -I"$INC" "$@" -L"$LIB" -Wl,-rpath,"$LIB" -lmpi
     return inc, lib, wrapper
 
 
+def tag_checkout(dst, message):
+    git = ["git", "-c", "user.name=baseline", "-c", "user.email=baseline@localhost", "-c", "init.defaultBranch=main"]
+    run(git + ["init", "-q"], cwd=dst)
+    run(git + ["add", "-A"], cwd=dst)
+    run(git + ["commit", "-q", "-m", message], cwd=dst)
+    run(git + ["tag", "v0.1.0"], cwd=dst)
+
+
 def checkout(dst):
     """copy of the reference sources as a tagged git checkout (its CMake derives the version
     header from `git describe --tags`)"""
@@ -86,11 +94,7 @@ def checkout(dst):
         shutil.rmtree(dst)
     shutil.copytree(REF_SRC, dst, symlinks=True, ignore=shutil.ignore_patterns(".git"))
     run(["chmod", "-R", "u+w", dst])
-    git = ["git", "-c", "user.name=baseline", "-c", "user.email=baseline@localhost", "-c", "init.defaultBranch=main"]
-    run(git + ["init", "-q"], cwd=dst)
-    run(git + ["add", "-A"], cwd=dst)
-    run(git + ["commit", "-q", "-m", "reference snapshot"], cwd=dst)
-    run(git + ["tag", "v0.1.0"], cwd=dst)
+    tag_checkout(dst, "reference snapshot")
 
 
 def cmake_build(src, bld, wrapper, targets):
@@ -109,6 +113,25 @@ def main():
     checkout(src)
     shutil.rmtree(os.path.join(OUT, "build"), ignore_errors=True)  # paths of another machine in its cache
     cmake_build(src, os.path.join(OUT, "build"), wrapper, ["spmv-min-time", "spmv", "halo-mcts-min-time"])
+    # the end-to-end driver: a user program of the reference's API, built with the reference as a
+    # CMake sub-project so that the reference's own files decide every flag.  The reference's
+    # git module only accepts a .git directory below the top-level source directory, hence the
+    # tagged checkout is copied below the driver's sources.
+    try:
+        drv, bld = os.path.join(OUT, "e2e_src"), os.path.join(OUT, "build_e2e")
+        for d in (drv, bld):
+            shutil.rmtree(d, ignore_errors=True)
+        shutil.copytree(os.path.join(HERE, "ref_driver"), drv)
+        shutil.copytree(src, os.path.join(drv, "tenzing"), symlinks=True)
+        src = os.path.join(drv, "tenzing")
+        os.makedirs(bld, exist_ok=True)
+        run(["cmake", "-S", drv, "-B", bld, "-G", "Ninja", f"-DTENZING_REF_SRC={src}",
+             "-DCMAKE_CUDA_ARCHITECTURES=100a", f"-DCMAKE_CUDA_COMPILER={CUDA_HOME}/bin/nvcc",
+             f"-DMPI_CXX_COMPILER={wrapper}", "-DMPI_CXX_SKIP_MPICXX=ON", "-DTENZING_ENABLE_TESTS=OFF",
+             "-DCMAKE_BUILD_TYPE=Release"])
+        run(["ninja", "-C", bld, "ref-e2e"])
+    except subprocess.CalledProcessError as e:
+        print("the end-to-end driver did not build (the stock drivers are unaffected):", e)
     with open(os.path.join(OUT, "BUILD_HOST"), "w") as f:
         f.write(host_id() + "\n")
     print("reference built in", OUT)

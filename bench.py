@@ -82,6 +82,71 @@ def _ref_result_rows(lines):
     return rows
 
 
+def _ref_parse_e2e(text):
+    """the `REF_E2E key=value ...` line of baseline/ref_driver/ref_e2e.cu -> dict of floats, or None"""
+    for line in text.splitlines():
+        if line.startswith("REF_E2E ") and "median_us=" in line:
+            try:
+                return {k: float(v) for k, v in (kv.split("=", 1) for kv in line.split()[1:])}
+            except ValueError:
+                return None
+    return None
+
+
+def _ref_e2e(args, rank, world, job, logdir):
+    """End-to-end step of the reference (rank 0 returns the `e2e` record, or None when the driver is
+    not there, fails or runs out of time - the arm's main value does not depend on it).
+    baseline/ref_driver/ref_e2e.cu is a user program of the reference's public API (the set-up of
+    its SpMV example, its DFS solver + EmpiricalBenchmarker over the first --ref-e2e-seqs
+    schedules it enumerates, then the best of them run with the H2D of x before and the D2H of y
+    after every step), built with the reference as a CMake sub-project."""
+    import signal
+    import subprocess
+    exe = os.path.join(REF_DIR, "build_e2e", "ref-e2e")
+    if not os.path.exists(exe) or args.ref_e2e_seconds <= 0:
+        return None
+    out_path = os.path.join(logdir, f"e2e_r{rank}.out")
+    env = dict(os.environ, TENZING_ACK_NOTICE="1", TZMPI_RANK=str(rank), TZMPI_SIZE=str(world), TZMPI_JOB=job + "e")
+    t0 = time.time()
+    with open(out_path, "w") as fo, open(os.path.join(logdir, f"e2e_r{rank}.err"), "w") as fe:
+        child = subprocess.Popen([exe, str(args.steps), str(max(args.warmup, 3)), str(args.ref_e2e_seqs)],
+                                 env=env, stdout=fo, stderr=fe, start_new_session=True)
+        while child.poll() is None:
+            if time.time() - t0 > args.ref_e2e_seconds:
+                try:
+                    os.killpg(child.pid, signal.SIGKILL)  # exactly the process group started above
+                except ProcessLookupError:
+                    pass
+                break
+            time.sleep(0.2)
+        child.wait()
+    _ref_clean_shm(env["TZMPI_JOB"])
+    if rank != 0:
+        return None
+    got = _ref_parse_e2e(open(out_path, errors="replace").read())
+    if not got:
+        return None
+    return {"value": round(got["median_us"], 3), "unit": "us",
+            "h2d_bytes_per_step": int(got.get("h2d_bytes", 0)), "d2h_bytes_per_step": int(got.get("d2h_bytes", 0)),
+            "p10_us": round(got.get("p10_us", 0.0), 3), "p90_us": round(got.get("p90_us", 0.0), 3),
+            "schedule_pct10_us": round(got.get("schedule_pct10_us", 0.0), 3),
+            "wall_seconds": round(time.time() - t0, 1),
+            "how": "baseline/ref_driver/ref_e2e.cu: the reference's own API (RowPartSpmv, SpMV, Platform, "
+                   f"dfs::explore + EmpiricalBenchmarker over its first {args.ref_e2e_seqs} schedules), then per step "
+                   "pinned H2D of this rank's x block, the best schedule op by op, D2H of the y block; host wall "
+                   "clock, max over ranks, median"}
+
+
+def _ref_clean_shm(job):
+    """killed ranks can leave message segments of the MPI stand-in behind"""
+    import glob
+    for f in glob.glob(f"/dev/shm/tzmpi_{os.getuid()}_{job}*"):
+        try:
+            os.unlink(f)
+        except OSError:
+            pass
+
+
 def reference_arm(args):
     """The reference arm: the UNMODIFIED reference (sandialabs/tenzing), built by its own CMake
     into baseline/_ref/ (baseline/build_ref.py), run through its own stock driver
@@ -126,6 +191,12 @@ def reference_arm(args):
     err_path = os.path.join(logdir, f"ref_n{world}_r{rank}.err")
     env = dict(os.environ, TENZING_ACK_NOTICE="1", TZMPI_RANK=str(rank), TZMPI_SIZE=str(world),
                TZMPI_JOB=_ref_job_id())
+    # first the short end-to-end run (every rank starts it at the same time and it ends by itself),
+    # then the stock driver
+    try:
+        e2e = _ref_e2e(args, rank, world, env["TZMPI_JOB"], logdir) if world > 1 else None
+    except Exception:
+        e2e = None
     t0 = time.time()
     with open(out_path, "w") as fo, open(err_path, "w") as fe:
         child = subprocess.Popen([exe], env=env, stdout=fo, stderr=fe, start_new_session=True)
@@ -146,13 +217,7 @@ def reference_arm(args):
             time.sleep(0.2)
         child.wait()
     wall = time.time() - t0
-    # killed ranks can leave message segments of the MPI stand-in behind
-    import glob
-    for f in glob.glob(f"/dev/shm/tzmpi_{os.getuid()}_{env['TZMPI_JOB']}*"):
-        try:
-            os.unlink(f)
-        except OSError:
-            pass
+    _ref_clean_shm(env["TZMPI_JOB"])
     if rank != 0:
         import shutil
         shutil.rmtree(logdir, ignore_errors=True)
@@ -169,6 +234,7 @@ def reference_arm(args):
     best = min(rows, key=lambda v: v[1])
     us = best[1] * 1e6
     print(json.dumps({
+        **({"e2e": e2e} if e2e else {}),
         "impl": "reference", "metric": REF_METRIC, "value": round(us, 3), "unit": "us", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(us / 1e3, 6),
         "reference_measurements_per_schedule": 50,
@@ -210,6 +276,10 @@ def main():
                     help="reference arm: wall-clock seconds its DFS driver gets before SIGINT")
     ap.add_argument("--ref-grace", type=float, default=25.0,
                     help="reference arm: seconds after the signal before the ranks are killed")
+    ap.add_argument("--ref-e2e-seconds", type=float, default=90.0,
+                    help="reference arm: wall-clock limit of its end-to-end run (0 = skip it)")
+    ap.add_argument("--ref-e2e-seqs", type=int, default=40,
+                    help="reference arm: schedules its DFS generates before the end-to-end run picks the best")
     ap.add_argument("--host-dry-run", action="store_true",
                     help="no GPU: the same control flow with the workloads executed on the CPU "
                          "(host memory, gloo); a test of this script, its number is not a result")

@@ -76,3 +76,13 @@ def test_reference_arm_reads_the_references_csv():
     ]
     rows = bench._ref_result_rows(text)
     assert len(rows) == 2 and min(r[1] for r in rows) == 6.486e-05
+
+
+def test_reference_arm_reads_the_end_to_end_line():
+    sys.path.insert(0, ROOT) if ROOT not in sys.path else None
+    import bench
+    got = bench._ref_parse_e2e("noise\nREF_E2E median_us=447.461 p10_us=442.611 p90_us=551.057 h2d_bytes=300000 "
+                               "d2h_bytes=300000 schedule_pct10_us=511.083\n")
+    assert got["median_us"] == pytest.approx(447.461) and got["h2d_bytes"] == 300000
+    assert bench._ref_parse_e2e("REF_E2E none\n") is None
+    assert bench._ref_parse_e2e("") is None
