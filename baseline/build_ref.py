@@ -129,7 +129,7 @@ def main():
              "-DCMAKE_CUDA_ARCHITECTURES=100a", f"-DCMAKE_CUDA_COMPILER={CUDA_HOME}/bin/nvcc",
              f"-DMPI_CXX_COMPILER={wrapper}", "-DMPI_CXX_SKIP_MPICXX=ON", "-DTENZING_ENABLE_TESTS=OFF",
              "-DCMAKE_BUILD_TYPE=Release"])
-        run(["ninja", "-C", bld, "ref-e2e"])
+        run(["ninja", "-C", bld, "ref-e2e", "ref-enum"])
     except subprocess.CalledProcessError as e:
         print("the end-to-end driver did not build (the stock drivers are unaffected):", e)
     with open(os.path.join(OUT, "BUILD_HOST"), "w") as f:

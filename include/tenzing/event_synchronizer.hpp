@@ -42,9 +42,13 @@ public:
   Event new_unique_event() const { return Event(nextEvent_); }
 
 private:
-  std::unordered_map<uint32_t, int> byUid_, byUnbound_;
-  std::unordered_map<int, std::vector<Record>> byStream_;
+  // paths are tens to a few hundred ops and an index is built for every state the search
+  // visits: flat sorted arrays (no node allocations) instead of hash maps
+  std::vector<std::pair<uint32_t, int>> byUid_, byUnbound_;       // sorted by id, first position wins
+  std::vector<std::pair<int, std::vector<Record>>> byStream_;    // a handful of streams
   int nextEvent_ = 0;
+  static int lookup(const std::vector<std::pair<uint32_t, int>> &v, uint32_t id);
+  std::vector<Record> &records_mut(int stream);
 };
 
 struct EventSynchronizer {

@@ -367,6 +367,34 @@ public:
     return r;
   }
 
+  // the same from a per-vertex "done" table (see mark_done): no lookups, what a search that
+  // extends one path step by step uses
+  std::vector<op_t> frontier_of_mask(const std::vector<char> &isDone) const {
+    std::vector<op_t> r;
+    for (vid_t i = 0; i < static_cast<vid_t>(v_.size()); ++i) {
+      if (!v_[i].alive || (size_t(i) < isDone.size() && isDone[size_t(i)])) continue;
+      bool ready = true;
+      for (vid_t p : v_[i].preds) {
+        if (!(size_t(p) < isDone.size() && isDone[size_t(p)])) {
+          ready = false;
+          break;
+        }
+      }
+      if (ready) r.push_back(v_[i].op);
+    }
+    return r;
+  }
+  // record in `isDone` (indexed by vertex, grown as needed) that `op` has been executed;
+  // ops that are not vertices (synchronisation inserted by the search) leave it unchanged.
+  // Vertex numbers survive clone_but_replace / clone_but_expand, so a table filled against a
+  // graph stays valid for the graphs rewritten from it.
+  void mark_done(std::vector<char> &isDone, const OpBase &op) const {
+    const vid_t i = find_vertex_unbound(op);
+    if (i < 0) return;
+    if (isDone.size() < v_.size()) isDone.resize(v_.size(), 0);
+    isDone[size_t(i)] = 1;
+  }
+
   // ---- output ----
   std::string str() const {
     std::ostringstream ss;

@@ -46,19 +46,51 @@ const std::string &interned_key(uint32_t uid);
 #define EQ_DEF(TYPE)
 #define LT_DEF(TYPE)
 
+// What an op is, as bits.  The search asks these questions of every op of every state it
+// visits; the answers depend on the dynamic type only, so each object works them out once
+// (dynamic_casts, src/core/operation.cpp) and keeps them.
+namespace op_trait {
+enum : uint16_t {
+  Bound = 1u << 0,           // BoundOp
+  Cpu = 1u << 1,             // CpuOp
+  BoundGpu = 1u << 2,        // exactly BoundGpuOp
+  Gpu = 1u << 3,             // GpuOp (unbound)
+  Compound = 1u << 4,        // CompoundOp
+  Choice = 1u << 5,          // ChoiceOp
+  Sync = 1u << 6,            // SyncOpBase
+  WithStream = 1u << 7,      // HasStream
+  WithEvent = 1u << 8,       // HasEvent
+  EventRecord = 1u << 9,     // exactly CudaEventRecord
+  EventSync = 1u << 10,      // exactly CudaEventSync
+  StreamWaitEvent = 1u << 11, // exactly CudaStreamWaitEvent
+  IsStart = 1u << 12,        // exactly Start
+  Known = 1u << 15
+};
+} // namespace op_trait
+
 class OpBase {
   mutable uint32_t uid_ = 0; // 0 = not interned yet
   mutable uint32_t unboundUid_ = 0;
+  mutable uint16_t traits_ = 0; // 0 = not worked out yet
+  uint16_t compute_traits() const;
 
 public:
   OpBase() = default;
   // copies must re-intern (a derived copy-constructor may change key fields)
-  OpBase(const OpBase &) : uid_(0), unboundUid_(0) {}
+  OpBase(const OpBase &) : uid_(0), unboundUid_(0), traits_(0) {}
   OpBase &operator=(const OpBase &) {
     uid_ = unboundUid_ = 0;
+    traits_ = 0;
     return *this;
   }
   virtual ~OpBase() = default;
+
+  // op_trait bits of this object's dynamic type
+  uint16_t traits() const {
+    if (!traits_) traits_ = compute_traits();
+    return traits_;
+  }
+  bool is(uint16_t trait) const { return (traits() & trait) != 0; }
 
   virtual std::string name() const = 0;
   virtual std::string desc() const { return name(); }

@@ -1,0 +1,90 @@
+#!/usr/bin/env python
+"""Search-engine throughput on the CPU, this framework against the unmodified reference
+(BASELINE.json config 1: noop-graph DFS schedule enumeration, no GPU).
+
+Both arms enumerate every schedule of the same graphs through their public DFS entry point
+(`dfs::get_all_sequences`): K independent chains of L NoOps between Start and Finish, which have
+(K*L)! / (L!)^K schedules.  The reference side is baseline/ref_driver/ref_enum.cu built against
+the reference by baseline/build_ref.py; both run on this machine, one thread.
+
+  python scripts/search_throughput.py [--out profiles/search_throughput.txt]
+"""
+import argparse
+import math
+import os
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+os.environ.setdefault("TENZING_ACK_NOTICE", "1")
+
+CASES = [(3, 1), (3, 2), (4, 2), (3, 3), (5, 2), (4, 3)]
+
+
+def ours(K, L, repeats):
+    import tenzing_b200 as tz
+    g = tz.Graph()
+    for k in range(K):
+        prev = None
+        for l in range(L):
+            op = tz.NoOp(f"op{k}_{l}")
+            if prev is None:
+                g.start_then(op)
+            else:
+                g.then(prev, op)
+            prev = op
+        g.then_finish(prev)
+    plat = tz.Platform.make_null(1)
+    best, n = float("inf"), 0
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        seqs = tz.dfs.get_all_sequences(g, plat)
+        best = min(best, time.perf_counter() - t0)
+        n = len(seqs)
+    return n, best
+
+
+def reference(K, L, repeats, limit_s):
+    exe = os.path.join(ROOT, "baseline", "_ref", "build_e2e", "ref-enum")
+    if not os.path.exists(exe):
+        return None, None
+    env = dict(os.environ, TZMPI_RANK="0", TZMPI_SIZE="1", TZMPI_JOB=f"enum{os.getpid()}")
+    best, n = float("inf"), None
+    for _ in range(repeats):
+        try:
+            r = subprocess.run([exe, str(K), str(L)], env=env, capture_output=True, text=True, timeout=limit_s)
+        except subprocess.TimeoutExpired:
+            return None, f">{limit_s:.0f}"
+        for line in r.stdout.splitlines():
+            if line.startswith("REF_ENUM "):
+                kv = dict(f.split("=") for f in line.split()[1:])
+                n, best = int(kv["sequences"]), min(best, float(kv["seconds"]))
+    return n, (best if n is not None else None)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--out", default="")
+    ap.add_argument("--repeats", type=int, default=3)
+    ap.add_argument("--ref-limit", type=float, default=600.0, help="seconds per reference run")
+    args = ap.parse_args()
+    lines = ["# noop-graph DFS enumeration on the CPU (one thread, best of %d): K chains of L NoOps" % args.repeats,
+             "# chains len schedules_expected ours_schedules ours_s reference_schedules reference_s reference/ours"]
+    for K, L in CASES:
+        want = math.factorial(K * L) // math.factorial(L) ** K
+        n_o, t_o = ours(K, L, args.repeats)
+        n_r, t_r = reference(K, L, 1 if want > 20000 else args.repeats, args.ref_limit)
+        ratio = f"{t_r / t_o:.1f}" if isinstance(t_r, float) and t_o > 0 else "-"
+        t_r_s = f"{t_r:.6f}" if isinstance(t_r, float) else str(t_r)
+        lines.append(f"{K} {L} {want} {n_o} {t_o:.6f} {n_r} {t_r_s} {ratio}")
+        print(lines[-1], flush=True)
+        assert n_o == want, "this framework's enumeration is wrong"
+    if args.out:
+        with open(os.path.join(ROOT, args.out), "w") as f:
+            f.write("\n".join(lines) + "\n")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,58 +1,89 @@
 #include "tenzing/event_synchronizer.hpp"
 
+#include <algorithm>
 #include <typeinfo>
 
 namespace tenzing {
 
 // ---------------------------------------------------------------- PathIndex
 PathIndex::PathIndex(const Sequence<BoundOp> &path) {
-  std::unordered_map<int, std::pair<int, size_t>> recordOf; // event -> (stream, index in byStream_)
+  struct Latest { int event, stream; size_t idx; };
+  std::vector<Latest> recordOf; // the latest record of each event: (stream, index in its stream's list)
+  auto latest = [&recordOf](int event) -> Latest * {
+    for (auto &r : recordOf)
+      if (r.event == event) return &r;
+    return nullptr;
+  };
   std::vector<char> used;
   auto mark = [&](const Event &e) {
     if (e.id() < 0) return;
     if (size_t(e.id()) >= used.size()) used.resize(size_t(e.id()) + 1, 0);
     used[size_t(e.id())] = 1;
   };
+  byUid_.reserve(path.size());
+  byUnbound_.reserve(path.size());
   for (size_t i = 0; i < path.size(); ++i) {
     const BoundOpPtr &op = path[i];
-    byUid_.emplace(op->uid(), int(i));
-    byUnbound_.emplace(op->unbound_uid(), int(i));
-    if (auto he = std::dynamic_pointer_cast<HasEvent>(op))
-      for (const Event &e : he->get_events()) mark(e);
-    if (auto cer = std::dynamic_pointer_cast<CudaEventRecord>(op)) {
-      auto &v = byStream_[cer->stream().id()];
+    byUid_.emplace_back(op->uid(), int(i));
+    byUnbound_.emplace_back(op->unbound_uid(), int(i));
+    const uint16_t t = op->traits();
+    if (!(t & op_trait::WithEvent)) continue;
+    if (t & op_trait::EventRecord) {
+      auto cer = std::static_pointer_cast<CudaEventRecord>(op);
+      mark(cer->event());
+      auto &v = records_mut(cer->stream().id());
       Record r;
       r.pos = int(i);
       r.event = cer->event();
       r.op = cer;
-      recordOf[cer->event().id()] = {cer->stream().id(), v.size()}; // the latest record of the event
+      if (Latest *l = latest(cer->event().id())) {
+        l->stream = cer->stream().id();
+        l->idx = v.size();
+      } else {
+        recordOf.push_back(Latest{cer->event().id(), cer->stream().id(), v.size()});
+      }
       v.push_back(std::move(r));
-    } else if (auto ces = std::dynamic_pointer_cast<CudaEventSync>(op)) {
-      auto it = recordOf.find(ces->event().id());
-      if (it != recordOf.end()) byStream_[it->second.first][it->second.second].hostSynced = true;
-    } else if (auto w = std::dynamic_pointer_cast<CudaStreamWaitEvent>(op)) {
-      auto it = recordOf.find(w->event().id());
-      if (it != recordOf.end())
-        byStream_[it->second.first][it->second.second].waiters.push_back(w->stream().id());
+    } else if (t & op_trait::EventSync) {
+      const auto &ces = static_cast<const CudaEventSync &>(*op);
+      mark(ces.event());
+      if (const Latest *l = latest(ces.event().id())) records_mut(l->stream)[l->idx].hostSynced = true;
+    } else if (t & op_trait::StreamWaitEvent) {
+      const auto &w = static_cast<const CudaStreamWaitEvent &>(*op);
+      mark(w.event());
+      if (const Latest *l = latest(w.event().id()))
+        records_mut(l->stream)[l->idx].waiters.push_back(w.stream().id());
+    } else if (const auto *he = dynamic_cast<const HasEvent *>(op.get())) {
+      for (const Event &e : he->get_events()) mark(e);
     }
   }
+  // (id, position) order: among equal ids the earliest position comes first, the one lookups return
+  std::sort(byUid_.begin(), byUid_.end());
+  std::sort(byUnbound_.begin(), byUnbound_.end());
   while (size_t(nextEvent_) < used.size() && used[size_t(nextEvent_)]) ++nextEvent_;
 }
 
-int PathIndex::pos_of(const OpBase &op) const {
-  auto it = byUid_.find(op.uid());
-  return it == byUid_.end() ? -1 : it->second;
+std::vector<PathIndex::Record> &PathIndex::records_mut(int stream) {
+  for (auto &kv : byStream_)
+    if (kv.first == stream) return kv.second;
+  byStream_.emplace_back(stream, std::vector<Record>{});
+  return byStream_.back().second;
 }
 
-int PathIndex::pos_of_unbound(const OpBase &op) const {
-  auto it = byUnbound_.find(op.unbound_uid());
-  return it == byUnbound_.end() ? -1 : it->second;
+int PathIndex::lookup(const std::vector<std::pair<uint32_t, int>> &v, uint32_t id) {
+  auto it = std::lower_bound(v.begin(), v.end(), id,
+                             [](const std::pair<uint32_t, int> &x, uint32_t key) { return x.first < key; });
+  return it == v.end() || it->first != id ? -1 : it->second;
 }
+
+int PathIndex::pos_of(const OpBase &op) const { return lookup(byUid_, op.uid()); }
+
+int PathIndex::pos_of_unbound(const OpBase &op) const { return lookup(byUnbound_, op.unbound_uid()); }
 
 const std::vector<PathIndex::Record> &PathIndex::records(const Stream &s) const {
   static const std::vector<Record> none;
-  auto it = byStream_.find(s.id());
-  return it == byStream_.end() ? none : it->second;
+  for (const auto &kv : byStream_)
+    if (kv.first == s.id()) return kv.second;
+  return none;
 }
 
 namespace {
@@ -98,14 +129,12 @@ struct PredInfo {
 
 PredInfo classify(const BoundOpPtr &pred, const BoundOpPtr &bo) {
   PredInfo r;
-  // BoundGpuOp and Start are final classes: an exact type test (one pointer comparison) is
-  // enough and this function runs once per (frontier op, predecessor) pair of every decision
-  const bool pIsGpu = typeid(*pred) == typeid(BoundGpuOp);
-  const bool bIsGpu = typeid(*bo) == typeid(BoundGpuOp);
-  if (!pIsGpu) {
-    if (typeid(*pred) == typeid(Start)) return r;
-    if (dynamic_cast<const CpuOp *>(pred.get()) && (bIsGpu || dynamic_cast<const CpuOp *>(bo.get())))
-      return r; // CPU -> anything: the host issues in order
+  // runs once per (frontier op, predecessor) pair of every decision: cached type bits, no casts
+  const uint16_t pt = pred->traits(), bt = bo->traits();
+  const bool bIsGpu = (bt & op_trait::BoundGpu) != 0;
+  if (!(pt & op_trait::BoundGpu)) {
+    if (pt & op_trait::IsStart) return r;
+    if ((pt & op_trait::Cpu) && (bIsGpu || (bt & op_trait::Cpu))) return r; // CPU -> anything: the host issues in order
     THROW_RUNTIME("unexpected op combination: " << pred->desc() << " -> " << bo->desc());
   }
   r.pGpu = std::static_pointer_cast<BoundGpuOp>(pred);
@@ -116,7 +145,7 @@ PredInfo classify(const BoundOpPtr &pred, const BoundOpPtr &bo) {
     r.need = Need::GpuThenGpu;
     return r;
   }
-  if (dynamic_cast<const CpuOp *>(bo.get())) {
+  if (bt & op_trait::Cpu) {
     r.need = Need::GpuThenCpu;
     return r;
   }

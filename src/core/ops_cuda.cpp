@@ -1,8 +1,30 @@
 #include "tenzing/cuda/ops_cuda.hpp"
 
+#include <typeinfo>
+
 #include "tenzing/host_streams.hpp"
 
 namespace tenzing {
+
+// the one place that asks the type system; every other part of the library reads the bits
+uint16_t OpBase::compute_traits() const {
+  uint16_t t = op_trait::Known;
+  const std::type_info &ti = typeid(*this);
+  if (dynamic_cast<const BoundOp *>(this)) t |= op_trait::Bound;
+  if (dynamic_cast<const CpuOp *>(this)) t |= op_trait::Cpu;
+  if (ti == typeid(BoundGpuOp)) t |= op_trait::BoundGpu;
+  if (dynamic_cast<const GpuOp *>(this)) t |= op_trait::Gpu;
+  if (dynamic_cast<const CompoundOp *>(this)) t |= op_trait::Compound;
+  if (dynamic_cast<const ChoiceOp *>(this)) t |= op_trait::Choice;
+  if (dynamic_cast<const SyncOpBase *>(this)) t |= op_trait::Sync;
+  if (dynamic_cast<const HasStream *>(this)) t |= op_trait::WithStream;
+  if (dynamic_cast<const HasEvent *>(this)) t |= op_trait::WithEvent;
+  if (ti == typeid(CudaEventRecord)) t |= op_trait::EventRecord;
+  if (ti == typeid(CudaEventSync)) t |= op_trait::EventSync;
+  if (ti == typeid(CudaStreamWaitEvent)) t |= op_trait::StreamWaitEvent;
+  if (ti == typeid(Start)) t |= op_trait::IsStart;
+  return t;
+}
 
 Json BoundGpuOp::json() const {
   Json j = op_->json();

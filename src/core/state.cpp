@@ -24,8 +24,11 @@ std::vector<DecisionPtr> State::get_decisions(const Platform &plat, bool quiet) 
   std::vector<DecisionPtr> decisions;
   std::unordered_set<uint32_t> offeredSyncs; // one ExecuteOp per distinct sync op
   const PathIndex idx(sequence_);            // one pass over the path serves every frontier op
-  for (const OpPtr &op : graph_->frontier(sequence_.vector())) {
-    if (auto bop = std::dynamic_pointer_cast<BoundOp>(op)) {
+  for (; doneCounted_ < sequence_.size(); ++doneCounted_) graph_->mark_done(done_, *sequence_[doneCounted_]);
+  for (const OpPtr &op : graph_->frontier_of_mask(done_)) {
+    const uint16_t t = op->traits();
+    if (t & op_trait::Bound) {
+      const BoundOpPtr bop = std::static_pointer_cast<BoundOp>(op);
       const std::vector<BoundOpPtr> syncs =
           Synchronizer::is_synced(bop, *graph_, sequence_, idx)
               ? std::vector<BoundOpPtr>{}
@@ -37,12 +40,14 @@ std::vector<DecisionPtr> State::get_decisions(const Platform &plat, bool quiet) 
           if (offeredSyncs.insert(s->uid()).second)
             decisions.push_back(std::make_shared<ExecuteOp>(s));
       }
-    } else if (auto gop = std::dynamic_pointer_cast<GpuOp>(op)) {
+    } else if (t & op_trait::Gpu) {
+      const auto gop = std::static_pointer_cast<GpuOp>(op);
       for (const Stream &s : plat.streams_)
         decisions.push_back(std::make_shared<AssignOpStream>(gop, s));
-    } else if (auto comp = std::dynamic_pointer_cast<CompoundOp>(op)) {
-      decisions.push_back(std::make_shared<ExpandOp>(comp));
-    } else if (auto choice = std::dynamic_pointer_cast<ChoiceOp>(op)) {
+    } else if (t & op_trait::Compound) {
+      decisions.push_back(std::make_shared<ExpandOp>(std::static_pointer_cast<CompoundOp>(op)));
+    } else if (t & op_trait::Choice) {
+      const auto choice = std::static_pointer_cast<ChoiceOp>(op);
       for (const OpPtr &alt : choice->choices())
         decisions.push_back(std::make_shared<ChooseOp>(choice, alt));
     } else {
@@ -54,26 +59,34 @@ std::vector<DecisionPtr> State::get_decisions(const Platform &plat, bool quiet) 
   return decisions;
 }
 
+State State::with_graph(Graph<OpBase> &&g) const {
+  State r(std::make_shared<const Graph<OpBase>>(std::move(g)), sequence_);
+  r.seqDigest_ = seqDigest_;
+  r.seqDigested_ = seqDigested_;
+  r.done_ = done_; // vertex numbers survive the rewrite
+  r.doneCounted_ = doneCounted_;
+  return r;
+}
+
 State State::apply(const Decision &d) const {
   switch (d.kind()) {
   case Decision::Kind::ExecuteOp: {
-    State r(*this);
+    State r(*this); // shares the graph and its prepared tokens, carries the sequence digest on
     r.keyCache_.clear();
     r.sequence_.push_back(static_cast<const ExecuteOp &>(d).op);
     return r;
   }
   case Decision::Kind::ExpandOp: {
     const auto &e = static_cast<const ExpandOp &>(d);
-    return State(graph_->clone_but_expand(e.op, e.op->graph()), sequence_);
+    return with_graph(graph_->clone_but_expand(e.op, e.op->graph()));
   }
   case Decision::Kind::AssignOpStream: {
     const auto &a = static_cast<const AssignOpStream &>(d);
-    return State(graph_->clone_but_replace(std::make_shared<BoundGpuOp>(a.op, a.stream), a.op),
-                 sequence_);
+    return with_graph(graph_->clone_but_replace(std::make_shared<BoundGpuOp>(a.op, a.stream), a.op));
   }
   case Decision::Kind::ChooseOp: {
     const auto &c = static_cast<const ChooseOp &>(d);
-    return State(graph_->clone_but_replace(c.replacement, c.orig), sequence_);
+    return with_graph(graph_->clone_but_replace(c.replacement, c.orig));
   }
   }
   THROW_RUNTIME("failed to apply decision, unexpected Decision type");
@@ -81,10 +94,15 @@ State State::apply(const Decision &d) const {
 
 std::vector<State> State::frontier(const Platform &plat, bool quiet) const {
   std::vector<State> result;
-  std::unordered_set<std::string> seen;
+  std::vector<StateKey> seen; // a handful of siblings
+  canonical_hash();           // so that every child inherits the digest of the common prefix
   for (const auto &d : get_decisions(plat, quiet)) {
     State s = apply(*d);
-    if (seen.insert(s.canonical_key()).second) result.push_back(std::move(s));
+    const StateKey k = s.canonical_hash();
+    if (std::find(seen.begin(), seen.end(), k) == seen.end()) {
+      seen.push_back(k);
+      result.push_back(std::move(s));
+    }
   }
   return result;
 }
@@ -143,6 +161,99 @@ std::string State::canonical_key() const {
   }
   keyCache_ = key;
   return key;
+}
+
+// ---- the digest form of the same key ----
+// Token for token what canonical_key() writes (sequence ops, '#', then the graph's vertices in
+// unbound-uid order with their sorted successor lists, one renumbering across both), folded into
+// 128 bits instead of a string.  Two things make it cheap: a state derived by ExecuteOp digests
+// only the op it added, and the graph's tokens are laid out once per graph object.
+void detail::KeyDigest::op(const OpBase &o) {
+  const uint16_t t = o.traits();
+  if (t & op_trait::Sync)
+    token('k', intern_key(o.kind()));
+  else
+    token('o', o.unbound_uid());
+  if (t & op_trait::BoundGpu) {
+    stream(static_cast<const BoundGpuOp &>(o).stream().id());
+    return;
+  }
+  if (t & op_trait::WithStream)
+    for (const Stream &st : dynamic_cast<const HasStream &>(o).get_streams()) stream(st.id());
+  if (t & op_trait::WithEvent)
+    for (const Event &e : dynamic_cast<const HasEvent &>(o).get_events()) event(e.id());
+}
+
+static std::shared_ptr<const detail::GraphTokens> make_graph_tokens(const Graph<OpBase> &g) {
+  auto gt = std::make_shared<detail::GraphTokens>();
+  auto put = [&gt](char tag, uint32_t v) { gt->tokens.push_back((uint64_t(uint8_t(tag)) << 32) | v); };
+  std::vector<OpPtr> verts = g.vertices();
+  std::sort(verts.begin(), verts.end(),
+            [](const OpPtr &x, const OpPtr &y) { return x->unbound_uid() < y->unbound_uid(); });
+  std::vector<uint32_t> succIds;
+  for (const auto &v : verts) {
+    if (const auto *sync = dynamic_cast<const SyncOpBase *>(v.get()))
+      put('k', intern_key(sync->kind()));
+    else
+      put('o', v->unbound_uid());
+    if (const auto *hs = dynamic_cast<const HasStream *>(v.get()))
+      for (const Stream &st : hs->get_streams()) {
+        put('s', uint32_t(st.id()));
+        gt->hasResources = true;
+      }
+    if (const auto *he = dynamic_cast<const HasEvent *>(v.get()))
+      for (const Event &e : he->get_events()) {
+        put('e', uint32_t(e.id()));
+        gt->hasResources = true;
+      }
+    put('>', 0);
+    succIds.clear();
+    for (const auto &sc : g.succs(v)) succIds.push_back(sc->unbound_uid());
+    std::sort(succIds.begin(), succIds.end());
+    for (uint32_t id : succIds) put(',', id);
+    put('|', 0);
+  }
+  if (!gt->hasResources) {
+    detail::KeyDigest d;
+    for (uint64_t t : gt->tokens) d.mix(t);
+    gt->plain = StateKey{d.a, d.b};
+  }
+  return gt;
+}
+
+StateKey State::sequence_hash() const {
+  for (; seqDigested_ < sequence_.size(); ++seqDigested_) seqDigest_.op(*sequence_[seqDigested_]);
+  return StateKey{seqDigest_.a, seqDigest_.b};
+}
+
+StateKey State::canonical_hash() const {
+  sequence_hash();
+  if (!graphTokens_) graphTokens_ = make_graph_tokens(*graph_);
+  detail::KeyDigest d;
+  d.a = seqDigest_.a;
+  d.b = seqDigest_.b;
+  d.mix('#');
+  if (!graphTokens_->hasResources) {
+    d.mix(graphTokens_->plain.a);
+    d.mix(graphTokens_->plain.b);
+  } else {
+    // the graph's streams and events continue the sequence's renumbering
+    d.streams = seqDigest_.streams;
+    d.events = seqDigest_.events;
+    for (uint64_t t : graphTokens_->tokens) {
+      const char tag = char(t >> 32);
+      if (tag == 's') d.stream(int(uint32_t(t)));
+      else if (tag == 'e') d.event(int(uint32_t(t)));
+      else d.mix(t);
+    }
+  }
+  return StateKey{d.a, d.b};
+}
+
+StateKey sequence_hash(const Sequence<BoundOp> &seq) {
+  detail::KeyDigest d;
+  for (const auto &op : seq) d.op(*op);
+  return StateKey{d.a, d.b};
 }
 
 Equivalence get_equivalence(const State &a, const State &b) {

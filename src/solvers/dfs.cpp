@@ -47,14 +47,54 @@ void Stop::bcast(int root, Communicator &comm) {
   value_ = v != 0;
 }
 
+namespace {
+// The set of digests seen so far.  One probe sequence in one flat array per look-up: with
+// millions of states a node-based set spends its time in cache misses and allocations.
+class KeySet {
+  std::vector<StateKey> slots_; // {0,0} = empty
+  size_t used_ = 0;
+  static StateKey norm(StateKey k) {
+    if (k.a == 0 && k.b == 0) k.b = 1;
+    return k;
+  }
+  bool place(const StateKey &k) {
+    const size_t mask = slots_.size() - 1;
+    for (size_t i = StateKeyHasher{}(k) & mask;; i = (i + 1) & mask) {
+      StateKey &s = slots_[i];
+      if (s.a == 0 && s.b == 0) {
+        s = k;
+        return true;
+      }
+      if (s == k) return false;
+    }
+  }
+
+public:
+  KeySet() : slots_(1024) {}
+  // true if the key was not there yet
+  bool insert(StateKey k) {
+    k = norm(k);
+    if ((used_ + 1) * 2 > slots_.size()) {
+      std::vector<StateKey> old(slots_.size() * 2);
+      old.swap(slots_);
+      for (const StateKey &o : old)
+        if (o.a || o.b) place(o);
+    }
+    const bool fresh = place(k);
+    used_ += fresh;
+    return fresh;
+  }
+};
+} // namespace
+
 std::vector<Sequence<BoundOp>> get_all_sequences(const Graph<OpBase> &g, const Platform &plat,
                                                  int64_t maxSeqs, bool removeRedundantSyncs) {
   const double t0 = counters::now();
   std::vector<Sequence<BoundOp>> ret;
-  std::unordered_set<std::string> seenStates, seenSeqs;
+  KeySet seenStates, seenSeqs;
   std::vector<SDP::State> stack;
   stack.emplace_back(g);
-  seenStates.insert(stack.back().canonical_key());
+  seenStates.insert(stack.back().canonical_hash());
   const uint64_t limit = maxSeqs < 0 ? UINT64_MAX : uint64_t(maxSeqs);
   while (!stack.empty() && ret.size() < limit) {
     SDP::State cur = std::move(stack.back());
@@ -63,13 +103,14 @@ std::vector<Sequence<BoundOp>> get_all_sequences(const Graph<OpBase> &g, const P
     if (cur.is_terminal()) {
       Sequence<BoundOp> seq = cur.sequence();
       if (removeRedundantSyncs) Schedule::remove_redundant_syncs(seq);
-      if (seenSeqs.insert(canonical_key(seq)).second) ret.push_back(std::move(seq));
+      const StateKey k = removeRedundantSyncs ? sequence_hash(seq) : cur.sequence_hash();
+      if (seenSeqs.insert(k)) ret.push_back(std::move(seq));
       continue;
     }
     std::vector<SDP::State> next = cur.frontier(plat);
     // push in reverse so the first decision is explored first
     for (auto it = next.rbegin(); it != next.rend(); ++it) {
-      if (seenStates.insert(it->canonical_key()).second) {
+      if (seenStates.insert(it->canonical_hash())) {
         stack.push_back(std::move(*it));
       } else {
         TENZING_COUNTER_OP(dfs, STATES_PRUNED, += 1);
