@@ -34,7 +34,13 @@ public:
     std::vector<int> waiters;    // streams with a CudaStreamWaitEvent on the event afterwards
     std::shared_ptr<CudaEventRecord> op;
   };
-  explicit PathIndex(const Sequence<BoundOp> &path);
+  PathIndex() = default;
+  explicit PathIndex(const Sequence<BoundOp> &path) { extend(path); }
+  // index the ops of `path` from position size() on: a path that has only grown at its end
+  // since the last call costs its new ops, which is what a search that derives states from
+  // one another pays (SDP::State keeps its index and hands a copy to its successors)
+  void extend(const Sequence<BoundOp> &path);
+  size_t size() const { return n_; }
   int pos_of(const OpBase &op) const;          // by identity; -1 if absent
   int pos_of_unbound(const OpBase &op) const;  // ignoring the stream binding; -1 if absent
   const std::vector<Record> &records(const Stream &s) const;
@@ -47,6 +53,14 @@ private:
   std::vector<std::pair<uint32_t, int>> byUid_, byUnbound_;       // sorted by id, first position wins
   std::vector<std::pair<int, std::vector<Record>>> byStream_;    // a handful of streams
   int nextEvent_ = 0;
+  size_t n_ = 0; // ops indexed so far
+  struct Latest {
+    int event, stream;
+    size_t idx;
+  };
+  std::vector<Latest> recordOf_; // the latest record of each event: (stream, index in its stream's list)
+  std::vector<char> used_;       // event ids in use
+  void append(const BoundOpPtr &op, int pos, bool sorted);
   static int lookup(const std::vector<std::pair<uint32_t, int>> &v, uint32_t id);
   std::vector<Record> &records_mut(int stream);
 };

@@ -21,31 +21,125 @@
 
 namespace tenzing {
 
+namespace detail {
+// The solvers make a graph per rewrite decision (a stream assignment copies the whole program
+// graph), so a copy must cost a few block copies, not two allocations per vertex plus a node
+// per index entry: adjacency lists keep their first entries inline and the indexes are sorted
+// flat arrays.
+
+// a short list of vertex numbers; up to N live inside the object
+template <int N> class SmallIds {
+  int n_ = 0;
+  int inl_[N];
+  std::vector<int> more_; // entries N.. when the list is longer
+
+public:
+  int size() const { return n_; }
+  bool empty() const { return n_ == 0; }
+  int operator[](int i) const { return i < N ? inl_[i] : more_[size_t(i - N)]; }
+  void push_back(int x) {
+    if (n_ < N) inl_[n_] = x;
+    else more_.push_back(x);
+    ++n_;
+  }
+  void clear() {
+    n_ = 0;
+    more_.clear();
+  }
+  bool contains(int x) const {
+    for (int i = 0; i < n_; ++i)
+      if ((*this)[i] == x) return true;
+    return false;
+  }
+  void remove(int x) {
+    int w = 0;
+    const int n = n_;
+    std::vector<int> keep;
+    for (int i = 0; i < n; ++i) {
+      const int v = (*this)[i];
+      if (v == x) continue;
+      if (w < N) inl_[w] = v;
+      else keep.push_back(v);
+      ++w;
+    }
+    n_ = w;
+    more_.swap(keep);
+  }
+  class const_iterator {
+    const SmallIds *s_;
+    int i_;
+
+  public:
+    using iterator_category = std::forward_iterator_tag;
+    using value_type = int;
+    using difference_type = std::ptrdiff_t;
+    using pointer = const int *;
+    using reference = int;
+    const_iterator(const SmallIds *s, int i) : s_(s), i_(i) {}
+    int operator*() const { return (*s_)[i_]; }
+    const_iterator &operator++() {
+      ++i_;
+      return *this;
+    }
+    bool operator!=(const const_iterator &o) const { return i_ != o.i_; }
+    bool operator==(const const_iterator &o) const { return i_ == o.i_; }
+  };
+  const_iterator begin() const { return const_iterator(this, 0); }
+  const_iterator end() const { return const_iterator(this, n_); }
+};
+
+// uid -> vertex number, sorted by uid
+class FlatIndex {
+  std::vector<std::pair<uint32_t, int>> v_;
+  std::vector<std::pair<uint32_t, int>>::const_iterator lower(uint32_t k) const {
+    return std::lower_bound(v_.begin(), v_.end(), k,
+                            [](const std::pair<uint32_t, int> &x, uint32_t key) { return x.first < key; });
+  }
+
+public:
+  int find(uint32_t k) const { // -1 if absent
+    auto it = lower(k);
+    return it == v_.end() || it->first != k ? -1 : it->second;
+  }
+  bool count(uint32_t k) const { return find(k) >= 0; }
+  // keeps an existing entry (like unordered_map::emplace)
+  void emplace(uint32_t k, int id) {
+    auto it = lower(k);
+    if (it != v_.end() && it->first == k) return;
+    v_.insert(it, std::make_pair(k, id));
+  }
+  void erase(uint32_t k) {
+    auto it = lower(k);
+    if (it != v_.end() && it->first == k) v_.erase(it);
+  }
+  void clear() { v_.clear(); }
+};
+} // namespace detail
+
 template <typename T> class Graph {
 public:
   using op_t = std::shared_ptr<T>;
   using vid_t = int;
+  using ids_t = detail::SmallIds<6>;
 
 private:
   struct Vertex {
     op_t op;
-    std::vector<vid_t> succs, preds;
+    ids_t succs, preds;
     bool alive = true;
   };
   std::vector<Vertex> v_;
-  std::unordered_map<uint32_t, vid_t> index_;  // op uid -> vertex
-  std::unordered_map<uint32_t, vid_t> uindex_; // op unbound uid -> vertex
+  detail::FlatIndex index_;  // op uid -> vertex
+  detail::FlatIndex uindex_; // op unbound uid -> vertex
   vid_t start_ = -1, finish_ = -1;
 
-  static void add_unique(std::vector<vid_t> &v, vid_t x) {
-    if (std::find(v.begin(), v.end(), x) == v.end()) v.push_back(x);
+  static void add_unique(ids_t &v, vid_t x) {
+    if (!v.contains(x)) v.push_back(x);
   }
-  static void remove_one(std::vector<vid_t> &v, vid_t x) {
-    v.erase(std::remove(v.begin(), v.end(), x), v.end());
-  }
+  static void remove_one(ids_t &v, vid_t x) { v.remove(x); }
   vid_t add_vertex(const op_t &op) {
-    auto it = index_.find(op->uid());
-    if (it != index_.end()) return it->second;
+    const vid_t have = index_.find(op->uid());
+    if (have >= 0) return have;
     vid_t id = static_cast<vid_t>(v_.size());
     v_.push_back(Vertex{op, {}, {}, true});
     index_.emplace(op->uid(), id);
@@ -56,9 +150,9 @@ private:
     add_unique(v_[a].succs, b);
     add_unique(v_[b].preds, a);
   }
-  std::vector<op_t> ops_of(const std::vector<vid_t> &ids) const {
+  std::vector<op_t> ops_of(const ids_t &ids) const {
     std::vector<op_t> r;
-    r.reserve(ids.size());
+    r.reserve(size_t(ids.size()));
     for (vid_t i : ids) r.push_back(v_[i].op);
     return r;
   }
@@ -118,15 +212,14 @@ public:
       if (v.alive) n += v.succs.size();
     return n;
   }
-  vid_t find_vertex(const OpBase &op) const {
-    auto it = index_.find(op.uid());
-    return it == index_.end() ? -1 : it->second;
-  }
+  vid_t find_vertex(const OpBase &op) const { return index_.find(op.uid()); }
   // vertex whose unbound identity equals op's unbound identity
-  vid_t find_vertex_unbound(const OpBase &op) const {
-    auto it = uindex_.find(op.unbound_uid());
-    return it == uindex_.end() ? -1 : it->second;
-  }
+  vid_t find_vertex_unbound(const OpBase &op) const { return uindex_.find(op.unbound_uid()); }
+  // by vertex number, for callers that walk the graph without copying op lists
+  const op_t &op_at(vid_t i) const { return v_[size_t(i)].op; }
+  const ids_t &pred_ids(vid_t i) const { return v_[size_t(i)].preds; }
+  const ids_t &succ_ids(vid_t i) const { return v_[size_t(i)].succs; }
+  size_t vertex_slots() const { return v_.size(); } // vertex numbers are < this (dead ones included)
   bool contains(const op_t &op) const { return op && find_vertex(*op) >= 0; }
   bool contains_unbound(const op_t &op) const { return op && find_vertex_unbound(*op) >= 0; }
   // the graph's own pointer for an op equal to `op` (null if absent)
@@ -210,20 +303,19 @@ public:
       if (!v_[i].alive) continue;
       for (vid_t s : v_[i].succs) {
         if (!live(s)) { err << v_[i].op->desc() << " has a dead successor"; return err.str(); }
-        if (std::find(v_[s].preds.begin(), v_[s].preds.end(), i) == v_[s].preds.end()) {
+        if (!v_[s].preds.contains(i)) {
           err << "edge " << v_[i].op->desc() << " -> " << v_[s].op->desc() << " has no mirror";
           return err.str();
         }
       }
       for (vid_t p : v_[i].preds) {
         if (!live(p)) { err << v_[i].op->desc() << " has a dead predecessor"; return err.str(); }
-        if (std::find(v_[p].succs.begin(), v_[p].succs.end(), i) == v_[p].succs.end()) {
+        if (!v_[p].succs.contains(i)) {
           err << "edge " << v_[p].op->desc() << " -> " << v_[i].op->desc() << " has no mirror";
           return err.str();
         }
       }
-      auto it = index_.find(v_[i].op->uid());
-      if (it == index_.end() || it->second != i) {
+      if (index_.find(v_[i].op->uid()) != i) {
         err << v_[i].op->desc() << " is not indexed";
         return err.str();
       }
@@ -304,7 +396,7 @@ public:
   Graph clone_but_expand(const op_t &op, const Graph &sub) const {
     Graph g(*this);
     const vid_t me = g.must_find(*op);
-    const std::vector<vid_t> myPreds = g.v_[me].preds, mySuccs = g.v_[me].succs;
+    const ids_t myPreds = g.v_[me].preds, mySuccs = g.v_[me].succs;
     g.erase_vertex(me);
     std::vector<vid_t> map(sub.v_.size(), -1);
     for (vid_t i = 0; i < static_cast<vid_t>(sub.v_.size()); ++i) {
@@ -381,6 +473,21 @@ public:
         }
       }
       if (ready) r.push_back(v_[i].op);
+    }
+    return r;
+  }
+  std::vector<vid_t> frontier_ids_of_mask(const std::vector<char> &isDone) const {
+    std::vector<vid_t> r;
+    for (vid_t i = 0; i < static_cast<vid_t>(v_.size()); ++i) {
+      if (!v_[i].alive || (size_t(i) < isDone.size() && isDone[size_t(i)])) continue;
+      bool ready = true;
+      for (vid_t p : v_[i].preds) {
+        if (!(size_t(p) < isDone.size() && isDone[size_t(p)])) {
+          ready = false;
+          break;
+        }
+      }
+      if (ready) r.push_back(i);
     }
     return r;
   }

@@ -137,7 +137,10 @@ public:
   std::string graphviz_name() const;
   std::string desc() const;
 
-  void ensure_children(const Platform &plat);
+  // `at`: the state of this node (its graph, the ops root..this) if the caller has it; a rollout
+  // walks down with one state and derives each level from the one above instead of rebuilding
+  // it from the root at every level
+  void ensure_children(const Platform &plat, const SDP::State *at = nullptr);
 };
 
 // exploit score in [0,1] (or +inf to force a child) plus per-rollout bookkeeping

@@ -75,6 +75,10 @@ class State {
   // which vertices the sequence has executed, by vertex number; extended like the digest
   mutable std::vector<char> done_;
   mutable size_t doneCounted_ = 0;
+  // what the synchronizer asks about the sequence, extended the same way
+  mutable PathIndex pathIndex_;
+  // frontier vertices already found synchronised with their predecessors (see get_decisions)
+  mutable std::vector<char> synced_;
 
   // same sequence (and its digest so far), other graph
   State with_graph(Graph<OpBase> &&g) const;

@@ -555,7 +555,13 @@ PYBIND11_MODULE(_C, m) {
       .def("is_terminal", &SDP::State::is_terminal)
       .def("canonical_key", [](const SDP::State &st) { return py::bytes(st.canonical_key()); },
            "opaque bytes: equal for states that differ only in the numbering of streams and events "
-           "(comparable within one process only)");
+           "(comparable within one process only)")
+      .def("canonical_hash",
+           [](const SDP::State &st) {
+             const StateKey k = st.canonical_hash();
+             return py::make_tuple(k.a, k.b);
+           },
+           "128-bit digest of the same canonical form (what the solvers de-duplicate on)");
   m.def("state_equivalence",
         [](const SDP::State &a, const SDP::State &b) { return SDP::get_equivalence(a, b); });
 

@@ -6,60 +6,69 @@
 namespace tenzing {
 
 // ---------------------------------------------------------------- PathIndex
-PathIndex::PathIndex(const Sequence<BoundOp> &path) {
-  struct Latest { int event, stream; size_t idx; };
-  std::vector<Latest> recordOf; // the latest record of each event: (stream, index in its stream's list)
-  auto latest = [&recordOf](int event) -> Latest * {
-    for (auto &r : recordOf)
+void PathIndex::append(const BoundOpPtr &op, int pos, bool sorted) {
+  auto put = [sorted](std::vector<std::pair<uint32_t, int>> &v, uint32_t id, int p) {
+    // (id, position) order: among equal ids the earliest position comes first, the one lookups return
+    if (sorted) v.insert(std::upper_bound(v.begin(), v.end(), std::make_pair(id, p)), std::make_pair(id, p));
+    else v.emplace_back(id, p);
+  };
+  put(byUid_, op->uid(), pos);
+  put(byUnbound_, op->unbound_uid(), pos);
+  const uint16_t t = op->traits();
+  if (!(t & op_trait::WithEvent)) return;
+  auto latest = [this](int event) -> Latest * {
+    for (auto &r : recordOf_)
       if (r.event == event) return &r;
     return nullptr;
   };
-  std::vector<char> used;
-  auto mark = [&](const Event &e) {
+  auto mark = [this](const Event &e) {
     if (e.id() < 0) return;
-    if (size_t(e.id()) >= used.size()) used.resize(size_t(e.id()) + 1, 0);
-    used[size_t(e.id())] = 1;
+    if (size_t(e.id()) >= used_.size()) used_.resize(size_t(e.id()) + 1, 0);
+    used_[size_t(e.id())] = 1;
   };
-  byUid_.reserve(path.size());
-  byUnbound_.reserve(path.size());
-  for (size_t i = 0; i < path.size(); ++i) {
-    const BoundOpPtr &op = path[i];
-    byUid_.emplace_back(op->uid(), int(i));
-    byUnbound_.emplace_back(op->unbound_uid(), int(i));
-    const uint16_t t = op->traits();
-    if (!(t & op_trait::WithEvent)) continue;
-    if (t & op_trait::EventRecord) {
-      auto cer = std::static_pointer_cast<CudaEventRecord>(op);
-      mark(cer->event());
-      auto &v = records_mut(cer->stream().id());
-      Record r;
-      r.pos = int(i);
-      r.event = cer->event();
-      r.op = cer;
-      if (Latest *l = latest(cer->event().id())) {
-        l->stream = cer->stream().id();
-        l->idx = v.size();
-      } else {
-        recordOf.push_back(Latest{cer->event().id(), cer->stream().id(), v.size()});
-      }
-      v.push_back(std::move(r));
-    } else if (t & op_trait::EventSync) {
-      const auto &ces = static_cast<const CudaEventSync &>(*op);
-      mark(ces.event());
-      if (const Latest *l = latest(ces.event().id())) records_mut(l->stream)[l->idx].hostSynced = true;
-    } else if (t & op_trait::StreamWaitEvent) {
-      const auto &w = static_cast<const CudaStreamWaitEvent &>(*op);
-      mark(w.event());
-      if (const Latest *l = latest(w.event().id()))
-        records_mut(l->stream)[l->idx].waiters.push_back(w.stream().id());
-    } else if (const auto *he = dynamic_cast<const HasEvent *>(op.get())) {
-      for (const Event &e : he->get_events()) mark(e);
+  if (t & op_trait::EventRecord) {
+    auto cer = std::static_pointer_cast<CudaEventRecord>(op);
+    mark(cer->event());
+    auto &v = records_mut(cer->stream().id());
+    Record r;
+    r.pos = pos;
+    r.event = cer->event();
+    r.op = cer;
+    if (Latest *l = latest(cer->event().id())) {
+      l->stream = cer->stream().id();
+      l->idx = v.size();
+    } else {
+      recordOf_.push_back(Latest{cer->event().id(), cer->stream().id(), v.size()});
     }
+    v.push_back(std::move(r));
+  } else if (t & op_trait::EventSync) {
+    const auto &ces = static_cast<const CudaEventSync &>(*op);
+    mark(ces.event());
+    if (const Latest *l = latest(ces.event().id())) records_mut(l->stream)[l->idx].hostSynced = true;
+  } else if (t & op_trait::StreamWaitEvent) {
+    const auto &w = static_cast<const CudaStreamWaitEvent &>(*op);
+    mark(w.event());
+    if (const Latest *l = latest(w.event().id()))
+      records_mut(l->stream)[l->idx].waiters.push_back(w.stream().id());
+  } else if (const auto *he = dynamic_cast<const HasEvent *>(op.get())) {
+    for (const Event &e : he->get_events()) mark(e);
   }
-  // (id, position) order: among equal ids the earliest position comes first, the one lookups return
-  std::sort(byUid_.begin(), byUid_.end());
-  std::sort(byUnbound_.begin(), byUnbound_.end());
-  while (size_t(nextEvent_) < used.size() && used[size_t(nextEvent_)]) ++nextEvent_;
+}
+
+void PathIndex::extend(const Sequence<BoundOp> &path) {
+  if (path.size() <= n_) return;
+  // a few new ops are inserted in place; a long stretch is appended and sorted once
+  const bool bulk = path.size() - n_ > 8;
+  if (bulk) {
+    byUid_.reserve(path.size());
+    byUnbound_.reserve(path.size());
+  }
+  for (; n_ < path.size(); ++n_) append(path[n_], int(n_), !bulk);
+  if (bulk) {
+    std::sort(byUid_.begin(), byUid_.end());
+    std::sort(byUnbound_.begin(), byUnbound_.end());
+  }
+  while (size_t(nextEvent_) < used_.size() && used_[size_t(nextEvent_)]) ++nextEvent_;
 }
 
 std::vector<PathIndex::Record> &PathIndex::records_mut(int stream) {
@@ -97,9 +106,9 @@ int index_of(const PathIndex &idx, const OpBase &a) {
 }
 
 // first CudaEventRecord on `stream` at or after position `from`
-std::shared_ptr<CudaEventRecord> first_record(const PathIndex &idx, int from, const Stream &stream) {
+const std::shared_ptr<CudaEventRecord> *first_record(const PathIndex &idx, int from, const Stream &stream) {
   for (const auto &r : idx.records(stream))
-    if (r.pos >= from) return r.op;
+    if (r.pos >= from) return &r.op;
   return nullptr;
 }
 
@@ -122,87 +131,79 @@ bool stream_waited(const PathIndex &idx, int ai, const Stream &stream, const Str
 
 enum class Need { None, GpuThenCpu, GpuThenGpu };
 
-struct PredInfo {
-  Need need = Need::None;
-  std::shared_ptr<BoundGpuOp> pGpu;
-};
-
-PredInfo classify(const BoundOpPtr &pred, const BoundOpPtr &bo) {
-  PredInfo r;
-  // runs once per (frontier op, predecessor) pair of every decision: cached type bits, no casts
-  const uint16_t pt = pred->traits(), bt = bo->traits();
+// Runs once per (frontier op, predecessor) pair of every decision: cached type bits, no casts,
+// no reference counting.
+Need classify(const BoundOp &pred, const BoundOp &bo) {
+  const uint16_t pt = pred.traits(), bt = bo.traits();
   const bool bIsGpu = (bt & op_trait::BoundGpu) != 0;
   if (!(pt & op_trait::BoundGpu)) {
-    if (pt & op_trait::IsStart) return r;
-    if ((pt & op_trait::Cpu) && (bIsGpu || (bt & op_trait::Cpu))) return r; // CPU -> anything: the host issues in order
-    THROW_RUNTIME("unexpected op combination: " << pred->desc() << " -> " << bo->desc());
+    if (pt & op_trait::IsStart) return Need::None;
+    if ((pt & op_trait::Cpu) && (bIsGpu || (bt & op_trait::Cpu))) return Need::None; // the host issues in order
+    THROW_RUNTIME("unexpected op combination: " << pred.desc() << " -> " << bo.desc());
   }
-  r.pGpu = std::static_pointer_cast<BoundGpuOp>(pred);
   if (bIsGpu) {
     // a flag-driven consumer only needs its GPU predecessors issued earlier, which the
     // sequence order already guarantees
-    if (static_cast<const BoundGpuOp &>(*bo).unbound()->issue_order_only()) return r;
-    r.need = Need::GpuThenGpu;
-    return r;
+    if (static_cast<const BoundGpuOp &>(bo).unbound()->issue_order_only()) return Need::None;
+    return Need::GpuThenGpu;
   }
-  if (bt & op_trait::Cpu) {
-    r.need = Need::GpuThenCpu;
-    return r;
-  }
-  THROW_RUNTIME("unexpected op combination: " << pred->desc() << " -> " << bo->desc());
+  if (bt & op_trait::Cpu) return Need::GpuThenCpu;
+  THROW_RUNTIME("unexpected op combination: " << pred.desc() << " -> " << bo.desc());
 }
 
-// graph predecessors of bo, as the bound ops found in the path
-std::vector<BoundOpPtr> preds_in_path(const BoundOpPtr &bo, const Graph<OpBase> &g, const Path &path,
-                                      const PathIndex &idx) {
-  auto found = g.preds_find_or_find_unbound(bo);
-  if (!found.first) THROW_RUNTIME("couldn't find " << bo->desc() << " in graph");
-  std::vector<BoundOpPtr> r;
-  for (const auto &gp : found.second) {
+// fn(pred) for every graph predecessor of bo, as the bound op found in the path; stops when fn
+// returns false.  Walks vertex numbers: no op lists are copied.
+template <typename Fn>
+void each_pred_in_path(const BoundOpPtr &bo, const Graph<OpBase> &g, const Path &path,
+                       const PathIndex &idx, Fn &&fn) {
+  const int v = g.find_vertex_unbound(*bo);
+  if (v < 0) THROW_RUNTIME("couldn't find " << bo->desc() << " in graph");
+  for (int p : g.pred_ids(v)) {
+    const OpPtr &gp = g.op_at(p);
     const int i = idx.pos_of_unbound(*gp);
     if (i < 0)
       THROW_RUNTIME("couldn't find " << gp->desc() << " in path (pred of " << bo->desc() << ")");
-    r.push_back(path[size_t(i)]);
+    if (!fn(path[size_t(i)])) return;
   }
-  return r;
 }
 
-bool synced_gpu_cpu(const std::shared_ptr<BoundGpuOp> &a, const PathIndex &idx) {
-  return host_waited(idx, index_of(idx, *a), a->stream());
+bool synced_gpu_cpu(const BoundGpuOp &a, const PathIndex &idx) {
+  return host_waited(idx, index_of(idx, a), a.stream());
 }
 
-bool synced_gpu_gpu(const std::shared_ptr<BoundGpuOp> &a, const std::shared_ptr<BoundGpuOp> &b,
-                    const PathIndex &idx) {
-  if (a->stream() == b->stream()) return true;
-  return stream_waited(idx, index_of(idx, *a), a->stream(), b->stream());
+bool synced_gpu_gpu(const BoundGpuOp &a, const BoundGpuOp &b, const PathIndex &idx) {
+  if (a.stream() == b.stream()) return true;
+  return stream_waited(idx, index_of(idx, a), a.stream(), b.stream());
 }
 
-BoundOpPtr sync_gpu_cpu(const std::shared_ptr<BoundGpuOp> &a, const std::shared_ptr<CpuOp> &b,
-                        const PathIndex &idx) {
-  const int ai = index_of(idx, *a);
-  if (host_waited(idx, ai, a->stream())) return nullptr;
-  if (auto cer = first_record(idx, ai, a->stream())) {
-    auto ces = std::make_shared<CudaEventSync>(cer->event());
-    ces->update_name({}, {b});
+// `aPtr` / `bPtr` own a and b; they are only needed to name a new op after its neighbours
+BoundOpPtr sync_gpu_cpu(const BoundOpPtr &aPtr, const BoundOpPtr &bPtr, const PathIndex &idx) {
+  const auto &a = static_cast<const BoundGpuOp &>(*aPtr);
+  const int ai = index_of(idx, a);
+  if (host_waited(idx, ai, a.stream())) return nullptr;
+  if (const auto *cer = first_record(idx, ai, a.stream())) {
+    auto ces = std::make_shared<CudaEventSync>((*cer)->event());
+    ces->update_name({}, {bPtr});
     return ces;
   }
-  auto cer = std::make_shared<CudaEventRecord>(idx.new_unique_event(), a->stream());
-  cer->update_name({a}, {});
+  auto cer = std::make_shared<CudaEventRecord>(idx.new_unique_event(), a.stream());
+  cer->update_name({aPtr}, {});
   return cer;
 }
 
-BoundOpPtr sync_gpu_gpu(const std::shared_ptr<BoundGpuOp> &a, const std::shared_ptr<BoundGpuOp> &b,
-                        const PathIndex &idx) {
-  if (a->stream() == b->stream()) return nullptr;
-  const int ai = index_of(idx, *a);
-  if (stream_waited(idx, ai, a->stream(), b->stream())) return nullptr;
-  if (auto cer = first_record(idx, ai, a->stream())) {
-    auto w = std::make_shared<CudaStreamWaitEvent>(b->stream(), cer->event());
-    w->update_name({a}, {});
+BoundOpPtr sync_gpu_gpu(const BoundOpPtr &aPtr, const BoundOpPtr &bPtr, const PathIndex &idx) {
+  const auto &a = static_cast<const BoundGpuOp &>(*aPtr);
+  const auto &b = static_cast<const BoundGpuOp &>(*bPtr);
+  if (a.stream() == b.stream()) return nullptr;
+  const int ai = index_of(idx, a);
+  if (stream_waited(idx, ai, a.stream(), b.stream())) return nullptr;
+  if (const auto *cer = first_record(idx, ai, a.stream())) {
+    auto w = std::make_shared<CudaStreamWaitEvent>(b.stream(), (*cer)->event());
+    w->update_name({aPtr}, {});
     return w;
   }
-  auto cer = std::make_shared<CudaEventRecord>(idx.new_unique_event(), a->stream());
-  cer->update_name({}, {b});
+  auto cer = std::make_shared<CudaEventRecord>(idx.new_unique_event(), a.stream());
+  cer->update_name({}, {bPtr});
   return cer;
 }
 
@@ -210,14 +211,14 @@ BoundOpPtr sync_gpu_gpu(const std::shared_ptr<BoundGpuOp> &a, const std::shared_
 
 bool EventSynchronizer::is_synced_gpu_then_cpu(const std::shared_ptr<BoundGpuOp> &a,
                                                const Path &path) {
-  return synced_gpu_cpu(a, PathIndex(path));
+  return synced_gpu_cpu(*a, PathIndex(path));
 }
 
 bool EventSynchronizer::is_synced_gpu_then_gpu(const std::shared_ptr<BoundGpuOp> &a,
                                                const std::shared_ptr<BoundGpuOp> &b,
                                                const Path &path) {
   if (a->stream() == b->stream()) return true;
-  return synced_gpu_gpu(a, b, PathIndex(path));
+  return synced_gpu_gpu(*a, *b, PathIndex(path));
 }
 
 BoundOpPtr EventSynchronizer::make_sync_gpu_then_cpu(const std::shared_ptr<BoundGpuOp> &a,
@@ -238,15 +239,16 @@ bool EventSynchronizer::is_synced(const BoundOpPtr &bo, const Graph<OpBase> &g, 
 
 bool EventSynchronizer::is_synced(const BoundOpPtr &bo, const Graph<OpBase> &g, const Path &path,
                                   const PathIndex &idx) {
-  for (const BoundOpPtr &pred : preds_in_path(bo, g, path, idx)) {
-    const PredInfo info = classify(pred, bo);
-    if (info.need == Need::GpuThenCpu) {
-      if (!synced_gpu_cpu(info.pGpu, idx)) return false;
-    } else if (info.need == Need::GpuThenGpu) {
-      if (!synced_gpu_gpu(info.pGpu, std::static_pointer_cast<BoundGpuOp>(bo), idx)) return false;
-    }
-  }
-  return true;
+  bool ok = true;
+  each_pred_in_path(bo, g, path, idx, [&](const BoundOpPtr &pred) {
+    const Need need = classify(*pred, *bo);
+    if (need == Need::GpuThenCpu)
+      ok = synced_gpu_cpu(static_cast<const BoundGpuOp &>(*pred), idx);
+    else if (need == Need::GpuThenGpu)
+      ok = synced_gpu_gpu(static_cast<const BoundGpuOp &>(*pred), static_cast<const BoundGpuOp &>(*bo), idx);
+    return ok;
+  });
+  return ok;
 }
 
 std::vector<BoundOpPtr> EventSynchronizer::make_syncs(const BoundOpPtr &bo, const Graph<OpBase> &g,
@@ -258,20 +260,20 @@ std::vector<BoundOpPtr> EventSynchronizer::make_syncs(const BoundOpPtr &bo, cons
                                                       const Path &path, const PathIndex &idx,
                                                       bool quiet) {
   std::vector<BoundOpPtr> syncs;
-  for (const BoundOpPtr &pred : preds_in_path(bo, g, path, idx)) {
-    const PredInfo info = classify(pred, bo);
+  each_pred_in_path(bo, g, path, idx, [&](const BoundOpPtr &pred) {
+    const Need need = classify(*pred, *bo);
     BoundOpPtr s;
-    if (info.need == Need::GpuThenCpu) {
-      s = sync_gpu_cpu(info.pGpu, std::static_pointer_cast<CpuOp>(bo), idx);
-    } else if (info.need == Need::GpuThenGpu) {
-      s = sync_gpu_gpu(info.pGpu, std::static_pointer_cast<BoundGpuOp>(bo), idx);
-    }
+    if (need == Need::GpuThenCpu) s = sync_gpu_cpu(pred, bo, idx);
+    else if (need == Need::GpuThenGpu) s = sync_gpu_gpu(pred, bo, idx);
     if (s) {
       if (!quiet) TENZING_INFO("sync " << s->desc() << " for " << pred->desc() << " -> " << bo->desc());
-      syncs.push_back(s);
+      // several predecessors on one stream ask for the same op: keep the first
+      bool have = false;
+      for (const BoundOpPtr &o : syncs) have = have || o->uid() == s->uid();
+      if (!have) syncs.push_back(std::move(s));
     }
-  }
-  keep_uniques(syncs);
+    return true;
+  });
   return syncs;
 }
 

@@ -22,23 +22,32 @@ std::vector<BoundOpPtr> State::get_syncs_before_op(const BoundOpPtr &op) const {
 
 std::vector<DecisionPtr> State::get_decisions(const Platform &plat, bool quiet) const {
   std::vector<DecisionPtr> decisions;
-  std::unordered_set<uint32_t> offeredSyncs; // one ExecuteOp per distinct sync op
-  const PathIndex idx(sequence_);            // one pass over the path serves every frontier op
+  std::vector<uint32_t> offeredSyncs;        // one ExecuteOp per distinct sync op
+  pathIndex_.extend(sequence_);              // one index serves every frontier op; only new ops cost
+  const PathIndex &idx = pathIndex_;
   for (; doneCounted_ < sequence_.size(); ++doneCounted_) graph_->mark_done(done_, *sequence_[doneCounted_]);
-  for (const OpPtr &op : graph_->frontier_of_mask(done_)) {
+  if (synced_.size() < graph_->vertex_slots()) synced_.resize(graph_->vertex_slots(), 0);
+  for (const int v : graph_->frontier_ids_of_mask(done_)) {
+    const OpPtr &op = graph_->op_at(v);
     const uint16_t t = op->traits();
     if (t & op_trait::Bound) {
       const BoundOpPtr bop = std::static_pointer_cast<BoundOp>(op);
-      const std::vector<BoundOpPtr> syncs =
-          Synchronizer::is_synced(bop, *graph_, sequence_, idx)
-              ? std::vector<BoundOpPtr>{}
-              : Synchronizer::make_syncs(bop, *graph_, sequence_, idx, true);
+      // A frontier op that was synchronised with its predecessors stays so while the path only
+      // grows (its predecessors are all executed, and records and waits are never taken back),
+      // so the answer is kept per vertex and inherited by the states derived from this one.
+      std::vector<BoundOpPtr> syncs;
+      if (!synced_[size_t(v)]) {
+        syncs = Synchronizer::make_syncs(bop, *graph_, sequence_, idx, true); // empty iff synced
+        if (syncs.empty()) synced_[size_t(v)] = 1;
+      }
       if (syncs.empty()) {
         decisions.push_back(std::make_shared<ExecuteOp>(bop));
       } else {
-        for (const BoundOpPtr &s : syncs)
-          if (offeredSyncs.insert(s->uid()).second)
-            decisions.push_back(std::make_shared<ExecuteOp>(s));
+        for (const BoundOpPtr &s : syncs) {
+          if (std::find(offeredSyncs.begin(), offeredSyncs.end(), s->uid()) != offeredSyncs.end()) continue;
+          offeredSyncs.push_back(s->uid());
+          decisions.push_back(std::make_shared<ExecuteOp>(s));
+        }
       }
     } else if (t & op_trait::Gpu) {
       const auto gop = std::static_pointer_cast<GpuOp>(op);
@@ -65,6 +74,8 @@ State State::with_graph(Graph<OpBase> &&g) const {
   r.seqDigested_ = seqDigested_;
   r.done_ = done_; // vertex numbers survive the rewrite
   r.doneCounted_ = doneCounted_;
+  r.pathIndex_ = pathIndex_;
+  r.synced_ = synced_;
   return r;
 }
 

@@ -131,12 +131,16 @@ std::string Node::graphviz_label(const Strategy *strategy) const {
   return s;
 }
 
-void Node::ensure_children(const Platform &plat) {
+void Node::ensure_children(const Platform &plat, const SDP::State *at) {
   if (expanded_) return;
   expanded_ = true;
   if (is_terminal()) return;
-  const SDP::State state(graph(), get_sequence());
-  for (const DecisionPtr &d : state.get_decisions(plat)) {
+  std::unique_ptr<SDP::State> own;
+  if (!at) {
+    own.reset(new SDP::State(graph(), get_sequence()));
+    at = own.get();
+  }
+  for (const DecisionPtr &d : at->get_decisions(plat)) {
     if (d->kind() == Decision::Kind::ExecuteOp) {
       const auto &e = static_cast<const ExecuteOp &>(*d);
       children_.emplace_back(new Node(graph(), e.op, this));
@@ -181,15 +185,23 @@ Node::RolloutResult Node::get_rollout(const Platform &plat, std::mt19937_64 &rng
   RolloutResult res;
   if (parent_) res.sequence = parent_->get_sequence();
   if (expand) {
+    if (op_) res.sequence.push_back(op_);
+    SDP::State state(graph(), res.sequence); // of `cur`, derived level by level
     Node *cur = this;
     while (cur) {
       res.backpropStart = cur;
-      if (cur->op_) res.sequence.push_back(cur->op_);
-      cur->ensure_children(plat);
+      cur->ensure_children(plat, &state);
       if (cur->children_.empty()) break;
       cur = cur->children_[std::uniform_int_distribution<size_t>(0, cur->children_.size() - 1)(rng)]
                 .get();
+      if (cur->op_) {
+        state = state.apply(ExecuteOp(cur->op_));
+      } else {
+        state = state.apply(*cur->rewrite_);
+        if (!cur->graph_) cur->graph_ = state.graph_ptr(); // the revised graph, built once
+      }
     }
+    res.sequence = state.sequence();
   } else {
     // play out on states only; nothing below this node is kept
     if (op_) res.sequence.push_back(op_);

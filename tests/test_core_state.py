@@ -180,3 +180,71 @@ def test_get_frontier_legacy():
     assert sorted(o.desc() for o in fr) == ["a(s0)", "a(s1)"]
     fr = _C.mcts.get_frontier(plat, g, [g.start(), tz.BoundGpuOp(a, 0)])
     assert sorted(o.kind() for o in fr) == ["BoundGpuOp", "CudaEventRecord"]
+
+
+def _rollouts_agree_with_fresh_states(graph, plat, seed, rollouts=6):
+    """A state derived step by step carries caches from its ancestors (sequence digest, executed
+    and synchronised vertices, the path index); a state built from (graph, sequence) has none.
+    Both must offer the same decisions and have the same digest at every step."""
+    import random
+    rng = random.Random(seed)
+    for _ in range(rollouts):
+        st = tz.State(graph)
+        steps = 0
+        while not st.is_terminal():
+            fresh = tz.State(st.graph(), st.sequence())
+            got = [d.desc() for d in st.get_decisions(plat)]
+            want = [d.desc() for d in fresh.get_decisions(plat)]
+            assert got == want, (steps, got, want)
+            assert st.canonical_hash() == fresh.canonical_hash()
+            assert st.canonical_key() == fresh.canonical_key()
+            ds = st.get_decisions(plat)
+            st = st.apply(ds[rng.randrange(len(ds))])
+            steps += 1
+        assert steps > 0
+
+
+def test_derived_states_agree_with_fresh_ones_on_a_gpu_diamond():
+    a, b, c, d = (tz.EmptyGpuOp(n) for n in "abcd")
+    h = tz.NoOp("h")
+    g = tz.Graph()
+    g.start_then(a)
+    g.then(a, b)
+    g.then(a, c)
+    g.then(b, d)
+    g.then(c, d)
+    g.then(c, h)
+    g.then_finish(d)
+    g.then_finish(h)
+    for n_streams in (1, 2, 3):
+        _rollouts_agree_with_fresh_states(g, tz.Platform.make_null(n_streams), seed=n_streams)
+
+
+def test_derived_states_agree_with_fresh_ones_on_the_workload_graphs():
+    from tenzing_b200.models import DistributedSpMV, HaloExchange
+    s = DistributedSpMV(n=2000, nnz_per_row=6, host=True)
+    for style in ("reference", "choice"):
+        _rollouts_agree_with_fresh_states(s.graph(style), s.platform, seed=7, rollouts=3)
+    h = HaloExchange(nX=8, nQ=1, nGhost=1, n_streams=2, host=True)
+    for style in ("direct", "choice"):
+        _rollouts_agree_with_fresh_states(h.graph(style), h.platform, seed=11, rollouts=2)
+
+
+def test_equal_digests_iff_equal_keys_over_a_whole_enumeration():
+    a, b, c = (tz.EmptyGpuOp(n) for n in "abc")
+    g = tz.Graph()
+    g.start_then(a)
+    g.start_then(b)
+    g.then(a, c)
+    g.then(b, c)
+    g.then_finish(c)
+    plat = tz.Platform.make_null(2)
+    seen = {}
+    stack = [tz.State(g)]
+    while stack:
+        st = stack.pop()
+        k, h = st.canonical_key(), st.canonical_hash()
+        assert seen.setdefault(k, h) == h
+        if not st.is_terminal():
+            stack.extend(st.apply(d) for d in st.get_decisions(plat))
+    assert len(set(seen.values())) == len(seen) > 50
