@@ -10,13 +10,24 @@ namespace {
 
 using Seq = Sequence<BoundOp>;
 
-template <typename T> std::shared_ptr<T> as(const BoundOpPtr &p) {
-  return std::dynamic_pointer_cast<T>(p);
+// what an op of the sequence is, from its cached type bits: these scans run over every pair of
+// positions for every redundancy removed, so no reference counting and no failing casts
+template <typename T> const T *as(const BoundOpPtr &p);
+template <> const CudaEventRecord *as<CudaEventRecord>(const BoundOpPtr &p) {
+  return p->is(op_trait::EventRecord) ? static_cast<const CudaEventRecord *>(p.get()) : nullptr;
+}
+template <> const CudaEventSync *as<CudaEventSync>(const BoundOpPtr &p) {
+  return p->is(op_trait::EventSync) ? static_cast<const CudaEventSync *>(p.get()) : nullptr;
+}
+template <> const CudaStreamWaitEvent *as<CudaStreamWaitEvent>(const BoundOpPtr &p) {
+  return p->is(op_trait::StreamWaitEvent) ? static_cast<const CudaStreamWaitEvent *>(p.get()) : nullptr;
+}
+template <> const StreamSync *as<StreamSync>(const BoundOpPtr &p) {
+  return p->is(op_trait::Sync) ? dynamic_cast<const StreamSync *>(p.get()) : nullptr;
 }
 
 bool gpu_op_on_stream(const BoundOpPtr &op, const Stream &s) {
-  auto g = as<BoundGpuOp>(op);
-  return g && g->stream() == s;
+  return op->is(op_trait::BoundGpu) && static_cast<const BoundGpuOp &>(*op).stream() == s;
 }
 
 // positions of the waits that consume event e after position `from`
@@ -30,9 +41,7 @@ Consumers consumers_of(const Seq &o, size_t from, const Event &e) {
       if (ces->event() == e) c.hostSyncs.push_back(i);
     } else if (auto w = as<CudaStreamWaitEvent>(o[i])) {
       if (w->event() == e) c.streamWaits.push_back(i);
-    } else if (auto sw = as<StreamWait>(o[i])) {
-      (void)sw; // records its own event
-    }
+    } // a legacy StreamWait records and consumes its own event
   }
   return c;
 }
