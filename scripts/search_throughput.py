@@ -7,6 +7,8 @@ Both arms enumerate every schedule of the same graphs through their public DFS e
 (K*L)! / (L!)^K schedules.  The reference side is baseline/ref_driver/ref_enum.cu built against
 the reference by baseline/build_ref.py; both run on this machine, one thread.
 
+A second section times MCTS playouts on the workload graphs (this framework only).
+
   python scripts/search_throughput.py [--out profiles/search_throughput.txt]
 """
 import argparse
@@ -81,6 +83,26 @@ def main():
         lines.append(f"{K} {L} {want} {n_o} {t_o:.6f} {n_r} {t_r_s} {ratio}")
         print(lines[-1], flush=True)
         assert n_o == want, "this framework's enumeration is wrong"
+    # MCTS playouts on the workload graphs (this framework only: the reference's MCTS cannot finish a
+    # rollout as shipped).  A constant-cost benchmarker, so the time is the search's own.
+    import tenzing_b200 as tz
+    from tenzing_b200 import _C
+    from tenzing_b200.models import DistributedSpMV, HaloExchange
+    lines.append("# MCTS (FastMin, rollouts expanded into the tree), constant-cost benchmarker: workload style ops_per_schedule rollouts ms_per_rollout")
+    halo = HaloExchange(nX=16, nQ=1, nGhost=1, n_streams=2, host=True)
+    spmv = DistributedSpMV(n=4000, nnz_per_row=6, host=True)
+    for name, wl, style in (("halo", halo, "reference"), ("halo", halo, "direct"), ("halo", halo, "choice"),
+                            ("spmv", spmv, "reference"), ("spmv", spmv, "choice")):
+        g = wl.graph(style)
+        opts = _C.mcts.Opts()
+        opts.n_iters = 200
+        t0 = time.perf_counter()
+        res = _C.mcts.explore(g, wl.platform, tz.PyBenchmarker(lambda s: 1.0), "FastMin", opts)
+        dt = time.perf_counter() - t0
+        n = len(res.sim_results)
+        ops = max(len(r.path) for r in res.sim_results)
+        lines.append(f"{name} {style} {ops} {n} {dt / n * 1e3:.3f}")
+        print(lines[-1], flush=True)
     if args.out:
         with open(os.path.join(ROOT, args.out), "w") as f:
             f.write("\n".join(lines) + "\n")
