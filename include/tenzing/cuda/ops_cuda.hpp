@@ -71,12 +71,33 @@ using OpSet = std::vector<std::shared_ptr<const OpBase>>;
 
 class SyncOpBase : public BoundOp {
 protected:
-  std::string name_;
-  void make_name(const char *prefix, const OpSet &preds, const OpSet &succs);
+  // The search makes a synchronisation op for every candidate placement and executes a few of
+  // them; the descriptive name (prefix + the neighbours' names) is only put together when
+  // somebody asks for it.  Identity does not depend on it (key() is kind + event/stream).
+  mutable std::string name_;
+  mutable const char *pendingPrefix_ = nullptr;
+  mutable OpSet pendingPreds_, pendingSuccs_;
+  void make_name(const char *prefix, const OpSet &preds, const OpSet &succs) {
+    pendingPrefix_ = prefix;
+    pendingPreds_ = preds;
+    pendingSuccs_ = succs;
+  }
+  void build_name() const;
+  // identity of an op that is fully described by a kind and two small integers, without
+  // building and hashing its key string on every new object (src/core/operation.cpp)
+  static uint32_t intern_small(char kindTag, int a, int b, const OpBase &op);
 
 public:
-  std::string name() const override { return name_; }
-  void set_name(const std::string &n) { name_ = n; }
+  std::string name() const override {
+    if (pendingPrefix_) build_name();
+    return name_;
+  }
+  void set_name(const std::string &n) {
+    name_ = n;
+    pendingPrefix_ = nullptr;
+    pendingPreds_.clear();
+    pendingSuccs_.clear();
+  }
 };
 
 class CudaEventRecord final : public SyncOpBase, public HasEvent, public HasStream {
@@ -90,8 +111,10 @@ public:
   }
   std::string kind() const override { return "CudaEventRecord"; }
   std::string key() const override { return "CER:e" + event_.str() + ":s" + stream_.str(); }
+  uint32_t intern_self() const override { return intern_small('R', event_.id(), stream_.id(), *this); }
+  uint32_t intern_unbound_self() const override { return uid(); }
   std::string desc() const override {
-    return name_ + "(e" + event_.str() + ",s" + stream_.str() + ")";
+    return name() + "(e" + event_.str() + ",s" + stream_.str() + ")";
   }
   Json json() const override;
   CLONE_DEF(CudaEventRecord)
@@ -114,8 +137,10 @@ public:
   }
   std::string kind() const override { return "CudaStreamWaitEvent"; }
   std::string key() const override { return "CSWE:s" + stream_.str() + ":e" + event_.str(); }
+  uint32_t intern_self() const override { return intern_small('W', stream_.id(), event_.id(), *this); }
+  uint32_t intern_unbound_self() const override { return uid(); }
   std::string desc() const override {
-    return name_ + "(s" + stream_.str() + ",e" + event_.str() + ")";
+    return name() + "(s" + stream_.str() + ",e" + event_.str() + ")";
   }
   Json json() const override;
   CLONE_DEF(CudaStreamWaitEvent)
@@ -136,7 +161,9 @@ public:
   }
   std::string kind() const override { return "CudaEventSync"; }
   std::string key() const override { return "CES:e" + event_.str(); }
-  std::string desc() const override { return name_ + "(e" + event_.str() + ")"; }
+  uint32_t intern_self() const override { return intern_small('S', event_.id(), 0, *this); }
+  uint32_t intern_unbound_self() const override { return uid(); }
+  std::string desc() const override { return name() + "(e" + event_.str() + ")"; }
   Json json() const override;
   CLONE_DEF(CudaEventSync)
   void update_name(const OpSet &preds, const OpSet &succs) { make_name("CES", preds, succs); }

@@ -123,12 +123,21 @@ public:
   using ids_t = detail::SmallIds<6>;
 
 private:
-  struct Vertex {
-    op_t op;
+  // A vertex is a slot number.  The op table belongs to the graph; the edges live in a block
+  // that a graph shares with its copies until one of them changes an edge: binding an op to a
+  // stream or choosing an alternative (the bulk of the search's rewrites) copies the op table
+  // and the indexes, and no adjacency list.
+  struct Adj {
     ids_t succs, preds;
     bool alive = true;
   };
-  std::vector<Vertex> v_;
+  std::vector<op_t> ops_;
+  std::shared_ptr<std::vector<Adj>> adj_ = std::make_shared<std::vector<Adj>>();
+  const std::vector<Adj> &adj() const { return *adj_; }
+  std::vector<Adj> &adj_mut() {
+    if (adj_.use_count() > 1) adj_ = std::make_shared<std::vector<Adj>>(*adj_);
+    return *adj_;
+  }
   detail::FlatIndex index_;  // op uid -> vertex
   detail::FlatIndex uindex_; // op unbound uid -> vertex
   vid_t start_ = -1, finish_ = -1;
@@ -140,20 +149,23 @@ private:
   vid_t add_vertex(const op_t &op) {
     const vid_t have = index_.find(op->uid());
     if (have >= 0) return have;
-    vid_t id = static_cast<vid_t>(v_.size());
-    v_.push_back(Vertex{op, {}, {}, true});
+    vid_t id = static_cast<vid_t>(ops_.size());
+    ops_.push_back(op);
+    adj_mut().push_back(Adj{});
     index_.emplace(op->uid(), id);
     uindex_.emplace(op->unbound_uid(), id);
     return id;
   }
   void add_edge(vid_t a, vid_t b) {
-    add_unique(v_[a].succs, b);
-    add_unique(v_[b].preds, a);
+    if (adj()[a].succs.contains(b) && adj()[b].preds.contains(a)) return;
+    auto &m = adj_mut();
+    add_unique(m[a].succs, b);
+    add_unique(m[b].preds, a);
   }
   std::vector<op_t> ops_of(const ids_t &ids) const {
     std::vector<op_t> r;
     r.reserve(size_t(ids.size()));
-    for (vid_t i : ids) r.push_back(v_[i].op);
+    for (vid_t i : ids) r.push_back(ops_[i]);
     return r;
   }
   vid_t must_find(const OpBase &op) const {
@@ -169,24 +181,24 @@ public:
   }
 
   // ---- construction ----
-  const op_t &start() const { return v_[start_].op; }
-  const op_t &finish() const { return v_[finish_].op; }
+  const op_t &start() const { return ops_[start_]; }
+  const op_t &finish() const { return ops_[finish_]; }
 
   // Start -> op
   const op_t &start_then(const op_t &op) {
     vid_t b = add_vertex(op);
     add_edge(start_, b);
-    return v_[b].op;
+    return ops_[b];
   }
   // a -> b; neither may be Start or Finish (use start_then / then_finish)
   const op_t &then(const op_t &a, const op_t &b) {
-    if (a->uid() == v_[start_].op->uid() || a->uid() == v_[finish_].op->uid() ||
-        b->uid() == v_[start_].op->uid() || b->uid() == v_[finish_].op->uid()) {
+    if (a->uid() == ops_[start_]->uid() || a->uid() == ops_[finish_]->uid() ||
+        b->uid() == ops_[start_]->uid() || b->uid() == ops_[finish_]->uid()) {
       THROW_RUNTIME("Graph::then does not take Start/Finish; use start_then/then_finish");
     }
     vid_t ia = add_vertex(a), ib = add_vertex(b);
     add_edge(ia, ib);
-    return v_[ib].op;
+    return ops_[ib];
   }
   // op -> Finish
   void then_finish(const op_t &op) {
@@ -203,89 +215,89 @@ public:
   // ---- queries ----
   size_t vertex_size() const {
     size_t n = 0;
-    for (const auto &v : v_) n += v.alive;
+    for (const auto &a : adj()) n += a.alive;
     return n;
   }
   size_t edge_size() const {
     size_t n = 0;
-    for (const auto &v : v_)
-      if (v.alive) n += v.succs.size();
+    for (const auto &a : adj())
+      if (a.alive) n += a.succs.size();
     return n;
   }
   vid_t find_vertex(const OpBase &op) const { return index_.find(op.uid()); }
   // vertex whose unbound identity equals op's unbound identity
   vid_t find_vertex_unbound(const OpBase &op) const { return uindex_.find(op.unbound_uid()); }
   // by vertex number, for callers that walk the graph without copying op lists
-  const op_t &op_at(vid_t i) const { return v_[size_t(i)].op; }
-  const ids_t &pred_ids(vid_t i) const { return v_[size_t(i)].preds; }
-  const ids_t &succ_ids(vid_t i) const { return v_[size_t(i)].succs; }
-  size_t vertex_slots() const { return v_.size(); } // vertex numbers are < this (dead ones included)
+  const op_t &op_at(vid_t i) const { return ops_[size_t(i)]; }
+  const ids_t &pred_ids(vid_t i) const { return adj()[size_t(i)].preds; }
+  const ids_t &succ_ids(vid_t i) const { return adj()[size_t(i)].succs; }
+  size_t vertex_slots() const { return ops_.size(); } // vertex numbers are < this (dead ones included)
   bool contains(const op_t &op) const { return op && find_vertex(*op) >= 0; }
   bool contains_unbound(const op_t &op) const { return op && find_vertex_unbound(*op) >= 0; }
   // the graph's own pointer for an op equal to `op` (null if absent)
   op_t find(const op_t &op) const {
     vid_t i = find_vertex(*op);
-    return i < 0 ? nullptr : v_[i].op;
+    return i < 0 ? nullptr : ops_[i];
   }
   op_t find_unbound(const op_t &op) const {
     vid_t i = find_vertex_unbound(*op);
-    return i < 0 ? nullptr : v_[i].op;
+    return i < 0 ? nullptr : ops_[i];
   }
   op_t find_name(const std::string &name) const {
-    for (const auto &v : v_)
-      if (v.alive && v.op->name() == name) return v.op;
+    for (size_t i = 0; i < ops_.size(); ++i)
+      if (adj()[i].alive && ops_[i]->name() == name) return ops_[i];
     return nullptr;
   }
 
   std::vector<op_t> vertices() const {
     std::vector<op_t> r;
-    for (const auto &v : v_)
-      if (v.alive) r.push_back(v.op);
+    for (size_t i = 0; i < ops_.size(); ++i)
+      if (adj()[i].alive) r.push_back(ops_[i]);
     return r;
   }
   template <typename U> std::vector<std::shared_ptr<U>> nodes_cast() const {
     std::vector<std::shared_ptr<U>> r;
-    for (const auto &v : v_)
-      if (v.alive)
-        if (auto p = std::dynamic_pointer_cast<U>(v.op)) r.push_back(p);
+    for (size_t i = 0; i < ops_.size(); ++i)
+      if (adj()[i].alive)
+        if (auto p = std::dynamic_pointer_cast<U>(ops_[i])) r.push_back(p);
     return r;
   }
-  std::vector<op_t> start_vertices() const { return ops_of(v_[start_].succs); }
-  std::vector<op_t> finish_vertices() const { return ops_of(v_[finish_].preds); }
+  std::vector<op_t> start_vertices() const { return ops_of(adj()[start_].succs); }
+  std::vector<op_t> finish_vertices() const { return ops_of(adj()[finish_].preds); }
 
-  std::vector<op_t> succs(const op_t &op) const { return ops_of(v_[must_find(*op)].succs); }
-  std::vector<op_t> preds(const op_t &op) const { return ops_of(v_[must_find(*op)].preds); }
+  std::vector<op_t> succs(const op_t &op) const { return ops_of(adj()[must_find(*op)].succs); }
+  std::vector<op_t> preds(const op_t &op) const { return ops_of(adj()[must_find(*op)].preds); }
   std::vector<op_t> succs_vec(const op_t &op) const { return succs(op); }
   std::vector<op_t> preds_vec(const op_t &op) const { return preds(op); }
   // (found, list) - `found` false when the op is not a vertex
   std::pair<bool, std::vector<op_t>> preds_find(const op_t &op) const {
     vid_t i = find_vertex(*op);
     return i < 0 ? std::make_pair(false, std::vector<op_t>{})
-                 : std::make_pair(true, ops_of(v_[i].preds));
+                 : std::make_pair(true, ops_of(adj()[i].preds));
   }
   std::pair<bool, std::vector<op_t>> succs_find(const op_t &op) const {
     vid_t i = find_vertex(*op);
     return i < 0 ? std::make_pair(false, std::vector<op_t>{})
-                 : std::make_pair(true, ops_of(v_[i].succs));
+                 : std::make_pair(true, ops_of(adj()[i].succs));
   }
   std::pair<bool, std::vector<op_t>> preds_find_or_find_unbound(const op_t &op) const {
     vid_t i = find_vertex_unbound(*op);
     return i < 0 ? std::make_pair(false, std::vector<op_t>{})
-                 : std::make_pair(true, ops_of(v_[i].preds));
+                 : std::make_pair(true, ops_of(adj()[i].preds));
   }
   std::pair<bool, std::vector<op_t>> succs_find_or_find_unbound(const op_t &op) const {
     vid_t i = find_vertex_unbound(*op);
     return i < 0 ? std::make_pair(false, std::vector<op_t>{})
-                 : std::make_pair(true, ops_of(v_[i].succs));
+                 : std::make_pair(true, ops_of(adj()[i].succs));
   }
   std::pair<bool, std::vector<op_t>> succs_find_name(const std::string &name) const {
-    for (const auto &v : v_)
-      if (v.alive && v.op->name() == name) return {true, ops_of(v.succs)};
+    for (size_t i = 0; i < ops_.size(); ++i)
+      if (adj()[i].alive && ops_[i]->name() == name) return {true, ops_of(adj()[i].succs)};
     return {false, {}};
   }
   std::pair<bool, std::vector<op_t>> preds_find_name(const std::string &name) const {
-    for (const auto &v : v_)
-      if (v.alive && v.op->name() == name) return {true, ops_of(v.preds)};
+    for (size_t i = 0; i < ops_.size(); ++i)
+      if (adj()[i].alive && ops_[i]->name() == name) return {true, ops_of(adj()[i].preds)};
     return {false, {}};
   }
 
@@ -296,47 +308,47 @@ public:
   // Builds with TENZING_RUNTIME_SANITY_CHECKS run it after every rewrite (reference:
   // CMakeLists.txt always defines that macro; here it is an option, off by default).
   std::string validate() const {
-    const vid_t n = static_cast<vid_t>(v_.size());
+    const vid_t n = static_cast<vid_t>(ops_.size());
     std::ostringstream err;
-    auto live = [&](vid_t i) { return i >= 0 && i < n && v_[i].alive; };
+    auto live = [&](vid_t i) { return i >= 0 && i < n && adj()[i].alive; };
     for (vid_t i = 0; i < n; ++i) {
-      if (!v_[i].alive) continue;
-      for (vid_t s : v_[i].succs) {
-        if (!live(s)) { err << v_[i].op->desc() << " has a dead successor"; return err.str(); }
-        if (!v_[s].preds.contains(i)) {
-          err << "edge " << v_[i].op->desc() << " -> " << v_[s].op->desc() << " has no mirror";
+      if (!adj()[i].alive) continue;
+      for (vid_t s : adj()[i].succs) {
+        if (!live(s)) { err << ops_[i]->desc() << " has a dead successor"; return err.str(); }
+        if (!adj()[s].preds.contains(i)) {
+          err << "edge " << ops_[i]->desc() << " -> " << ops_[s]->desc() << " has no mirror";
           return err.str();
         }
       }
-      for (vid_t p : v_[i].preds) {
-        if (!live(p)) { err << v_[i].op->desc() << " has a dead predecessor"; return err.str(); }
-        if (!v_[p].succs.contains(i)) {
-          err << "edge " << v_[p].op->desc() << " -> " << v_[i].op->desc() << " has no mirror";
+      for (vid_t p : adj()[i].preds) {
+        if (!live(p)) { err << ops_[i]->desc() << " has a dead predecessor"; return err.str(); }
+        if (!adj()[p].succs.contains(i)) {
+          err << "edge " << ops_[p]->desc() << " -> " << ops_[i]->desc() << " has no mirror";
           return err.str();
         }
       }
-      if (index_.find(v_[i].op->uid()) != i) {
-        err << v_[i].op->desc() << " is not indexed";
+      if (index_.find(ops_[i]->uid()) != i) {
+        err << ops_[i]->desc() << " is not indexed";
         return err.str();
       }
     }
     if (!live(start_) || !live(finish_)) return "Start or Finish missing";
-    if (!v_[start_].preds.empty()) return "an edge enters Start";
-    if (!v_[finish_].succs.empty()) return "an edge leaves Finish";
+    if (!adj()[start_].preds.empty()) return "an edge enters Start";
+    if (!adj()[finish_].succs.empty()) return "an edge leaves Finish";
     // Kahn: all live vertices must come out, and only Start may have no predecessor
     std::vector<int> indeg(n, 0);
     std::vector<vid_t> ready;
     size_t nLive = 0, seen = 0;
     for (vid_t i = 0; i < n; ++i) {
-      if (!v_[i].alive) continue;
+      if (!adj()[i].alive) continue;
       ++nLive;
-      indeg[i] = int(v_[i].preds.size());
+      indeg[i] = int(adj()[i].preds.size());
       if (indeg[i] == 0) {
-        if (i != start_) { err << v_[i].op->desc() << " is not reachable from Start"; return err.str(); }
+        if (i != start_) { err << ops_[i]->desc() << " is not reachable from Start"; return err.str(); }
         ready.push_back(i);
       }
-      if (v_[i].succs.empty() && i != finish_) {
-        err << v_[i].op->desc() << " does not lead to Finish";
+      if (adj()[i].succs.empty() && i != finish_) {
+        err << ops_[i]->desc() << " does not lead to Finish";
         return err.str();
       }
     }
@@ -344,7 +356,7 @@ public:
       vid_t i = ready.back();
       ready.pop_back();
       ++seen;
-      for (vid_t s : v_[i].succs)
+      for (vid_t s : adj()[i].succs)
         if (--indeg[s] == 0) ready.push_back(s);
     }
     if (seen != nLive) return "the graph has a cycle";
@@ -365,11 +377,11 @@ public:
     Graph g(*this);
     g.index_.clear();
     g.uindex_.clear();
-    for (vid_t i = 0; i < static_cast<vid_t>(g.v_.size()); ++i) {
-      if (!g.v_[i].alive) continue;
-      g.v_[i].op = std::dynamic_pointer_cast<T>(v_[i].op->clone());
-      g.index_.emplace(g.v_[i].op->uid(), i);
-      g.uindex_.emplace(g.v_[i].op->unbound_uid(), i);
+    for (vid_t i = 0; i < static_cast<vid_t>(g.ops_.size()); ++i) {
+      if (!g.adj()[i].alive) continue;
+      g.ops_[i] = std::dynamic_pointer_cast<T>(ops_[i]->clone());
+      g.index_.emplace(g.ops_[i]->uid(), i);
+      g.uindex_.emplace(g.ops_[i]->unbound_uid(), i);
     }
     return g;
   }
@@ -378,9 +390,9 @@ public:
     vid_t i = must_find(*src);
     if (dst->uid() != src->uid() && index_.count(dst->uid()))
       THROW_RUNTIME("replacement " << dst->desc() << " is already in the graph");
-    index_.erase(v_[i].op->uid());
-    uindex_.erase(v_[i].op->unbound_uid());
-    v_[i].op = dst;
+    index_.erase(ops_[i]->uid());
+    uindex_.erase(ops_[i]->unbound_uid());
+    ops_[i] = dst;
     index_.emplace(dst->uid(), i);
     uindex_.emplace(dst->unbound_uid(), i);
   }
@@ -396,32 +408,32 @@ public:
   Graph clone_but_expand(const op_t &op, const Graph &sub) const {
     Graph g(*this);
     const vid_t me = g.must_find(*op);
-    const ids_t myPreds = g.v_[me].preds, mySuccs = g.v_[me].succs;
+    const ids_t myPreds = g.adj()[me].preds, mySuccs = g.adj()[me].succs;
     g.erase_vertex(me);
-    std::vector<vid_t> map(sub.v_.size(), -1);
-    for (vid_t i = 0; i < static_cast<vid_t>(sub.v_.size()); ++i) {
-      if (!sub.v_[i].alive || i == sub.start_ || i == sub.finish_) continue;
-      if (g.index_.count(sub.v_[i].op->uid()))
-        THROW_RUNTIME("expanding " << op->name() << ": inner op " << sub.v_[i].op->name()
+    std::vector<vid_t> map(sub.ops_.size(), -1);
+    for (vid_t i = 0; i < static_cast<vid_t>(sub.ops_.size()); ++i) {
+      if (!sub.adj()[i].alive || i == sub.start_ || i == sub.finish_) continue;
+      if (g.index_.count(sub.ops_[i]->uid()))
+        THROW_RUNTIME("expanding " << op->name() << ": inner op " << sub.ops_[i]->name()
                                    << " already exists in the outer graph");
-      map[i] = g.add_vertex(sub.v_[i].op);
+      map[i] = g.add_vertex(sub.ops_[i]);
     }
-    for (vid_t i = 0; i < static_cast<vid_t>(sub.v_.size()); ++i) {
+    for (vid_t i = 0; i < static_cast<vid_t>(sub.ops_.size()); ++i) {
       if (map[i] < 0) continue;
-      for (vid_t s : sub.v_[i].succs) {
+      for (vid_t s : sub.adj()[i].succs) {
         if (s == sub.finish_) {
           for (vid_t o : mySuccs) g.add_edge(map[i], o);
         } else {
           g.add_edge(map[i], map[s]);
         }
       }
-      for (vid_t p : sub.v_[i].preds) {
+      for (vid_t p : sub.adj()[i].preds) {
         if (p == sub.start_)
           for (vid_t o : myPreds) g.add_edge(o, map[i]);
       }
     }
     // an empty compound (Start -> Finish) collapses to direct edges
-    for (vid_t s : sub.v_[sub.start_].succs)
+    for (vid_t s : sub.adj()[sub.start_].succs)
       if (s == sub.finish_)
         for (vid_t p : myPreds)
           for (vid_t q : mySuccs) g.add_edge(p, q);
@@ -432,29 +444,30 @@ public:
   void erase(const op_t &op) { erase_vertex(must_find(*op)); }
   void erase_edge_only(const op_t &a, const op_t &b) {
     vid_t ia = must_find(*a), ib = must_find(*b);
-    remove_one(v_[ia].succs, ib);
-    remove_one(v_[ib].preds, ia);
+    auto &m = adj_mut();
+    remove_one(m[ia].succs, ib);
+    remove_one(m[ib].preds, ia);
   }
 
   // ops whose predecessors are all in `done` and that are not in `done`
   // themselves; comparison ignores stream bindings
   template <typename U> std::vector<op_t> frontier(const std::vector<std::shared_ptr<U>> &done) const {
-    std::vector<char> isDone(v_.size(), 0);
+    std::vector<char> isDone(ops_.size(), 0);
     for (const auto &d : done) {
       vid_t i = find_vertex_unbound(*d);
       if (i >= 0) isDone[i] = 1;
     }
     std::vector<op_t> r;
-    for (vid_t i = 0; i < static_cast<vid_t>(v_.size()); ++i) {
-      if (!v_[i].alive || isDone[i]) continue;
+    for (vid_t i = 0; i < static_cast<vid_t>(ops_.size()); ++i) {
+      if (!adj()[i].alive || isDone[i]) continue;
       bool ready = true;
-      for (vid_t p : v_[i].preds) {
+      for (vid_t p : adj()[i].preds) {
         if (!isDone[p]) {
           ready = false;
           break;
         }
       }
-      if (ready) r.push_back(v_[i].op);
+      if (ready) r.push_back(ops_[i]);
     }
     return r;
   }
@@ -463,25 +476,25 @@ public:
   // extends one path step by step uses
   std::vector<op_t> frontier_of_mask(const std::vector<char> &isDone) const {
     std::vector<op_t> r;
-    for (vid_t i = 0; i < static_cast<vid_t>(v_.size()); ++i) {
-      if (!v_[i].alive || (size_t(i) < isDone.size() && isDone[size_t(i)])) continue;
+    for (vid_t i = 0; i < static_cast<vid_t>(ops_.size()); ++i) {
+      if (!adj()[i].alive || (size_t(i) < isDone.size() && isDone[size_t(i)])) continue;
       bool ready = true;
-      for (vid_t p : v_[i].preds) {
+      for (vid_t p : adj()[i].preds) {
         if (!(size_t(p) < isDone.size() && isDone[size_t(p)])) {
           ready = false;
           break;
         }
       }
-      if (ready) r.push_back(v_[i].op);
+      if (ready) r.push_back(ops_[i]);
     }
     return r;
   }
   std::vector<vid_t> frontier_ids_of_mask(const std::vector<char> &isDone) const {
     std::vector<vid_t> r;
-    for (vid_t i = 0; i < static_cast<vid_t>(v_.size()); ++i) {
-      if (!v_[i].alive || (size_t(i) < isDone.size() && isDone[size_t(i)])) continue;
+    for (vid_t i = 0; i < static_cast<vid_t>(ops_.size()); ++i) {
+      if (!adj()[i].alive || (size_t(i) < isDone.size() && isDone[size_t(i)])) continue;
       bool ready = true;
-      for (vid_t p : v_[i].preds) {
+      for (vid_t p : adj()[i].preds) {
         if (!(size_t(p) < isDone.size() && isDone[size_t(p)])) {
           ready = false;
           break;
@@ -498,17 +511,17 @@ public:
   void mark_done(std::vector<char> &isDone, const OpBase &op) const {
     const vid_t i = find_vertex_unbound(op);
     if (i < 0) return;
-    if (isDone.size() < v_.size()) isDone.resize(v_.size(), 0);
+    if (isDone.size() < ops_.size()) isDone.resize(ops_.size(), 0);
     isDone[size_t(i)] = 1;
   }
 
   // ---- output ----
   std::string str() const {
     std::ostringstream ss;
-    for (const auto &v : v_) {
-      if (!v.alive) continue;
-      ss << v.op->desc() << " ->";
-      for (vid_t s : v.succs) ss << " " << v_[s].op->desc();
+    for (size_t i = 0; i < ops_.size(); ++i) {
+      if (!adj()[i].alive) continue;
+      ss << ops_[i]->desc() << " ->";
+      for (vid_t s : adj()[i].succs) ss << " " << ops_[size_t(s)]->desc();
       ss << "\n";
     }
     return ss.str();
@@ -517,22 +530,22 @@ public:
   std::string graphviz() const {
     std::ostringstream ss;
     ss << "digraph D {\n";
-    for (vid_t i = 0; i < static_cast<vid_t>(v_.size()); ++i) {
-      if (!v_[i].alive) continue;
-      ss << "  op_" << i << " [label=\"" << v_[i].op->name();
-      if (auto hs = std::dynamic_pointer_cast<HasStream>(v_[i].op)) {
+    for (vid_t i = 0; i < static_cast<vid_t>(ops_.size()); ++i) {
+      if (!adj()[i].alive) continue;
+      ss << "  op_" << i << " [label=\"" << ops_[i]->name();
+      if (auto hs = std::dynamic_pointer_cast<HasStream>(ops_[i])) {
         ss << "\\nstream";
         for (const Stream &s : hs->get_streams()) ss << " " << s.str();
       }
-      if (auto he = std::dynamic_pointer_cast<HasEvent>(v_[i].op)) {
+      if (auto he = std::dynamic_pointer_cast<HasEvent>(ops_[i])) {
         ss << "\\nevent";
         for (const Event &e : he->get_events()) ss << " " << e.str();
       }
       ss << "\"];\n";
     }
-    for (vid_t i = 0; i < static_cast<vid_t>(v_.size()); ++i) {
-      if (!v_[i].alive) continue;
-      for (vid_t s : v_[i].succs) ss << "  op_" << i << " -> op_" << s << ";\n";
+    for (vid_t i = 0; i < static_cast<vid_t>(ops_.size()); ++i) {
+      if (!adj()[i].alive) continue;
+      for (vid_t s : adj()[i].succs) ss << "  op_" << i << " -> op_" << s << ";\n";
     }
     ss << "}\n";
     return ss.str();
@@ -546,13 +559,14 @@ public:
 private:
   void erase_vertex(vid_t i) {
     if (i == start_ || i == finish_) THROW_RUNTIME("cannot erase Start/Finish");
-    for (vid_t p : v_[i].preds) remove_one(v_[p].succs, i);
-    for (vid_t s : v_[i].succs) remove_one(v_[s].preds, i);
-    v_[i].preds.clear();
-    v_[i].succs.clear();
-    v_[i].alive = false;
-    index_.erase(v_[i].op->uid());
-    uindex_.erase(v_[i].op->unbound_uid());
+    auto &m = adj_mut();
+    for (vid_t p : m[i].preds) remove_one(m[p].succs, i);
+    for (vid_t s : m[i].succs) remove_one(m[s].preds, i);
+    m[i].preds.clear();
+    m[i].succs.clear();
+    m[i].alive = false;
+    index_.erase(ops_[i]->uid());
+    uindex_.erase(ops_[i]->unbound_uid());
   }
 };
 

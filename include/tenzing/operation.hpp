@@ -104,11 +104,11 @@ public:
   virtual std::string unbound_key() const { return key(); }
 
   uint32_t uid() const {
-    if (!uid_) uid_ = intern_key(key());
+    if (!uid_) uid_ = intern_self();
     return uid_;
   }
   uint32_t unbound_uid() const {
-    if (!unboundUid_) unboundUid_ = intern_key(unbound_key());
+    if (!unboundUid_) unboundUid_ = intern_unbound_self();
     return unboundUid_;
   }
   bool eq(const OpBase &rhs) const { return uid() == rhs.uid(); }
@@ -127,6 +127,11 @@ public:
 protected:
   // call after changing a field that key() depends on
   void invalidate_identity() { uid_ = unboundUid_ = 0; }
+  // how uid() / unbound_uid() get their number; ops made by the thousand during a search
+  // override these with something cheaper than building and hashing the key string, and must
+  // return exactly intern_key(key()) / intern_key(unbound_key())
+  virtual uint32_t intern_self() const { return intern_key(key()); }
+  virtual uint32_t intern_unbound_self() const { return intern_key(unbound_key()); }
 };
 
 // not executable: several implementation alternatives for one logical operation

@@ -1,6 +1,8 @@
 #include "tenzing/cuda/ops_cuda.hpp"
 
+#include <mutex>
 #include <typeinfo>
+#include <unordered_map>
 
 #include "tenzing/host_streams.hpp"
 
@@ -47,17 +49,40 @@ void BoundGpuOp::run(Platform &plat) {
   op_->run(plat, plat.cuda_stream(stream_));
 }
 
-void SyncOpBase::make_name(const char *prefix, const OpSet &preds, const OpSet &succs) {
-  std::string n(prefix);
-  if (!preds.empty()) {
+void SyncOpBase::build_name() const {
+  std::string n(pendingPrefix_);
+  if (!pendingPreds_.empty()) {
     n += "-after";
-    for (const auto &p : preds) n += "-" + p->name();
+    for (const auto &p : pendingPreds_) n += "-" + p->name();
   }
-  if (!succs.empty()) {
+  if (!pendingSuccs_.empty()) {
     n += "-b4";
-    for (const auto &s : succs) n += "-" + s->name();
+    for (const auto &s : pendingSuccs_) n += "-" + s->name();
   }
   name_ = n;
+  pendingPrefix_ = nullptr;
+  pendingPreds_.clear();
+  pendingSuccs_.clear();
+}
+
+uint32_t SyncOpBase::intern_small(char kindTag, int a, int b, const OpBase &op) {
+  // (kind, a, b) -> the uid intern_key(op.key()) gave the first op of that description
+  struct Table {
+    std::mutex mu;
+    std::unordered_map<uint64_t, uint32_t> ids;
+  };
+  static Table *t = new Table(); // leaked on purpose, like the key table
+  if (a < -1 || b < -1 || a >= (1 << 24) || b >= (1 << 24)) return intern_key(op.key());
+  const uint64_t k = (uint64_t(uint8_t(kindTag)) << 56) | (uint64_t(uint32_t(a + 1)) << 28) | uint64_t(uint32_t(b + 1));
+  {
+    std::lock_guard<std::mutex> lk(t->mu);
+    auto it = t->ids.find(k);
+    if (it != t->ids.end()) return it->second;
+  }
+  const uint32_t id = intern_key(op.key());
+  std::lock_guard<std::mutex> lk(t->mu);
+  t->ids.emplace(k, id);
+  return id;
 }
 
 Json CudaEventRecord::json() const {
