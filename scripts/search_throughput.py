@@ -71,13 +71,22 @@ def main():
     ap.add_argument("--out", default="")
     ap.add_argument("--repeats", type=int, default=3)
     ap.add_argument("--ref-limit", type=float, default=600.0, help="seconds per reference run")
+    ap.add_argument("--reuse-reference", default="",
+                    help="take the reference's times from this earlier output file instead of running it again "
+                         "(its side does not change when this framework does)")
     args = ap.parse_args()
+    reused = {}
+    if args.reuse_reference:
+        for line in open(os.path.join(ROOT, args.reuse_reference)):
+            f = line.split()
+            if len(f) >= 8 and f[0].isdigit():
+                reused[(int(f[0]), int(f[1]))] = (int(f[5]), float(f[6]))
     lines = ["# noop-graph DFS enumeration on the CPU (one thread, best of %d): K chains of L NoOps" % args.repeats,
              "# chains len schedules_expected ours_schedules ours_s reference_schedules reference_s reference/ours"]
     for K, L in CASES:
         want = math.factorial(K * L) // math.factorial(L) ** K
         n_o, t_o = ours(K, L, args.repeats)
-        n_r, t_r = reference(K, L, 1 if want > 20000 else args.repeats, args.ref_limit)
+        n_r, t_r = reused.get((K, L)) or reference(K, L, 1 if want > 20000 else args.repeats, args.ref_limit)
         ratio = f"{t_r / t_o:.1f}" if isinstance(t_r, float) and t_o > 0 else "-"
         t_r_s = f"{t_r:.6f}" if isinstance(t_r, float) else str(t_r)
         lines.append(f"{K} {L} {want} {n_o} {t_o:.6f} {n_r} {t_r_s} {ratio}")
