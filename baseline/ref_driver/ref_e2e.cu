@@ -23,45 +23,59 @@
 #include "tenzing/dfs/dfs.hpp"
 
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
 
-typedef int Ordinal;
-typedef float Scalar;
-template <Where w> using csr_type = CsrMat<w, Ordinal, Scalar>;
+using Index = int;
+using Value = float; // the reference's SpMV ops accept float only
+using Clock = std::chrono::steady_clock;
+
+namespace {
+struct World {
+  int rank = 0, size = 1;
+};
+World join_world(int &argc, char **&argv) {
+  World w;
+  MPI_Init(&argc, &argv);
+  MPI_Comm_rank(MPI_COMM_WORLD, &w.rank);
+  MPI_Comm_size(MPI_COMM_WORLD, &w.size);
+  int nDev = 0;
+  CUDA_RUNTIME(cudaGetDeviceCount(&nDev));
+  CUDA_RUNTIME(cudaSetDevice(w.rank % nDev));
+  CUDA_RUNTIME(cudaFree(0));
+  return w;
+}
+} // namespace
 
 int main(int argc, char **argv) {
   const int steps = argc > 1 ? std::atoi(argv[1]) : 20;
   const int warmup = argc > 2 ? std::atoi(argv[2]) : 5;
   const int maxSeqs = argc > 3 ? std::atoi(argv[3]) : 48;
   tenzing::init(argc, argv);
-  MPI_Init(&argc, &argv);
-  int rank = 0, size = 1;
-  MPI_Comm_rank(MPI_COMM_WORLD, &rank);
-  MPI_Comm_size(MPI_COMM_WORLD, &size);
-  int devcount = 0;
-  CUDA_RUNTIME(cudaGetDeviceCount(&devcount));
-  CUDA_RUNTIME(cudaSetDevice(rank % devcount));
-  CUDA_RUNTIME(cudaFree(0));
+  const World world = join_world(argc, argv);
+  const int rank = world.rank;
 
-  // the problem of the reference's example
-  const int m = 150000, bw = m / size, nnz = m * 10;
-  csr_type<Where::host> A;
-  if (0 == rank) A = random_band_matrix<Ordinal, Scalar>(m, bw, nnz);
-  RowPartSpmv<Ordinal, Scalar> rps(A, 0, MPI_COMM_WORLD);
-  auto spmv = std::make_shared<SpMV<Ordinal, Scalar>>(rps, MPI_COMM_WORLD);
-  Graph<OpBase> orig;
-  orig.start_then(spmv);
-  orig.then_finish(spmv);
-  Platform plat = Platform::make_n_streams(2, MPI_COMM_WORLD);
+  // the problem of the reference's example: 150000 rows, 10 non-zeros per row, band m / ranks
+  const int rowsTotal = 150000;
+  CsrMat<Where::host, Index, Value> whole;
+  if (rank == 0) whole = random_band_matrix<Index, Value>(rowsTotal, rowsTotal / world.size, rowsTotal * 10);
+  RowPartSpmv<Index, Value> rps(whole, 0, MPI_COMM_WORLD);
+  Graph<OpBase> program;
+  {
+    auto product = std::make_shared<SpMV<Index, Value>>(rps, MPI_COMM_WORLD);
+    program.start_then(product);
+    program.then_finish(product);
+  }
+  Platform platform = Platform::make_n_streams(2, MPI_COMM_WORLD);
 
   // a schedule: the reference's solver over the first schedules it enumerates
-  EmpiricalBenchmarker benchmarker;
-  tenzing::dfs::Opts opts;
-  opts.benchOpts.nIters = 10;
-  opts.maxSeqs = maxSeqs;
-  tenzing::dfs::Result result = tenzing::dfs::explore(orig, plat, benchmarker, opts);
+  EmpiricalBenchmarker timer;
+  tenzing::dfs::Opts searchOpts;
+  searchOpts.maxSeqs = maxSeqs;
+  searchOpts.benchOpts.nIters = 10;
+  const tenzing::dfs::Result result = tenzing::dfs::explore(program, platform, timer, searchOpts);
   if (result.simResults.empty()) {
     if (0 == rank) std::printf("REF_E2E none\n");
     MPI_Finalize();
@@ -79,28 +93,28 @@ int main(int argc, char **argv) {
     if (HasEvent *he = dynamic_cast<HasEvent *>(op.get()))
       for (Event e : he->get_events())
         if (!rmap.contains(e)) rmap.insert(e, pool.new_event());
-  plat.resource_map() = rmap;
+  platform.resource_map() = rmap;
 
   // pinned host copies of this rank's x and y blocks
   const size_t nx = size_t(rps.lx().size()), ny = size_t(rps.ly().size());
-  Scalar *hx = nullptr, *hy = nullptr;
-  CUDA_RUNTIME(cudaHostAlloc(reinterpret_cast<void **>(&hx), std::max<size_t>(nx, 1) * sizeof(Scalar), cudaHostAllocDefault));
-  CUDA_RUNTIME(cudaHostAlloc(reinterpret_cast<void **>(&hy), std::max<size_t>(ny, 1) * sizeof(Scalar), cudaHostAllocDefault));
-  for (size_t i = 0; i < nx; ++i) hx[i] = Scalar(1) + Scalar(i % 7);
+  Value *hx = nullptr, *hy = nullptr;
+  CUDA_RUNTIME(cudaHostAlloc(reinterpret_cast<void **>(&hx), std::max<size_t>(nx, 1) * sizeof(Value), cudaHostAllocDefault));
+  CUDA_RUNTIME(cudaHostAlloc(reinterpret_cast<void **>(&hy), std::max<size_t>(ny, 1) * sizeof(Value), cudaHostAllocDefault));
+  for (size_t i = 0; i < nx; ++i) hx[i] = Value(1) + Value(i % 7);
   cudaStream_t io;
   CUDA_RUNTIME(cudaStreamCreate(&io));
-  Scalar *dx = const_cast<Scalar *>(rps.lx().data());
-  const Scalar *dy = rps.ly().data();
+  Value *dx = const_cast<Value *>(rps.lx().data());
+  const Value *dy = rps.ly().data();
 
   std::vector<double> t;
   for (int s = 0; s < warmup + steps; ++s) {
     CUDA_RUNTIME(cudaDeviceSynchronize());
     MPI_Barrier(MPI_COMM_WORLD);
     const double t0 = MPI_Wtime();
-    CUDA_RUNTIME(cudaMemcpyAsync(dx, hx, nx * sizeof(Scalar), cudaMemcpyHostToDevice, io));
+    CUDA_RUNTIME(cudaMemcpyAsync(dx, hx, nx * sizeof(Value), cudaMemcpyHostToDevice, io));
     CUDA_RUNTIME(cudaStreamSynchronize(io));
-    for (auto &op : seq) op->run(plat);
-    CUDA_RUNTIME(cudaMemcpyAsync(hy, dy, ny * sizeof(Scalar), cudaMemcpyDeviceToHost, io));
+    for (auto &op : seq) op->run(platform);
+    CUDA_RUNTIME(cudaMemcpyAsync(hy, dy, ny * sizeof(Value), cudaMemcpyDeviceToHost, io));
     CUDA_RUNTIME(cudaStreamSynchronize(io));
     double dt = MPI_Wtime() - t0;
     MPI_Allreduce(MPI_IN_PLACE, &dt, 1, MPI_DOUBLE, MPI_MAX, MPI_COMM_WORLD);
@@ -109,8 +123,8 @@ int main(int argc, char **argv) {
   std::sort(t.begin(), t.end());
   if (0 == rank && !t.empty())
     std::printf("REF_E2E median_us=%.3f p10_us=%.3f p90_us=%.3f h2d_bytes=%zu d2h_bytes=%zu schedule_pct10_us=%.3f\n",
-                t[t.size() / 2] * 1e6, t[t.size() / 10] * 1e6, t[t.size() * 9 / 10] * 1e6, nx * sizeof(Scalar),
-                ny * sizeof(Scalar), result.simResults[best].benchResult.pct10 * 1e6);
+                t[t.size() / 2] * 1e6, t[t.size() / 10] * 1e6, t[t.size() * 9 / 10] * 1e6, nx * sizeof(Value),
+                ny * sizeof(Value), result.simResults[best].benchResult.pct10 * 1e6);
   std::fflush(stdout);
   MPI_Finalize();
   return 0;
