@@ -86,3 +86,19 @@ def test_reference_arm_reads_the_end_to_end_line():
     assert got["median_us"] == pytest.approx(447.461) and got["h2d_bytes"] == 300000
     assert bench._ref_parse_e2e("REF_E2E none\n") is None
     assert bench._ref_parse_e2e("") is None
+
+
+def test_side_records_that_do_not_finish_cannot_take_the_line_down():
+    """with no time at all for the side records the line is still printed, says so, and the exit
+    code is 0 (two ranks: the one that is behind must leave as well)"""
+    env = dict(os.environ, TENZING_ACK_NOTICE="1")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+           "--master-addr", "127.0.0.1", "--master-port", str(29700 + os.getpid() % 100),
+           os.path.join(ROOT, "bench.py"), "--gpus", "2"] + ARGS + ["--side-budget", "0.001"]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=500, env=env, cwd=ROOT)
+    assert p.returncode == 0, p.stderr[-2000:]
+    lines = [l for l in p.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 1
+    rec = json.loads(lines[0])
+    assert rec["value"] > 0 and "halo" in rec and "spmv_1m" in rec
+    assert "side_records_incomplete" in rec or "oracle_pass" in rec
