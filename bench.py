@@ -280,6 +280,9 @@ def main():
                     help="reference arm: wall-clock limit of its end-to-end run (0 = skip it)")
     ap.add_argument("--ref-e2e-seqs", type=int, default=40,
                     help="reference arm: schedules its DFS generates before the end-to-end run picks the best")
+    ap.add_argument("--records-budget", type=float, default=1200.0,
+                    help="seconds the sub-records after the headline (halo, spmv_1m, spmv_random) get before the line "
+                         "is printed with what is complete")
     ap.add_argument("--side-budget", type=float, default=300.0,
                     help="seconds the side records (msg_sweep, oracle_pass) get before the line is printed without them")
     ap.add_argument("--host-dry-run", action="store_true",
@@ -560,111 +563,11 @@ def main():
     }
     del spmv32, replay_s
 
-    # ---------------- BASELINE config 3: 3-D halo exchange ----------------
-    if "halo" not in skip:
-        halo = HaloExchange(comm=comm, nX=args.nx, nQ=args.nq, nGhost=3, storage_order="XYZQ",
-                            neighbors=26, host=host)
-        if host:
-            halo.platform.set_host_execution(True)
-        halo.fill()
-        # the search: exhaustive inside every small fused implementation style, MCTS for
-        # fused_groups and over the ChoiceOp of ALL styles, reference structure included;
-        # most promising styles first, so a spent budget drops the least promising ones
-        fused = ["fused_mixed", "fused_staged", "fused_all", "fused_pipelined", "fused_groups", "fused_pull"]
-        seq_h = find_best(halo, "mcts", fused + ["choice"], args.search_iters, args.search_budget)
-        ok_h = run_and_check(halo, seq_h)
-        ok_all &= ok_h
-        times_h, launches_h, rec_h, replay_h = measure(halo, seq_h, args.steps, args.warmup)
-        # end to end: H2D of one fresh interior z-plane (all quantities), the exchange, D2H of a ghost row
-        a = halo.args
-        g = a.nGhost
-        plane = torch.randn(a.nQ, a.nY, a.nX, dtype=torch.float64)
-        row_out = torch.empty(a.nX, dtype=torch.float64)
-        if not host:
-            plane, row_out = plane.pin_memory(), row_out.pin_memory()
-        cells = halo.cells()
-        halo.platform.provision_events(seq_h)
-        e2e = []
-        for i in range(args.warmup + args.steps):
-            if not host:
-                _C.kernels.l2_flush(flush.data_ptr(), flush.numel(), i, 0)
-            device_sync()
-            comm.barrier()
-            t0 = time.perf_counter()
-            cells[:, g, g:g + a.nY, g:g + a.nX].copy_(plane, non_blocking=True)
-            stream_sync()
-            if replay_h is not None:
-                replay_h.launch()
-                halo.platform.synchronize()
-            else:
-                seq_h.run(halo.platform)
-            row_out.copy_(cells[0, 0, g, g:g + a.nX], non_blocking=True)
-            stream_sync()
-            e2e.append(time.perf_counter() - t0)
-        e2e_h = [v * 1e6 for v in max_over_ranks(e2e[args.warmup:])]
-        us_h = statistics.mean(times_h) * 1e6
-        bytes_out = halo.bytes_per_exchange()
-        remote = halo.remote_bytes_per_exchange()
-        # roofline: the slower of (bytes over NVLink / link bw) and (HBM bytes / HBM bw); every halo
-        # byte is read once and written once somewhere (locally or on the peer)
-        roof_h = max(remote / nvl, (2 * bytes_out - remote) / hbm)
-        out["halo"] = {"us": round(us_h, 3), **rec_h, **stats([t * 1e6 for t in times_h]),
-                       "config": f"halo {args.nx}^3 fp64/rank nQ={args.nq} radius 3, 26 neighbours, XYZQ, "
-                                 "rank grid " + "x".join(map(str, halo.domain.rank_grid())),
-                       "schedule": seq_h.names(), "correct": bool(ok_h),
-                       "bytes_out_per_rank": bytes_out, "remote_bytes_per_rank": remote,
-                       "roofline_us": round(roof_h * 1e6, 3),
-                       "roofline_frac_of_measured": round(roof_h * 1e6 / us_h, 4),
-                       "gbs_per_rank": round(bytes_out / (us_h * 1e-6) / 1e9, 1),
-                       "gpu_launches": int(launches_h),
-                       "e2e_us": stats(e2e_h), "e2e_h2d_bytes": plane.numel() * 8, "e2e_d2h_bytes": row_out.numel() * 8}
-        del replay_h, halo, cells
-
-    # ---------------- BASELINE config 2: band SpMV 1M x 1M, fp64, DFS ----------------
-    if "spmv_1m" not in skip:
-        big = DistributedSpMV(comm=comm, n=args.spmv_big_n, nnz_per_row=10, host=host)
-        if host:
-            big.platform.set_host_execution(True)
-        big.fill()
-        seq_b = find_best(big, "dfs", SPMV_STYLES, 64, args.search_budget / 2)
-        ok_b = run_and_check(big, seq_b)
-        ok_all &= ok_b
-        times_b, launches_b, rec_b, replay_b = measure(big, seq_b, args.steps, args.warmup)
-        us_b = statistics.mean(times_b) * 1e6
-        roof_b = max((big.recv_bytes() if world > 1 else 0) / nvl, big.hbm_bytes() / hbm)
-        out["spmv_1m"] = {"us": round(us_b, 3), **rec_b, **stats([t * 1e6 for t in times_b]), "n": args.spmv_big_n,
-                          "schedule": seq_b.names(), "correct": bool(ok_b), "roofline_us": round(roof_b * 1e6, 3),
-                          "roofline_frac_of_measured": round(roof_b * 1e6 / us_b, 4),
-                          "gpu_launches": int(launches_b)}
-        del replay_b, big
-
-    # ---------------- BASELINE config 4: random-sparse SpMV, MCTS, 3 streams ----------------
-    if "spmv_random" not in skip and not host:
-        n_r = args.random_rows_per_gpu * world
-        rnd = DistributedSpMV(comm=comm, n=n_r, bw=n_r, nnz_per_row=10, n_streams=3)
-        rnd.fill()
-        if args.no_search:
-            seq_r = common.fixed_schedule(rnd.graph("fused_all"), rnd.platform)
-        else:
-            bo = common.bench_opts(n_iters=3, target_secs=0.002, max_retries=0, check_randomness=False)
-            res = rnd.search("mcts", style="choice", iters=args.search_iters, bench=bo, strategy="FastMin", cache=True)
-            seq_r, _ = common.best_of(res)
-        ok_r = run_and_check(rnd, seq_r)
-        ok_all &= ok_r
-        times_r, launches_r, rec_r, replay_r = measure(rnd, seq_r, args.steps, args.warmup)
-        us_r = statistics.mean(times_r) * 1e6
-        roof_r = max((rnd.recv_bytes() if world > 1 else 0) / nvl, rnd.hbm_bytes() / hbm)
-        out["spmv_random"] = {"us": round(us_r, 3), **rec_r, **stats([t * 1e6 for t in times_r]), "n": n_r, "streams": 3,
-                              "search": f"MCTS FastMin {args.search_iters} iterations over the ChoiceOp of all styles",
-                              "schedule": seq_r.names(), "correct": bool(ok_r),
-                              "roofline_us": round(roof_r * 1e6, 3),
-                              "roofline_frac_of_measured": round(roof_r * 1e6 / us_r, 4),
-                              "gpu_launches": int(launches_r)}
-        del replay_r, rnd
-
-    # The two side records below are not the headline and must not be able to take it down: if
-    # they fail, or have not finished after --side-budget seconds (a rank stuck in a collective
-    # behind a failed peer), rank 0 prints the line with what is complete and every rank leaves.
+    # From here on the headline record is complete.  Everything below adds sub-records and must
+    # not be able to take it down: if a section fails (say a device wait that trapped, after
+    # which the CUDA context is gone), or the rest has not finished after --records-budget seconds
+    # (a rank stuck in a collective behind a failed peer), rank 0 prints the line with what is
+    # complete, says so in it, and every rank leaves with exit code 0.
     import threading
     done_lock = threading.Lock()
     state = {"printed": False, "ok_all": ok_all}
@@ -675,18 +578,132 @@ def main():
                 return False
             state["printed"] = True
         if note:
-            out["side_records_incomplete"] = note
+            out["records_incomplete"] = note
             out["correct"] = bool(state["ok_all"])
         out["setup_and_search_seconds"] = round(time.time() - t_setup, 1)
         if rank == 0:
             print(json.dumps(out), flush=True)
         return True
 
-    def failsafe():
-        if emit(f"msg_sweep / oracle_pass did not finish within {args.side_budget:.0f} s; every other record is complete"):
+    def failsafe(what, seconds):
+        if emit(f"{what} did not finish within {seconds:.0f} s; the records present are complete"):
             os._exit(0)
 
-    timer = threading.Timer(args.side_budget, failsafe)
+    timer = threading.Timer(args.records_budget, failsafe, ("the sub-records", args.records_budget))
+    timer.daemon = True
+    timer.start()
+    try:
+        # ---------------- BASELINE config 3: 3-D halo exchange ----------------
+        if "halo" not in skip:
+            halo = HaloExchange(comm=comm, nX=args.nx, nQ=args.nq, nGhost=3, storage_order="XYZQ",
+                                neighbors=26, host=host)
+            if host:
+                halo.platform.set_host_execution(True)
+            halo.fill()
+            # the search: exhaustive inside every small fused implementation style, MCTS for
+            # fused_groups and over the ChoiceOp of ALL styles, reference structure included;
+            # most promising styles first, so a spent budget drops the least promising ones
+            fused = ["fused_mixed", "fused_staged", "fused_all", "fused_pipelined", "fused_groups", "fused_pull"]
+            seq_h = find_best(halo, "mcts", fused + ["choice"], args.search_iters, args.search_budget)
+            ok_h = run_and_check(halo, seq_h)
+            ok_all &= ok_h
+            times_h, launches_h, rec_h, replay_h = measure(halo, seq_h, args.steps, args.warmup)
+            # end to end: H2D of one fresh interior z-plane (all quantities), the exchange, D2H of a ghost row
+            a = halo.args
+            g = a.nGhost
+            plane = torch.randn(a.nQ, a.nY, a.nX, dtype=torch.float64)
+            row_out = torch.empty(a.nX, dtype=torch.float64)
+            if not host:
+                plane, row_out = plane.pin_memory(), row_out.pin_memory()
+            cells = halo.cells()
+            halo.platform.provision_events(seq_h)
+            e2e = []
+            for i in range(args.warmup + args.steps):
+                if not host:
+                    _C.kernels.l2_flush(flush.data_ptr(), flush.numel(), i, 0)
+                device_sync()
+                comm.barrier()
+                t0 = time.perf_counter()
+                cells[:, g, g:g + a.nY, g:g + a.nX].copy_(plane, non_blocking=True)
+                stream_sync()
+                if replay_h is not None:
+                    replay_h.launch()
+                    halo.platform.synchronize()
+                else:
+                    seq_h.run(halo.platform)
+                row_out.copy_(cells[0, 0, g, g:g + a.nX], non_blocking=True)
+                stream_sync()
+                e2e.append(time.perf_counter() - t0)
+            e2e_h = [v * 1e6 for v in max_over_ranks(e2e[args.warmup:])]
+            us_h = statistics.mean(times_h) * 1e6
+            bytes_out = halo.bytes_per_exchange()
+            remote = halo.remote_bytes_per_exchange()
+            # roofline: the slower of (bytes over NVLink / link bw) and (HBM bytes / HBM bw); every halo
+            # byte is read once and written once somewhere (locally or on the peer)
+            roof_h = max(remote / nvl, (2 * bytes_out - remote) / hbm)
+            out["halo"] = {"us": round(us_h, 3), **rec_h, **stats([t * 1e6 for t in times_h]),
+                           "config": f"halo {args.nx}^3 fp64/rank nQ={args.nq} radius 3, 26 neighbours, XYZQ, "
+                                     "rank grid " + "x".join(map(str, halo.domain.rank_grid())),
+                           "schedule": seq_h.names(), "correct": bool(ok_h),
+                           "bytes_out_per_rank": bytes_out, "remote_bytes_per_rank": remote,
+                           "roofline_us": round(roof_h * 1e6, 3),
+                           "roofline_frac_of_measured": round(roof_h * 1e6 / us_h, 4),
+                           "gbs_per_rank": round(bytes_out / (us_h * 1e-6) / 1e9, 1),
+                           "gpu_launches": int(launches_h),
+                           "e2e_us": stats(e2e_h), "e2e_h2d_bytes": plane.numel() * 8, "e2e_d2h_bytes": row_out.numel() * 8}
+            del replay_h, halo, cells
+
+        # ---------------- BASELINE config 2: band SpMV 1M x 1M, fp64, DFS ----------------
+        if "spmv_1m" not in skip:
+            big = DistributedSpMV(comm=comm, n=args.spmv_big_n, nnz_per_row=10, host=host)
+            if host:
+                big.platform.set_host_execution(True)
+            big.fill()
+            seq_b = find_best(big, "dfs", SPMV_STYLES, 64, args.search_budget / 2)
+            ok_b = run_and_check(big, seq_b)
+            ok_all &= ok_b
+            times_b, launches_b, rec_b, replay_b = measure(big, seq_b, args.steps, args.warmup)
+            us_b = statistics.mean(times_b) * 1e6
+            roof_b = max((big.recv_bytes() if world > 1 else 0) / nvl, big.hbm_bytes() / hbm)
+            out["spmv_1m"] = {"us": round(us_b, 3), **rec_b, **stats([t * 1e6 for t in times_b]), "n": args.spmv_big_n,
+                              "schedule": seq_b.names(), "correct": bool(ok_b), "roofline_us": round(roof_b * 1e6, 3),
+                              "roofline_frac_of_measured": round(roof_b * 1e6 / us_b, 4),
+                              "gpu_launches": int(launches_b)}
+            del replay_b, big
+
+        # ---------------- BASELINE config 4: random-sparse SpMV, MCTS, 3 streams ----------------
+        if "spmv_random" not in skip and not host:
+            n_r = args.random_rows_per_gpu * world
+            rnd = DistributedSpMV(comm=comm, n=n_r, bw=n_r, nnz_per_row=10, n_streams=3)
+            rnd.fill()
+            if args.no_search:
+                seq_r = common.fixed_schedule(rnd.graph("fused_all"), rnd.platform)
+            else:
+                bo = common.bench_opts(n_iters=3, target_secs=0.002, max_retries=0, check_randomness=False)
+                res = rnd.search("mcts", style="choice", iters=args.search_iters, bench=bo, strategy="FastMin", cache=True)
+                seq_r, _ = common.best_of(res)
+            ok_r = run_and_check(rnd, seq_r)
+            ok_all &= ok_r
+            times_r, launches_r, rec_r, replay_r = measure(rnd, seq_r, args.steps, args.warmup)
+            us_r = statistics.mean(times_r) * 1e6
+            roof_r = max((rnd.recv_bytes() if world > 1 else 0) / nvl, rnd.hbm_bytes() / hbm)
+            out["spmv_random"] = {"us": round(us_r, 3), **rec_r, **stats([t * 1e6 for t in times_r]), "n": n_r, "streams": 3,
+                                  "search": f"MCTS FastMin {args.search_iters} iterations over the ChoiceOp of all styles",
+                                  "schedule": seq_r.names(), "correct": bool(ok_r),
+                                  "roofline_us": round(roof_r * 1e6, 3),
+                                  "roofline_frac_of_measured": round(roof_r * 1e6 / us_r, 4),
+                                  "gpu_launches": int(launches_r)}
+            del replay_r, rnd
+
+        state["ok_all"] = ok_all
+    except Exception as e:  # noqa: BLE001
+        timer.cancel()
+        if emit(f"a sub-record failed: {str(e)[:200]}"):
+            os._exit(0)
+    timer.cancel()
+
+    # The two side records get their own, shorter budget.
+    timer = threading.Timer(args.side_budget, failsafe, ("msg_sweep / oracle_pass", args.side_budget))
     timer.daemon = True
     timer.start()
     try:
@@ -698,7 +715,7 @@ def main():
         out["correct"] = bool(ok.item() > 0.5)
     except Exception as e:  # noqa: BLE001 - e.g. a device wait that trapped: the context is gone, the line is not
         timer.cancel()
-        if emit(f"side records failed: {str(e)[:200]}"):
+        if emit(f"msg_sweep / oracle_pass failed: {str(e)[:200]}"):
             os._exit(0)
     timer.cancel()
     emit()

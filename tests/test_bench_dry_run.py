@@ -101,4 +101,4 @@ def test_side_records_that_do_not_finish_cannot_take_the_line_down():
     assert len(lines) == 1
     rec = json.loads(lines[0])
     assert rec["value"] > 0 and "halo" in rec and "spmv_1m" in rec
-    assert "side_records_incomplete" in rec or "oracle_pass" in rec
+    assert "records_incomplete" in rec or "oracle_pass" in rec
