@@ -3,10 +3,11 @@
 // Reference: include/tenzing/graph.hpp:19-580, src/graph.cpp:13-420.  Same
 // vocabulary (start_then / then / then_finish / clone_but_replace /
 // clone_but_expand / frontier / dump_graphviz ...), different representation:
-// vertices live in a dense vector, edges are integer adjacency lists and a
-// hash index maps an op's interned uid to its vertex.  Rewrites copy the
-// (small) index arrays and share the op objects, so the solvers can afford a
-// graph per decision.
+// vertices are slots of a dense op table, edges are integer adjacency lists
+// (short ones stored inline) in a block that copies share until an edge
+// changes, and sorted flat arrays map an op's interned uid to its slot.
+// Rewrites share the op objects, so the solvers can afford a graph per
+// decision: binding one op copies the op table and the two indexes.
 #pragma once
 
 #include <algorithm>

@@ -3,7 +3,10 @@
 //
 // Reference: include/tenzing/state.hpp:15-54, src/state.cpp:5-143.
 // The graph is held through a shared pointer, so the common decision
-// (ExecuteOp) copies only the sequence.
+// (ExecuteOp) copies the sequence and a few small tables: what a state has
+// already worked out about its path (digest, executed and synchronised
+// vertices, the synchronizer's index) goes to its successors, which then
+// only account for the op they add.
 #pragma once
 
 #include <cstdint>
