@@ -19,6 +19,7 @@
 
 #include <cstdint>
 #include <functional>
+#include <atomic>
 #include <memory>
 #include <set>
 #include <string>
@@ -69,26 +70,32 @@ enum : uint16_t {
 } // namespace op_trait
 
 class OpBase {
-  mutable uint32_t uid_ = 0; // 0 = not interned yet
-  mutable uint32_t unboundUid_ = 0;
-  mutable uint16_t traits_ = 0; // 0 = not worked out yet
+  // Caches filled on first use.  Relaxed atomics: two threads that race to fill one compute the
+  // same value, and ops are shared between the threads of a multi-rank-in-one-process run.
+  mutable std::atomic<uint32_t> uid_{0}; // 0 = not interned yet
+  mutable std::atomic<uint32_t> unboundUid_{0};
+  mutable std::atomic<uint16_t> traits_{0}; // 0 = not worked out yet
   uint16_t compute_traits() const;
 
 public:
   OpBase() = default;
   // copies must re-intern (a derived copy-constructor may change key fields)
-  OpBase(const OpBase &) : uid_(0), unboundUid_(0), traits_(0) {}
+  OpBase(const OpBase &) {}
   OpBase &operator=(const OpBase &) {
-    uid_ = unboundUid_ = 0;
-    traits_ = 0;
+    invalidate_identity();
+    traits_.store(0, std::memory_order_relaxed);
     return *this;
   }
   virtual ~OpBase() = default;
 
   // op_trait bits of this object's dynamic type
   uint16_t traits() const {
-    if (!traits_) traits_ = compute_traits();
-    return traits_;
+    uint16_t t = traits_.load(std::memory_order_relaxed);
+    if (!t) {
+      t = compute_traits();
+      traits_.store(t, std::memory_order_relaxed);
+    }
+    return t;
   }
   bool is(uint16_t trait) const { return (traits() & trait) != 0; }
 
@@ -104,12 +111,20 @@ public:
   virtual std::string unbound_key() const { return key(); }
 
   uint32_t uid() const {
-    if (!uid_) uid_ = intern_self();
-    return uid_;
+    uint32_t u = uid_.load(std::memory_order_relaxed);
+    if (!u) {
+      u = intern_self();
+      uid_.store(u, std::memory_order_relaxed);
+    }
+    return u;
   }
   uint32_t unbound_uid() const {
-    if (!unboundUid_) unboundUid_ = intern_unbound_self();
-    return unboundUid_;
+    uint32_t u = unboundUid_.load(std::memory_order_relaxed);
+    if (!u) {
+      u = intern_unbound_self();
+      unboundUid_.store(u, std::memory_order_relaxed);
+    }
+    return u;
   }
   bool eq(const OpBase &rhs) const { return uid() == rhs.uid(); }
   bool eq(const std::shared_ptr<const OpBase> &rhs) const { return rhs && uid() == rhs->uid(); }
@@ -126,7 +141,10 @@ public:
 
 protected:
   // call after changing a field that key() depends on
-  void invalidate_identity() { uid_ = unboundUid_ = 0; }
+  void invalidate_identity() {
+    uid_.store(0, std::memory_order_relaxed);
+    unboundUid_.store(0, std::memory_order_relaxed);
+  }
   // how uid() / unbound_uid() get their number; ops made by the thousand during a search
   // override these with something cheaper than building and hashing the key string, and must
   // return exactly intern_key(key()) / intern_key(unbound_key())
