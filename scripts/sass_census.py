@@ -1,6 +1,7 @@
 #!/usr/bin/env python
 """SASS census of the kernel library: per kernel, the memory / synchronisation / tensor / TMA
-instructions in the sm_100a SASS (cuobjdump -sass).  Writes profiles/sass_census.txt.
+instructions in the sm_100a SASS (cuobjdump -sass).  Writes profiles/sass_census.txt and the
+listings of the measured kernels under profiles/sass/.
 
   python scripts/sass_census.py [path/to/libtenzing_b200_kernels.so]
 """
@@ -45,8 +46,55 @@ def strip_params(name):
     return name
 
 
+# the listings kept under profiles/sass/: file name -> the demangled kernel it holds (fp64 instances)
+LISTINGS = {
+    "box_copy_kernel_f64": "box_copy_kernel<double, (bool)0>",
+    "box_copy_kernel_f64_vec": "box_copy_kernel<double, (bool)1>",
+    "box_copy_sync_kernel_f64": "box_copy_sync_kernel<double, (int)4>",
+    "box_copy_sync_kernel_f64_ordered": "box_copy_sync_kernel<double, (int)2>",
+    "box_bulk_kernel": "box_bulk_kernel",
+    "flags_signal_kernel": "flags_signal_kernel",
+    "flags_wait_kernel": "flags_wait_kernel",
+    "gather_put_kernel_f64": "gather_put_kernel<double>",
+    "multicast_put_kernel_f64": "multicast_put_kernel<double>",
+    "spmv_csr_pull_kernel_f64_tpr8": "spmv_csr_pull_kernel<double, (int)8>",
+    "spmv_csr_stream_kernel_f64_u12": "spmv_csr_stream_kernel<double, (int)12, (bool)0>",
+    "spmv_csr_stream_kernel_f64_u12_wait": "spmv_csr_stream_kernel<double, (int)12, (bool)1>",
+    "spmv_fused_all_kernel_f64_u12": "spmv_fused_all_kernel<double, (int)12>",
+}
+
+
+def write_listings(sass):
+    """profiles/sass/<name>.sass: the instruction stream of each kernel of LISTINGS, encodings stripped"""
+    blocks, cur = collections.OrderedDict(), None
+    for line in sass.splitlines():
+        m = re.search(r"Function : (\S+)", line)
+        if m:
+            cur = m.group(1)
+            blocks[cur] = []
+            continue
+        if cur and re.match(r"\s+/\*[0-9a-f]{4}\*/", line):
+            blocks[cur].append(re.sub(r"\s*/\* 0x[0-9a-f]+ \*/\s*$", "", line))
+    names = demangle(list(blocks))
+    outdir = os.path.join(ROOT, "profiles", "sass")
+    os.makedirs(outdir, exist_ok=True)
+    written = 0
+    for fname, want in LISTINGS.items():
+        for mangled, name in zip(blocks, names):
+            short = strip_params(re.sub(r"^void ", "", name))
+            if short.endswith("::" + want) or short == want:
+                with open(os.path.join(outdir, fname + ".sass"), "w") as f:
+                    f.write("// " + name + "\n" + "\n".join(blocks[mangled]) + "\n")
+                written += 1
+                break
+        else:
+            print("no kernel matches", want)
+    print(f"{written} listings -> {outdir}")
+
+
 def main():
     sass = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True, check=True).stdout
+    write_listings(sass)
     kernels, cur = collections.OrderedDict(), None
     for line in sass.splitlines():
         m = re.search(r"Function : (\S+)", line)
