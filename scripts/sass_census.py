@@ -92,9 +92,37 @@ def write_listings(sass):
     print(f"{written} listings -> {outdir}")
 
 
+def write_resources():
+    """profiles/kernel_resources.txt: registers, stack (spills), static shared memory per kernel"""
+    text = subprocess.run(["cuobjdump", "--dump-resource-usage", LIB], capture_output=True, text=True, check=True).stdout
+    rows, mangled = [], None
+    for line in text.splitlines():
+        m = re.match(r"\s*Function (\S+):", line)
+        if m:
+            mangled = m.group(1)
+            continue
+        m = re.match(r"\s*REG:(\d+) STACK:(\d+) SHARED:(\d+) LOCAL:(\d+)", line)
+        if m and mangled:
+            rows.append((mangled,) + tuple(int(v) for v in m.groups()))
+            mangled = None
+    names = demangle([r[0] for r in rows])
+    path = os.path.join(ROOT, "profiles", "kernel_resources.txt")
+    with open(path, "w") as f:
+        f.write("# cuobjdump --dump-resource-usage of libtenzing_b200_kernels.so (sm_100a): registers per thread,\n"
+                "# stack bytes per thread (non-zero = spills or local arrays), static shared memory bytes per block\n"
+                "# (scripts/sass_census.py).  64 registers x 256 threads = 4 blocks per SM; 32 x 256 = 8.\n"
+                "# box_copy_sync_kernel<*, 2> (the ordered plans of fused_groups / fused_pipelined) is held to 64\n"
+                "# registers so that its partner kernel is guaranteed SM slots beside it; it pays 120 bytes of stack.\n")
+        for (m_, reg, stack, shared, local), name in zip(rows, names):
+            short = strip_params(re.sub(r"^void ", "", re.sub(r"\(anonymous namespace\)::|<unnamed>::", "", name)))
+            f.write(f"{short}: REG {reg} STACK {stack} SHARED {shared} LOCAL {local}\n")
+    print(f"{len(rows)} kernels -> {path}")
+
+
 def main():
     sass = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True, check=True).stdout
     write_listings(sass)
+    write_resources()
     kernels, cur = collections.OrderedDict(), None
     for line in sass.splitlines():
         m = re.search(r"Function : (\S+)", line)
