@@ -86,8 +86,12 @@ def checkout(dst):
     """copy of the reference sources as a tagged git checkout (its CMake derives the version
     header from `git describe --tags`)"""
     if not os.path.isdir(REF_SRC):
-        # on a GPU box only the copy that travelled with the repository exists
+        # on a GPU box only the copy that travelled with the repository exists; if it travelled
+        # without its .git directory it is made a tagged checkout again
         if os.path.isdir(os.path.join(dst, ".git")):
+            return
+        if os.path.isfile(os.path.join(dst, "CMakeLists.txt")):
+            tag_checkout(dst, "reference snapshot")
             return
         raise SystemExit(f"reference sources not found: neither {REF_SRC} nor {dst}")
     if os.path.exists(dst):
