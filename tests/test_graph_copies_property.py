@@ -81,9 +81,19 @@ def test_changing_a_copy_never_changes_the_original(seed, n, steps):
             copy.erase(live[k])
             model = {e for e in model if k not in e}
             del live[k]
+            # keep the copy well formed: whoever lost its last predecessor / successor is
+            # attached to Start / Finish (builds with TENZING_RUNTIME_SANITY_CHECKS insist)
+            for d, op in live.items():
+                if not any(b == d for _a, b in model):
+                    copy.start_then(op)
+                    model.add(("Start", d))
+                if not any(a == d for a, _b in model):
+                    copy.then_finish(op)
+                    model.add((d, "Finish"))
         elif what == "copy_again":
             other = tz.Graph(copy)       # a copy of the copy, changed and thrown away
-            other.erase(live[rng.choice(names)]) if len(names) > 1 else None
+            if len(names) > 1:
+                other.erase(live[rng.choice(names)])
         assert edges_of(copy) == model
     # the original is what it was
     assert edges_of(g) == want_edges
