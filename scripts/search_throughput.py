@@ -97,6 +97,20 @@ def main():
     import tenzing_b200 as tz
     from tenzing_b200 import _C
     from tenzing_b200.models import DistributedSpMV, HaloExchange
+    # exhaustive enumeration of the workload graphs with GPU ops (two streams; this framework only -
+    # the reference needs a GPU to build these graphs; its stock SpMV driver spends about 40 s on the
+    # same 2036 schedules before its first benchmark)
+    lines.append("# DFS enumeration of workload graphs, 2 streams: workload style distinct_schedules seconds")
+    spmv_e = DistributedSpMV(n=4000, nnz_per_row=6, host=True)
+    for style in ("reference", "fused", "choice"):
+        g = spmv_e.graph(style)
+        best, n = float("inf"), 0
+        for _ in range(args.repeats):
+            t0 = time.perf_counter()
+            n = len(tz.dfs.get_all_sequences(g, spmv_e.platform, 200000))
+            best = min(best, time.perf_counter() - t0)
+        lines.append(f"spmv {style} {n} {best:.4f}")
+        print(lines[-1], flush=True)
     lines.append("# MCTS (FastMin, rollouts expanded into the tree), constant-cost benchmarker: workload style ops_per_schedule rollouts ms_per_rollout")
     halo = HaloExchange(nX=16, nQ=1, nGhost=1, n_streams=2, host=True)
     spmv = DistributedSpMV(n=4000, nnz_per_row=6, host=True)
